@@ -1,0 +1,2 @@
+from .fused_ddp import FusedDDP  # noqa: F401
+from .optimizer import FusedAdamW  # noqa: F401

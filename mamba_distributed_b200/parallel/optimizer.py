@@ -1,0 +1,94 @@
+"""``FusedAdamW`` — AdamW over the flat arenas of :class:`FusedDDP`.
+
+Replaces the tail of the reference's step (/root/reference/train.py:221-227):
+``clip_grad_norm_(…, 1.0)`` + per-group LR set + ``torch.optim.AdamW(fused=True).step()``
+(constructed at /root/reference/model.py:141-148 with betas (0.9, 0.95), eps 1e-8).
+
+``step(max_norm=...)`` returns the global gradient norm (what ``clip_grad_norm_`` returns) and
+performs, in order: finish the gradient mean over ranks, global L2 norm, clip coefficient
+``min(1, max_norm / (norm + 1e-6))``, decoupled-weight-decay Adam on the fp32 master, refresh
+of the bf16 compute copy.  On the GPU ``comm="fused"`` path this is two kernel launches
+(``csrc/comm_adamw.cu``): optimizer state is sharded over ranks (ZeRO-1), each rank updates
+its shard and stores the new bf16 parameters into every peer's arena over NVLink.  On CPU
+(and ``comm="allreduce"``) the same arithmetic runs as flat PyTorch ops.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+
+
+class FusedAdamW:
+    def __init__(self, ddp, param_groups, lr=6e-4, betas=(0.9, 0.95), eps=1e-8):
+        self.ddp = ddp
+        self.betas, self.eps = betas, eps
+        self.param_groups = [dict(g, lr=lr) for g in param_groups]
+        self.step_count = 0
+        # per-element weight decay expressed as merged arena segments
+        wd_of = {}
+        for g in self.param_groups:
+            for p in g["params"]:
+                wd_of[id(p)] = (g["weight_decay"], g)
+        segs = []
+        for p, off in zip(ddp.params, ddp.offsets):
+            wd, g = wd_of[id(p)]
+            gi = self.param_groups.index(g)
+            end = off + (p.numel() + 15) // 16 * 16
+            if segs and segs[-1][2] == gi and segs[-1][1] == off:
+                segs[-1] = (segs[-1][0], end, gi)
+            else:
+                segs.append((off, end, gi))
+        self.segments = segs  # (start, end, group index)
+        dev = ddp.device
+        if ddp.comm == "fused":
+            self.impl = ddp.symm.make_optimizer(self)
+        else:
+            self.impl = None
+            self.m = torch.zeros(ddp.total, dtype=torch.float32, device=dev)
+            self.v = torch.zeros(ddp.total, dtype=torch.float32, device=dev)
+
+    # -------------------------------------------------------------- torch-like surface
+    def zero_grad(self, set_to_none=False):
+        self.ddp.zero_grad()
+
+    def state_dict(self):
+        if self.impl is not None:
+            return self.impl.state_dict()
+        return {"step": self.step_count, "m": self.m.cpu(), "v": self.v.cpu(),
+                "lrs": [g["lr"] for g in self.param_groups]}
+
+    def load_state_dict(self, sd):
+        if self.impl is not None:
+            return self.impl.load_state_dict(sd)
+        self.step_count = sd["step"]
+        self.m.copy_(sd["m"])
+        self.v.copy_(sd["v"])
+
+    # -------------------------------------------------------------- step
+    @torch.no_grad()
+    def step(self, max_norm=None):
+        self.step_count += 1
+        if self.impl is not None:
+            return self.impl.step(self, max_norm)
+        ddp = self.ddp
+        g = ddp.flat_grad
+        norm = torch.linalg.vector_norm(g)
+        if max_norm is not None:
+            coef = torch.clamp(max_norm / (norm + 1e-6), max=1.0)
+            g.mul_(coef)
+        b1, b2 = self.betas
+        t = self.step_count
+        bc1, bc2 = 1.0 - b1 ** t, 1.0 - b2 ** t
+        self.m.mul_(b1).add_(g, alpha=1.0 - b1)
+        self.v.mul_(b2).addcmul_(g, g, value=1.0 - b2)
+        for s, e, gi in self.segments:
+            grp = self.param_groups[gi]
+            lr, wd = grp["lr"], grp["weight_decay"]
+            p = ddp.flat_param[s:e]
+            if wd != 0.0:
+                p.mul_(1.0 - lr * wd)
+            denom = (self.v[s:e].sqrt() / math.sqrt(bc2)).add_(self.eps)
+            p.addcdiv_(self.m[s:e], denom, value=-lr / bc1)
+        ddp.refresh_bf16()
+        return norm
