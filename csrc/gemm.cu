@@ -1,0 +1,331 @@
+// K16: bf16 GEMM on tcgen05 / TMEM / TMA for sm_100a.
+//
+// Replaces the cuBLAS GEMMs behind nn.Linear (in_proj / out_proj / x_proj / dt_proj / lm_head;
+// SURVEY.md section 2.3 row K16) in all three layouts autograd needs:
+//   forward  y  = x  W^T   : A K-major [M,K],   B K-major  [N,K]
+//   dgrad    dx = dy W     : A K-major [M,N'],  B MN-major [N',K]   (W read as stored)
+//   wgrad    dW += dy^T x  : A MN-major [M',N], B MN-major [M',K]   (activations read as stored)
+// so no operand is ever transposed in memory.  wgrad accumulates in fp32 straight into the
+// gradient arena (vector reductions), which is also what makes split-K free.
+//
+// Structure (one CTA per SM, persistent over output tiles, 6 warps):
+//   warp 0    TMA producer   cp.async.bulk.tensor -> 128B-swizzled smem ring, mbarrier tx-count
+//   warp 1    MMA issuer     tcgen05.mma.cta_group::1.kind::f16, 128 x BN x 16, fp32 accum in TMEM;
+//                            tcgen05.commit releases smem stages and publishes the accumulator
+//   warps 2-5 epilogue       tcgen05.ld (32 lanes x 32 cols) -> registers -> global
+// Two TMEM accumulators (2 x BN columns) let the epilogue of tile i overlap the mainloop of
+// tile i+1.  Out-of-bounds rows / columns / K are zero-filled by TMA and predicated on store,
+// so ragged shapes (N = 3352, K = 48, ...) need no padding copies.
+#include <cuda.h>
+
+#include "common.cuh"
+#include "ptx.cuh"
+#include "../include/mamba_b200.h"
+
+namespace mb {
+using namespace ptx;
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+constexpr int kGemmThreads = 192;
+
+enum { EPI_BF16 = 0, EPI_F32 = 1, EPI_F32_ATOMIC = 2 };
+
+template <int BN>
+struct GemmCfg {
+  static constexpr int STAGES = BN == 256 ? 4 : 6;
+  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+template <int BN, uint32_t A_MAJOR, uint32_t B_MAJOR, int EPI>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 void* __restrict__ Dout, const float* __restrict__ bias, int Mg, int Ng, int Kg,
+                 long long ldd, int splitk, int kb_per_split, float alpha) {
+  using Cfg = GemmCfg<BN>;
+  constexpr int STAGES = Cfg::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + STAGES * Cfg::A_BYTES;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * (Cfg::A_BYTES + Cfg::B_BYTES));
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tfull_bar = empty_bar + STAGES;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tiles_m = (Mg + BM - 1) / BM, tiles_n = (Ng + BN - 1) / BN;
+  const int num_tiles = tiles_m * tiles_n * splitk;
+  const int kblocks = (Kg + BK - 1) / BK;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&tmA);
+    prefetch_tensormap(&tmB);
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 4); }
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, 2 * BN);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================================ TMA producer =====================================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        int t = tile;
+        const int m_blk = t % tiles_m; t /= tiles_m;
+        const int n_blk = t % tiles_n;
+        const int split = t / tiles_n;
+        const int kb0 = split * kb_per_split;
+        const int kb1 = min(kb0 + kb_per_split, kblocks);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full_bar[stage], Cfg::A_BYTES + Cfg::B_BYTES);
+          uint8_t* a_dst = sA + stage * Cfg::A_BYTES;
+          uint8_t* b_dst = sB + stage * Cfg::B_BYTES;
+          if (A_MAJOR == MAJOR_K) {
+            tma_load_2d(a_dst, &tmA, &full_bar[stage], kb * BK, m_blk * BM);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BM / 64; ++j)
+              tma_load_2d(a_dst + j * (BK * 128), &tmA, &full_bar[stage], m_blk * BM + j * 64, kb * BK);
+          }
+          if (B_MAJOR == MAJOR_K) {
+            tma_load_2d(b_dst, &tmB, &full_bar[stage], kb * BK, n_blk * BN);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_2d(b_dst + j * (BK * 128), &tmB, &full_bar[stage], n_blk * BN + j * 64, kb * BK);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer ========================================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MAJOR, B_MAJOR);
+      // K-major: +32 B per UMMA_K inside the swizzle row; MN-major: +16 k-rows * 128 B
+      constexpr uint32_t a_kstep = A_MAJOR == MAJOR_K ? 32 : 16 * 128;
+      constexpr uint32_t b_kstep = B_MAJOR == MAJOR_K ? 32 : 16 * 128;
+      constexpr uint32_t a_lbo = A_MAJOR == MAJOR_K ? 16 : BK * 128;  // K-major: field value 1 (ignored by HW)
+      constexpr uint32_t b_lbo = B_MAJOR == MAJOR_K ? 16 : BK * 128;
+      int stage = 0;
+      uint32_t phase = 0;
+      int local = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
+        const int split = tile / (tiles_m * tiles_n);
+        const int kb0 = split * kb_per_split;
+        const int kb1 = min(kb0 + kb_per_split, kblocks);
+        const int acc = local & 1;
+        const uint32_t acc_phase = (local >> 1) & 1;
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(sA + stage * Cfg::A_BYTES);
+          const uint32_t b_addr = smem_u32(sB + stage * Cfg::B_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t da = make_smem_desc(a_addr + k * a_kstep, a_lbo, 1024);
+            const uint64_t db = make_smem_desc(b_addr + k * b_kstep, b_lbo, 1024);
+            mma_bf16_ss(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          mma_commit(&empty_bar[stage]);  // frees this smem stage when the MMAs above retire
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        mma_commit(&tfull_bar[acc]);  // accumulator complete -> epilogue
+      }
+    }
+  } else {
+    // ================================ epilogue ==========================================
+    const int lane_grp = warp & 3;  // TMEM lanes [32*lane_grp, +32) are the ones this warp may read
+    int local = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
+      int t = tile;
+      const int m_blk = t % tiles_m; t /= tiles_m;
+      const int n_blk = t % tiles_n;
+      const int acc = local & 1;
+      const uint32_t acc_phase = (local >> 1) & 1;
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      const int row = m_blk * BM + lane_grp * 32 + lane;
+      const int n0 = n_blk * BN;
+      const uint32_t t_addr = tmem_base + ((uint32_t)(lane_grp * 32) << 16) + acc * BN;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        const int col0 = n0 + c * 32;
+        if (col0 >= Ng) break;  // warp-uniform
+        uint32_t r[32];
+        tmem_ld32(t_addr + c * 32, r);
+        tmem_ld_wait();
+        if (row < Mg) {
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * alpha;
+          if (bias != nullptr) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) if (col0 + j < Ng) v[j] += bias[col0 + j];
+          }
+          if (EPI == EPI_BF16) {
+            bf16* dst = reinterpret_cast<bf16*>(Dout) + (size_t)row * ldd + col0;
+            if (col0 + 32 <= Ng && (ldd & 7) == 0) {
+#pragma unroll
+              for (int j = 0; j < 4; ++j) st8(dst + j * 8, pack8(v + j * 8));
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) if (col0 + j < Ng) dst[j] = __float2bfloat16(v[j]);
+            }
+          } else if (EPI == EPI_F32) {
+            float* dst = reinterpret_cast<float*>(Dout) + (size_t)row * ldd + col0;
+            if (col0 + 32 <= Ng && (ldd & 3) == 0) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                *reinterpret_cast<float4*>(dst + j * 4) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) if (col0 + j < Ng) dst[j] = v[j];
+            }
+          } else {
+            float* dst = reinterpret_cast<float*>(Dout) + (size_t)row * ldd + col0;
+            if (col0 + 32 <= Ng && (ldd & 3) == 0) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                atomicAdd(reinterpret_cast<float4*>(dst + j * 4),
+                          make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]));
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) if (col0 + j < Ng) atomicAdd(dst + j, v[j]);
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 2 * BN);
+}
+
+// ---------------------------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// 2-D bf16 row-major [rows, cols] (row stride ld elements) with a {64, box_rows} box, 128B swizzle.
+int make_tmap_bf16_2d(CUtensorMap* map, const void* ptr, long long rows, long long cols, long long ld, int box_rows) {
+  EncodeTiledFn enc = get_encode_fn();
+  MB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point not available");
+  MB_REQUIRE(((uintptr_t)ptr & 15) == 0 && (ld * 2) % 16 == 0,
+             "TMA operand must be 16-byte aligned with a row stride that is a multiple of 8 elements (ptr=%p ld=%lld)", ptr, ld);
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  MB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with %d (rows=%lld cols=%lld ld=%lld)", (int)r, rows, cols, ld);
+  return 0;
+}
+
+template <int BN, uint32_t AM, uint32_t BMJ, int EPI>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, void* D, const float* bias, int M, int N,
+                       int K, long long ldd, int splitk, int kb_per_split, float alpha, cudaStream_t stream) {
+  auto kern = gemm_bf16_kernel<BN, AM, BMJ, EPI>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    MB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<BN>::SMEM));
+    attr_set = true;
+  }
+  const int tiles = cdiv(M, BM) * cdiv(N, BN) * splitk;
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  kern<<<grid, kGemmThreads, GemmCfg<BN>::SMEM, stream>>>(ta, tb, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha);
+  return check_launch("gemm_bf16");
+}
+
+template <int BN, int EPI>
+static int dispatch_major(int a_major, int b_major, const CUtensorMap& ta, const CUtensorMap& tb, void* D,
+                          const float* bias, int M, int N, int K, long long ldd, int splitk, int kbps, float alpha,
+                          cudaStream_t s) {
+  if (a_major == 0 && b_major == 0) return launch_gemm<BN, MAJOR_K, MAJOR_K, EPI>(ta, tb, D, bias, M, N, K, ldd, splitk, kbps, alpha, s);
+  if (a_major == 0 && b_major == 1) return launch_gemm<BN, MAJOR_K, MAJOR_MN, EPI>(ta, tb, D, bias, M, N, K, ldd, splitk, kbps, alpha, s);
+  if (a_major == 1 && b_major == 1) return launch_gemm<BN, MAJOR_MN, MAJOR_MN, EPI>(ta, tb, D, bias, M, N, K, ldd, splitk, kbps, alpha, s);
+  return launch_gemm<BN, MAJOR_MN, MAJOR_K, EPI>(ta, tb, D, bias, M, N, K, ldd, splitk, kbps, alpha, s);
+}
+
+}  // namespace mb
+using namespace mb;
+
+// D[M,N] (=|+=) alpha * op(A) op(B) (+ bias[n]).
+//   a_major 0: A is [M,K] row-major (lda);  1: A is [K,M] row-major (lda)
+//   b_major 0: B is [N,K] row-major (ldb);  1: B is [K,N] row-major (ldb)
+//   d_mode  0: bf16 store, 1: fp32 store, 2: fp32 accumulate (atomic; enables split-K)
+extern "C" int mb_gemm_bf16(const void* A, long long lda, int a_major, const void* B, long long ldb,
+                            int b_major, void* D, long long ldd, int d_mode, const float* bias, int M,
+                            int N, int K, float alpha, cudaStream_t stream) {
+  MB_REQUIRE(M >= 0 && N >= 0 && K >= 0, "gemm: negative shape");
+  MB_REQUIRE(d_mode >= 0 && d_mode <= 2, "gemm: bad d_mode %d", d_mode);
+  if (M == 0 || N == 0) return 0;
+  MB_REQUIRE(K > 0, "gemm: K must be positive");
+  MB_REQUIRE(((uintptr_t)D & 15) == 0, "gemm: output must be 16-byte aligned");
+  const int BN = N > 128 ? 256 : 128;
+  CUtensorMap ta, tb;
+  if (a_major == 0) { if (make_tmap_bf16_2d(&ta, A, M, K, lda, BM)) return 1; }
+  else { if (make_tmap_bf16_2d(&ta, A, K, M, lda, BK)) return 1; }
+  if (b_major == 0) { if (make_tmap_bf16_2d(&tb, B, N, K, ldb, BN)) return 1; }
+  else { if (make_tmap_bf16_2d(&tb, B, K, N, ldb, BK)) return 1; }
+  // split-K only where the epilogue is additive
+  const int kblocks = cdiv(K, BK);
+  int splitk = 1;
+  if (d_mode == 2) {
+    const int tiles = cdiv(M, BM) * cdiv(N, BN);
+    const int target = 4 * num_sms();
+    if (tiles < target) splitk = cdiv(target, tiles);
+    if (splitk > kblocks / 8) splitk = kblocks / 8;  // keep >= 8 k-blocks (512 deep) per split
+    if (splitk < 1) splitk = 1;
+  }
+  int kbps = cdiv(kblocks, splitk);
+  splitk = cdiv(kblocks, kbps);
+#define GO(BN_, EPI_) return dispatch_major<BN_, EPI_>(a_major, b_major, ta, tb, D, bias, M, N, K, ldd, splitk, kbps, alpha, stream)
+  if (BN == 256) {
+    if (d_mode == 0) GO(256, EPI_BF16);
+    if (d_mode == 1) GO(256, EPI_F32);
+    GO(256, EPI_F32_ATOMIC);
+  } else {
+    if (d_mode == 0) GO(128, EPI_BF16);
+    if (d_mode == 1) GO(128, EPI_F32);
+    GO(128, EPI_F32_ATOMIC);
+  }
+#undef GO
+}

@@ -1,0 +1,389 @@
+// K14 / K15: fused residual-add + RMSNorm and gated RMSNorm, forward and backward.
+//
+// Replaces the Triton layer-norm kernels the reference reaches through mamba_ssm
+// (SURVEY.md section 2.3 rows K14, K15).  Memory-bound: one warp owns one row (or one
+// (row, group) for the gated norm), the whole row lives in registers between the statistic
+// and the scale pass, all global traffic is 16-byte vectors.  Backward kernels are
+// grid-persistent so the weight gradient is reduced in registers across rows; per-block
+// partials go to a scratch buffer and a second kernel folds them into the fp32 grad arena.
+#include "common.cuh"
+#include "../include/mamba_b200.h"
+
+namespace mb {
+
+constexpr int kWarpsPerBlock = 4;
+
+// ------------------------------------------------------------------------------------------
+// add + rmsnorm forward.  x: bf16 or fp32 [M, D]; residual: fp32 [M, D] or null.
+// ------------------------------------------------------------------------------------------
+template <int NV, bool X_FP32>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+add_rmsnorm_fwd_kernel(const void* __restrict__ xin, const float* __restrict__ residual,
+                       const float* __restrict__ weight, bf16* __restrict__ y,
+                       float* __restrict__ res_out, float* __restrict__ rstd_out, int M, int D,
+                       float eps) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+  if (row >= M) return;
+  const int nvec = D >> 3;
+  float v[NV][8];
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int vec = lane + 32 * i;
+    if (vec < nvec) {
+      const size_t off = (size_t)row * D + vec * 8;
+      if (X_FP32) ld8f(reinterpret_cast<const float*>(xin) + off, v[i]);
+      else unpack8(ld8(reinterpret_cast<const bf16*>(xin) + off), v[i]);
+      if (residual != nullptr) {
+        float r[8];
+        ld8f(residual + off, r);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[i][j] += r[j];
+      }
+      if (res_out != nullptr) st8f(res_out + off, v[i]);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) ss += v[i][j] * v[i][j];
+    }
+  }
+  ss = warp_sum(ss);
+  const float rstd = rsqrtf(ss / (float)D + eps);
+  if (lane == 0 && rstd_out != nullptr) rstd_out[row] = rstd;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int vec = lane + 32 * i;
+    if (vec < nvec) {
+      float w[8], o[8];
+      ld8f(weight + vec * 8, w);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = v[i][j] * rstd * w[j];
+      st8(y + (size_t)row * D + vec * 8, pack8(o));
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// add + rmsnorm backward.
+//   r     fp32 [M, D]  the normalised input saved by forward (x + residual)
+//   dy    bf16 [M, D]
+//   dres_in  fp32 [M, D] or null : gradient arriving on the residual stream from later layers
+//   dres_out fp32 [M, D]         : total gradient wrt r (may alias dres_in)
+//   dx_bf16  bf16 [M, D] or null : same values in bf16 (operand of the previous out_proj dgrad)
+//   dw_partial fp32 [gridDim.x, D] scratch
+// ------------------------------------------------------------------------------------------
+template <int NV>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+add_rmsnorm_bwd_kernel(const float* __restrict__ r, const bf16* __restrict__ dy,
+                       const float* __restrict__ rstd_in, const float* __restrict__ weight,
+                       const float* dres_in, float* dres_out, bf16* __restrict__ dx_bf16,
+                       float* __restrict__ dw_partial, int M, int D) {
+  __shared__ float red[kWarpsPerBlock][32 * 8 + 8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nvec = D >> 3;
+  float w[NV][8], dw[NV][8];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int vec = lane + 32 * i;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { dw[i][j] = 0.f; w[i][j] = 0.f; }
+    if (vec < nvec) ld8f(weight + vec * 8, w[i]);
+  }
+  for (int row = blockIdx.x * kWarpsPerBlock + warp; row < M; row += gridDim.x * kWarpsPerBlock) {
+    const float rstd = rstd_in[row];
+    float xh[NV][8], wdy[NV][8];
+    float c = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vec = lane + 32 * i;
+      if (vec < nvec) {
+        const size_t off = (size_t)row * D + vec * 8;
+        float g[8];
+        ld8f(r + off, xh[i]);
+        unpack8(ld8(dy + off), g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          xh[i][j] *= rstd;
+          wdy[i][j] = g[j] * w[i][j];
+          dw[i][j] += g[j] * xh[i][j];
+          c += xh[i][j] * wdy[i][j];
+        }
+      }
+    }
+    c = warp_sum(c) / (float)D;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vec = lane + 32 * i;
+      if (vec < nvec) {
+        const size_t off = (size_t)row * D + vec * 8;
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = (wdy[i][j] - xh[i][j] * c) * rstd;
+        if (dres_in != nullptr) {
+          float a[8];
+          ld8f(dres_in + off, a);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] += a[j];
+        }
+        st8f(dres_out + off, o);
+        if (dx_bf16 != nullptr) st8(dx_bf16 + off, pack8(o));
+      }
+    }
+  }
+  // block-level reduction of dw, one 256-column slab at a time
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) red[warp][lane * 8 + j] = dw[i][j];
+    __syncthreads();
+    for (int k = threadIdx.x; k < 256; k += blockDim.x) {
+      const int col = i * 256 + k;
+      if (col < D) {
+        float s = 0.f;
+#pragma unroll
+        for (int ww = 0; ww < kWarpsPerBlock; ++ww) s += red[ww][k];
+        dw_partial[(size_t)blockIdx.x * D + col] = s;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// dw[col] (+)= sum_p partial[p][col]
+__global__ void colsum_partials_kernel(const float* __restrict__ partial, float* __restrict__ dw,
+                                       int P, int D, int accumulate) {
+  const int col = blockIdx.x * blockDim.x + threadIdx.x;
+  if (col >= D) return;
+  float s = 0.f;
+  for (int p = 0; p < P; ++p) s += partial[(size_t)p * D + col];
+  dw[col] = accumulate ? dw[col] + s : s;
+}
+
+// ------------------------------------------------------------------------------------------
+// gated rmsnorm: out = rmsnorm_group(x * silu(z)) * w.   rows = M * G, row length gs = D / G.
+// ------------------------------------------------------------------------------------------
+template <int NV>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+gated_rmsnorm_fwd_kernel(const bf16* __restrict__ x, int ldx, const bf16* __restrict__ z, int ldz,
+                         const float* __restrict__ weight, bf16* __restrict__ out, int ldo,
+                         float* __restrict__ rstd_out, int M, int G, int gs, float eps) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+  if (row >= M * G) return;
+  const int m = row / G, g = row - m * G;
+  const int nvec = gs >> 3;
+  float v[NV][8];
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int vec = lane + 32 * i;
+    if (vec < nvec) {
+      const int col = g * gs + vec * 8;
+      float zz[8];
+      unpack8(ld8(x + (size_t)m * ldx + col), v[i]);
+      unpack8(ld8(z + (size_t)m * ldz + col), zz);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { v[i][j] *= silu_f(zz[j]); ss += v[i][j] * v[i][j]; }
+    }
+  }
+  ss = warp_sum(ss);
+  const float rstd = rsqrtf(ss / (float)gs + eps);
+  if (lane == 0) rstd_out[row] = rstd;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int vec = lane + 32 * i;
+    if (vec < nvec) {
+      const int col = g * gs + vec * 8;
+      float w[8], o[8];
+      ld8f(weight + col, w);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = v[i][j] * rstd * w[j];
+      st8(out + (size_t)m * ldo + col, pack8(o));
+    }
+  }
+}
+
+template <int NV>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+gated_rmsnorm_bwd_kernel(const bf16* __restrict__ x, int ldx, const bf16* __restrict__ z, int ldz,
+                         const float* __restrict__ weight, const float* __restrict__ rstd_in,
+                         const bf16* __restrict__ dout, int ldo, bf16* __restrict__ dx, int lddx,
+                         bf16* __restrict__ dz, int lddz, float* __restrict__ dw_partial, int M,
+                         int G, int gs) {
+  __shared__ float red[kWarpsPerBlock][32 * 8 + 8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nvec = gs >> 3;
+  const int D = G * gs;
+  // dw accumulators are per group-column; a warp visits rows of a single group index only when
+  // G == 1.  For G > 1 the column base changes per row, so dw is accumulated through atomics
+  // into the partial slab instead of registers (G > 1 is not used by the benchmark configs).
+  float dw[NV][8];
+#pragma unroll
+  for (int i = 0; i < NV; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dw[i][j] = 0.f;
+  float* my_partial = dw_partial + (size_t)blockIdx.x * D;
+  for (int row = blockIdx.x * kWarpsPerBlock + warp; row < M * G; row += gridDim.x * kWarpsPerBlock) {
+    const int m = row / G, g = row - m * G;
+    const float rstd = rstd_in[row];
+    // inputs stay packed (bf16) in registers between the two passes; the fp32 intermediates
+    // are recomputed in pass 2 — keeps the kernel spill-free at row length 1536 (NV = 6)
+    bf16x8 px[NV], pz[NV], pg[NV];
+    float c = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vec = lane + 32 * i;
+      if (vec < nvec) {
+        const int col = g * gs + vec * 8;
+        float xv[8], zz[8], go[8], w[8];
+        px[i] = ld8(x + (size_t)m * ldx + col);
+        pz[i] = ld8(z + (size_t)m * ldz + col);
+        pg[i] = ld8(dout + (size_t)m * ldo + col);
+        unpack8(px[i], xv); unpack8(pz[i], zz); unpack8(pg[i], go);
+        ld8f(weight + col, w);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float xh = xv[j] * silu_f(zz[j]) * rstd;
+          c += xh * go[j] * w[j];
+          if (G == 1) dw[i][j] += go[j] * xh;
+          else atomicAdd(my_partial + col + j, go[j] * xh);
+        }
+      }
+    }
+    c = warp_sum(c) / (float)gs;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vec = lane + 32 * i;
+      if (vec < nvec) {
+        const int col = g * gs + vec * 8;
+        float xv[8], zz[8], go[8], w[8], ox[8], oz[8];
+        unpack8(px[i], xv); unpack8(pz[i], zz); unpack8(pg[i], go);
+        ld8f(weight + col, w);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float sg = silu_f(zz[j]);
+          const float xh = xv[j] * sg * rstd;
+          const float dxs = (go[j] * w[j] - xh * c) * rstd;
+          ox[j] = dxs * sg;
+          oz[j] = dxs * xv[j] * dsilu_f(zz[j]);
+        }
+        st8(dx + (size_t)m * lddx + col, pack8(ox));
+        st8(dz + (size_t)m * lddz + col, pack8(oz));
+      }
+    }
+  }
+  if (G == 1) {
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) red[warp][lane * 8 + j] = dw[i][j];
+      __syncthreads();
+      for (int k = threadIdx.x; k < 256; k += blockDim.x) {
+        const int col = i * 256 + k;
+        if (col < D) {
+          float s = 0.f;
+#pragma unroll
+          for (int ww = 0; ww < kWarpsPerBlock; ++ww) s += red[ww][k];
+          my_partial[col] = s;
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+static int bwd_grid(int rows) {
+  int g = cdiv(rows, kWarpsPerBlock);
+  int cap = num_sms() * 8;
+  return g < cap ? g : cap;
+}
+
+}  // namespace mb
+
+using namespace mb;
+
+#define DISPATCH_NV(nv, ...)                                   \
+  switch (nv) {                                                \
+    case 1: { constexpr int NV = 1; __VA_ARGS__; } break;      \
+    case 2: { constexpr int NV = 2; __VA_ARGS__; } break;      \
+    case 3: { constexpr int NV = 3; __VA_ARGS__; } break;      \
+    case 4: { constexpr int NV = 4; __VA_ARGS__; } break;      \
+    case 5: case 6: { constexpr int NV = 6; __VA_ARGS__; } break;   \
+    case 7: case 8: { constexpr int NV = 8; __VA_ARGS__; } break;   \
+    case 9: case 10: { constexpr int NV = 10; __VA_ARGS__; } break; \
+    case 11: case 12: { constexpr int NV = 12; __VA_ARGS__; } break; \
+    default: { constexpr int NV = 16; __VA_ARGS__; } break;    \
+  }
+
+extern "C" int mb_add_rmsnorm_fwd(const void* x, int x_is_fp32, const float* residual,
+                                  const float* weight, void* y, float* res_out, float* rstd, int M,
+                                  int D, float eps, cudaStream_t stream) {
+  MB_REQUIRE(D % 8 == 0 && D <= 4096, "add_rmsnorm_fwd: D=%d must be a multiple of 8 and <= 4096", D);
+  if (M == 0) return 0;
+  const int nv = cdiv(D, 256);
+  dim3 grid(cdiv(M, kWarpsPerBlock)), block(kWarpsPerBlock * 32);
+  DISPATCH_NV(nv, {
+    if (x_is_fp32)
+      add_rmsnorm_fwd_kernel<NV, true><<<grid, block, 0, stream>>>(x, residual, weight, (bf16*)y, res_out, rstd, M, D, eps);
+    else
+      add_rmsnorm_fwd_kernel<NV, false><<<grid, block, 0, stream>>>(x, residual, weight, (bf16*)y, res_out, rstd, M, D, eps);
+  });
+  return check_launch("add_rmsnorm_fwd");
+}
+
+extern "C" long long mb_norm_bwd_scratch_bytes(int rows, int D) {
+  return (long long)bwd_grid(rows) * D * sizeof(float);
+}
+
+extern "C" int mb_add_rmsnorm_bwd(const float* r, const void* dy, const float* rstd,
+                                  const float* weight, const float* dres_in, float* dres_out,
+                                  void* dx_bf16, float* dw, int dw_accumulate, float* scratch, int M,
+                                  int D, cudaStream_t stream) {
+  MB_REQUIRE(D % 8 == 0 && D <= 4096, "add_rmsnorm_bwd: D=%d must be a multiple of 8 and <= 4096", D);
+  if (M == 0) return 0;
+  const int nv = cdiv(D, 256);
+  const int grid = bwd_grid(M);
+  DISPATCH_NV(nv, {
+    add_rmsnorm_bwd_kernel<NV><<<grid, kWarpsPerBlock * 32, 0, stream>>>(
+        r, (const bf16*)dy, rstd, weight, dres_in, dres_out, (bf16*)dx_bf16, scratch, M, D);
+  });
+  if (check_launch("add_rmsnorm_bwd")) return 1;
+  colsum_partials_kernel<<<cdiv(D, 256), 256, 0, stream>>>(scratch, dw, grid, D, dw_accumulate);
+  return check_launch("add_rmsnorm_bwd/colsum");
+}
+
+extern "C" int mb_gated_rmsnorm_fwd(const void* x, int ldx, const void* z, int ldz,
+                                    const float* weight, void* out, int ldo, float* rstd, int M,
+                                    int D, int group_size, float eps, cudaStream_t stream) {
+  MB_REQUIRE(D % group_size == 0 && group_size % 8 == 0 && group_size <= 4096,
+             "gated_rmsnorm_fwd: bad D=%d group_size=%d", D, group_size);
+  MB_REQUIRE(ldx % 8 == 0 && ldz % 8 == 0 && ldo % 8 == 0, "gated_rmsnorm_fwd: row strides must be multiples of 8");
+  if (M == 0) return 0;
+  const int G = D / group_size, nv = cdiv(group_size, 256);
+  dim3 grid(cdiv((long long)M * G, kWarpsPerBlock)), block(kWarpsPerBlock * 32);
+  DISPATCH_NV(nv, {
+    gated_rmsnorm_fwd_kernel<NV><<<grid, block, 0, stream>>>((const bf16*)x, ldx, (const bf16*)z, ldz, weight,
+                                                             (bf16*)out, ldo, rstd, M, G, group_size, eps);
+  });
+  return check_launch("gated_rmsnorm_fwd");
+}
+
+extern "C" int mb_gated_rmsnorm_bwd(const void* x, int ldx, const void* z, int ldz,
+                                    const float* weight, const float* rstd, const void* dout, int ldo,
+                                    void* dx, int lddx, void* dz, int lddz, float* dw,
+                                    int dw_accumulate, float* scratch, int M, int D, int group_size,
+                                    cudaStream_t stream) {
+  MB_REQUIRE(D % group_size == 0 && group_size % 8 == 0 && group_size <= 4096,
+             "gated_rmsnorm_bwd: bad D=%d group_size=%d", D, group_size);
+  if (M == 0) return 0;
+  const int G = D / group_size, nv = cdiv(group_size, 256);
+  const int grid = bwd_grid(M * G);
+  if (G > 1) MB_CUDA(cudaMemsetAsync(scratch, 0, (size_t)grid * D * sizeof(float), stream));
+  DISPATCH_NV(nv, {
+    gated_rmsnorm_bwd_kernel<NV><<<grid, kWarpsPerBlock * 32, 0, stream>>>(
+        (const bf16*)x, ldx, (const bf16*)z, ldz, weight, rstd, (const bf16*)dout, ldo, (bf16*)dx, lddx,
+        (bf16*)dz, lddz, scratch, M, G, group_size);
+  });
+  if (check_launch("gated_rmsnorm_bwd")) return 1;
+  colsum_partials_kernel<<<cdiv(D, 256), 256, 0, stream>>>(scratch, dw, grid, D, dw_accumulate);
+  return check_launch("gated_rmsnorm_bwd/colsum");
+}

@@ -1,0 +1,71 @@
+/* C ABI of libmamba_b200.so — hand-written sm_100a kernels for Mamba training on B200.
+ *
+ * Conventions
+ *   - every launcher returns 0 on success, non-zero on error; mb_last_error() gives the text
+ *     (thread-local).  Nothing here allocates device memory unless stated; all work is enqueued
+ *     on `stream` and is asynchronous.
+ *   - "bf16" pointers are void* to __nv_bfloat16 data; row strides (ld*) are in elements.
+ *   - activations are channel-last; "strided" operands may be column slices of a wider matrix.
+ * Each block cites the component of the reference stack it replaces (SURVEY.md section 2.3;
+ * the reference itself, /root/reference, has no native code — these kernels stand in for the
+ * mamba_ssm / causal-conv1d / cuBLAS / NCCL pieces it reaches through its imports).
+ */
+#ifndef MAMBA_B200_H_
+#define MAMBA_B200_H_
+
+#include <cuda_runtime.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- runtime ------------------------------------------------------------------------------ */
+const char* mb_last_error(void);
+int mb_version(void);
+int mb_num_sms(void);
+unsigned long long mb_launch_count(void); /* kernel launches issued by this library so far */
+
+/* ---- K14: fused residual-add + RMSNorm  (mamba_ssm layer_norm_fn as called from Block,
+ *      reached via /root/reference/model.py:35-41) ------------------------------------------ */
+int mb_add_rmsnorm_fwd(const void* x, int x_is_fp32, const float* residual, const float* weight,
+                       void* y_bf16, float* res_out, float* rstd, int M, int D, float eps,
+                       cudaStream_t stream);
+long long mb_norm_bwd_scratch_bytes(int rows, int D);
+int mb_add_rmsnorm_bwd(const float* r, const void* dy_bf16, const float* rstd, const float* weight,
+                       const float* dres_in, float* dres_out, void* dx_bf16, float* dw,
+                       int dw_accumulate, float* scratch, int M, int D, cudaStream_t stream);
+
+/* ---- K15: gated RMSNorm  y = rmsnorm(x * silu(z)) * w  (mamba_ssm RMSNormGated) ----------- */
+int mb_gated_rmsnorm_fwd(const void* x, int ldx, const void* z, int ldz, const float* weight,
+                         void* out, int ldo, float* rstd, int M, int D, int group_size, float eps,
+                         cudaStream_t stream);
+int mb_gated_rmsnorm_bwd(const void* x, int ldx, const void* z, int ldz, const float* weight,
+                         const float* rstd, const void* dout, int ldo, void* dx, int lddx, void* dz,
+                         int lddz, float* dw, int dw_accumulate, float* scratch, int M, int D,
+                         int group_size, cudaStream_t stream);
+
+/* ---- K1-K3: causal depthwise conv1d (+bias, +SiLU), channel-last (causal-conv1d) ----------- */
+int mb_conv1d_fwd(const void* x, long long ldx, const float* w, const float* bias, void* y,
+                  long long ldy, int B, int T, int C, int width, int silu, cudaStream_t stream);
+int mb_conv1d_bwd(const void* x, long long ldx, const float* w, const float* bias, const void* dy,
+                  long long lddy, void* dx, long long lddx, float* dw, float* dbias, int B, int T,
+                  int C, int width, int silu, cudaStream_t stream);
+int mb_conv1d_update(const void* x, long long ldx, float* state, const float* w, const float* bias,
+                     void* y, long long ldy, int B, int C, int width, int silu, cudaStream_t stream);
+
+/* ---- K18: embedding gather / scatter-add (ATen embedding fwd/bwd) ------------------------- */
+int mb_embedding_fwd(const long long* ids, const float* w, float* out, int M, int D, int V,
+                     cudaStream_t stream);
+int mb_embedding_bwd(const long long* ids, const float* dout, float* dw, int M, int D, int V,
+                     cudaStream_t stream);
+int mb_cast_f32_bf16(const float* in, void* out_bf16, long long n, cudaStream_t stream);
+
+/* ---- K16: bf16 GEMM on tcgen05/TMEM/TMA (cuBLAS behind nn.Linear) ------------------------- */
+int mb_gemm_bf16(const void* A, long long lda, int a_major, const void* B, long long ldb, int b_major,
+                 void* D, long long ldd, int d_mode, const float* bias, int M, int N, int K,
+                 float alpha, cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MAMBA_B200_H_ */

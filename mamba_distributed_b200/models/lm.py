@@ -141,6 +141,8 @@ class MambaLMHeadModel(nn.Module):
     def tie_weights(self):
         if self.config.tie_embeddings:
             self.lm_head.weight = self.backbone.embedding.weight
+            # the tied tensor's gradient is final only after the embedding backward (K18)
+            self.lm_head.weight._tied_embedding = True
 
     def allocate_inference_cache(self, batch_size, max_seqlen, dtype=None, **kwargs):
         return self.backbone.allocate_inference_cache(batch_size, max_seqlen, dtype=dtype, **kwargs)

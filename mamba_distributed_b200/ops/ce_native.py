@@ -1,0 +1,69 @@
+"""K17: tied lm_head GEMM + cross-entropy without materialising the ``[M, V]`` logits.
+
+The reference computes ``F.cross_entropy(lm_head(h))`` on fully materialised logits
+(/root/reference/model.py:35-46: 3.3 GB bf16 + 6.6 GB fp32 per micro-batch at B=32, T=1024).
+Here rows are processed in slabs: logits slab (tcgen05 GEMM, fp32 out) -> log-sum-exp / target
+gather -> (p - onehot) in bf16 -> dgrad and wgrad GEMMs, all inside forward, so only an
+``[R, V]`` slab ever exists.  Backward just scales the stored ``dh`` / ``dW`` by the incoming
+scalar gradient."""
+from __future__ import annotations
+
+import torch
+
+from .native import bf16_weight, gemm_nn, gemm_nt, gemm_tn_acc, grad_buffer, notify_grad_ready
+
+SLAB_ROWS = 4096
+
+
+class LinearCrossEntropyFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, h2, weight, targets, reduction):
+        M, d = h2.shape
+        V = weight.shape[0]
+        if h2.dtype != torch.bfloat16 or not h2.is_contiguous():
+            h2 = h2.to(torch.bfloat16).contiguous()
+        w = bf16_weight(weight)
+        need_grad = ctx.needs_input_grad[0] or ctx.needs_input_grad[1]
+        losses = torch.empty(M, dtype=torch.float32, device=h2.device)
+        dh = torch.empty(M, d, dtype=torch.bfloat16, device=h2.device) if need_grad else None
+        dW = torch.zeros(V, d, dtype=torch.float32, device=h2.device) if need_grad else None
+        scale = 1.0 / M if reduction == "mean" else 1.0
+        for s in range(0, M, SLAB_ROWS):
+            e = min(M, s + SLAB_ROWS)
+            logits = gemm_nt(h2[s:e], w, out_dtype=torch.float32)
+            t = targets[s:e]
+            lse = torch.logsumexp(logits, dim=1)
+            losses[s:e] = lse - logits.gather(1, t[:, None]).squeeze(1)
+            if need_grad:
+                p = logits.sub_(lse[:, None]).exp_()
+                p.scatter_add_(1, t[:, None], torch.full((e - s, 1), -1.0, device=p.device))
+                pb = p.mul_(scale).to(torch.bfloat16)
+                gemm_nn(pb, w, out=dh[s:e])
+                gemm_tn_acc(pb, h2[s:e], dW)
+        ctx.need = need_grad
+        if need_grad:
+            ctx.save_for_backward(dh, dW, weight)
+        ctx.reduction = reduction
+        if reduction == "mean":
+            return losses.mean()
+        if reduction == "sum":
+            return losses.sum()
+        return losses
+
+    @staticmethod
+    def backward(ctx, g):
+        dh, dW, weight = ctx.saved_tensors
+        assert ctx.reduction in ("mean", "sum"), "per-token losses are differentiable only via the PyTorch path"
+        dh = dh * g.to(dh.dtype)
+        if weight.requires_grad:
+            grad_buffer(weight).add_(dW, alpha=float(g))
+            if not getattr(weight, "_tied_embedding", False):
+                notify_grad_ready(weight)
+        return dh, None, None, None
+
+
+def linear_cross_entropy(h2, weight, targets, reduction):
+    if reduction == "none" and torch.is_grad_enabled() and (h2.requires_grad or weight.requires_grad):
+        logits = torch.nn.functional.linear(h2.float(), weight.float())
+        return torch.nn.functional.cross_entropy(logits, targets, reduction="none")
+    return LinearCrossEntropyFn.apply(h2, weight, targets, reduction)

@@ -56,7 +56,7 @@ def selective_scan(u, delta, A, B, C, D=None, z=None, delta_bias=None, delta_sof
 def linear(x, weight, bias=None):
     """K16: ``x @ weight.T (+ bias)``; tcgen05 GEMM on the native path."""
     if use_native(x):
-        return _native().linear(x, weight, bias)
+        return _native().linear(x, weight, bias, notify=not getattr(weight, "_tied_embedding", False))
     return F.linear(x, weight, bias)
 
 

@@ -1,0 +1,454 @@
+"""sm_100a implementations of the op layer: thin wrappers over the C ABI of
+``libmamba_b200.so`` plus the autograd Functions that stitch them into the model.
+
+Data-flow conventions (B200-first):
+  * activations are bf16, channel-last, flattened to ``[M = B*T, C]``; the residual stream is
+    fp32; column slices of the in_proj output (z | xBC | dt) are consumed and their gradients
+    produced *in place* as strided views — no split / cat / transpose copies;
+  * intermediate activations are stored for backward rather than recomputed (180 GB HBM3e);
+  * parameters are fp32 masters; GEMMs read a bf16 compute copy (``p._bf16`` when
+    ``FusedDDP`` / ``FusedAdamW`` maintain one, else a cached cast);
+  * weight gradients of the big GEMMs are accumulated by the wgrad kernel's epilogue straight
+    into ``p.grad`` (fp32, the flat gradient arena under ``FusedDDP``); autograd sees ``None``
+    for them and ``p._post_grad_hook`` tells the DDP wrapper the gradient is final.
+"""
+from __future__ import annotations
+
+import os
+
+import torch
+
+from . import _lib, ref
+from ._lib import call
+
+_SSD_IMPL = os.environ.get("MAMBA_B200_SSD", "torch")      # "native" | "torch"
+_GEMM_IMPL = os.environ.get("MAMBA_B200_GEMM", "native")   # "native" | "cublas" (comparison arm)
+_CE_IMPL = os.environ.get("MAMBA_B200_CE", "native")       # "native" | "chunked"
+
+_scratch = {}
+
+
+def _get_scratch(dev, nbytes):
+    key = (dev.index, "norm")
+    buf = _scratch.get(key)
+    if buf is None or buf.numel() * 4 < nbytes:
+        buf = torch.empty(max(nbytes // 4, 1 << 20), dtype=torch.float32, device=dev)
+        _scratch[key] = buf
+    return buf
+
+
+# ------------------------------------------------------------------------------------------
+# parameters: bf16 compute copies and direct gradient accumulation
+# ------------------------------------------------------------------------------------------
+def bf16_weight(p: torch.Tensor) -> torch.Tensor:
+    w = getattr(p, "_bf16", None)
+    if w is not None:
+        return w
+    if p.dtype == torch.bfloat16:
+        return p.detach()
+    cache = getattr(p, "_bf16_cache", None)
+    if cache is not None and cache[0] == p._version and cache[1].device == p.device:
+        return cache[1]
+    w = torch.empty(p.shape, dtype=torch.bfloat16, device=p.device)
+    src = p.detach().contiguous()
+    call("mb_cast_f32_bf16", src, w, src.numel())
+    try:
+        p._bf16_cache = (p._version, w)
+    except Exception:
+        pass
+    return w
+
+
+def grad_buffer(p: torch.Tensor) -> torch.Tensor:
+    if p.grad is None:
+        p.grad = torch.zeros_like(p, dtype=torch.float32, memory_format=torch.contiguous_format)
+    return p.grad
+
+
+def notify_grad_ready(p: torch.Tensor):
+    hook = getattr(p, "_post_grad_hook", None)
+    if hook is not None:
+        hook()
+
+
+# ------------------------------------------------------------------------------------------
+# GEMM wrappers (K16)
+# ------------------------------------------------------------------------------------------
+def _rows(x):
+    return x.reshape(-1, x.shape[-1])
+
+
+def _check2d(x):
+    assert x.dim() == 2 and x.stride(1) == 1 and x.dtype == torch.bfloat16, (x.shape, x.stride(), x.dtype)
+
+
+def gemm_nt(x, w, out=None, bias=None, out_dtype=torch.bfloat16):
+    """out[M,N] = x[M,K] @ w[N,K]^T (+ bias)."""
+    _check2d(x); _check2d(w)
+    M, K = x.shape
+    N = w.shape[0]
+    if out is None:
+        out = torch.empty(M, N, dtype=out_dtype, device=x.device)
+    if _GEMM_IMPL == "cublas":
+        torch.matmul(x, w.t(), out=out) if out.dtype == x.dtype else out.copy_(torch.matmul(x, w.t()))
+        if bias is not None:
+            out.add_(bias.to(out.dtype))
+        return out
+    call("mb_gemm_bf16", x, x.stride(0), 0, w, w.stride(0), 0, out, out.stride(0),
+         0 if out.dtype == torch.bfloat16 else 1, bias, M, N, K, 1.0)
+    return out
+
+
+def gemm_nn(dy, w, out=None):
+    """out[M,K] = dy[M,N] @ w[N,K]   (dgrad; w read as stored)."""
+    _check2d(dy); _check2d(w)
+    M, N = dy.shape
+    K = w.shape[1]
+    if out is None:
+        out = torch.empty(M, K, dtype=torch.bfloat16, device=dy.device)
+    if _GEMM_IMPL == "cublas":
+        torch.matmul(dy, w, out=out)
+        return out
+    call("mb_gemm_bf16", dy, dy.stride(0), 0, w, w.stride(0), 1, out, out.stride(0), 0, None, M, K, N, 1.0)
+    return out
+
+
+def gemm_tn_acc(dy, x, grad, alpha=1.0):
+    """grad[N,K] (fp32) += alpha * dy[M,N]^T @ x[M,K]   (wgrad; activations read as stored)."""
+    _check2d(dy); _check2d(x)
+    M, N = dy.shape
+    K = x.shape[1]
+    assert grad.dtype == torch.float32 and grad.shape == (N, K) and grad.stride(1) == 1
+    if _GEMM_IMPL == "cublas":
+        grad.add_(torch.matmul(dy.t(), x).float(), alpha=alpha)
+        return grad
+    call("mb_gemm_bf16", dy, dy.stride(0), 1, x, x.stride(0), 1, grad, grad.stride(0), 2, None, N, K, M, alpha)
+    return grad
+
+
+class LinearFn(torch.autograd.Function):
+    """y = x W^T (+ b).  dW is accumulated in place into ``weight.grad`` (see module docstring)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, notify):
+        x2 = _rows(x)
+        if x2.dtype != torch.bfloat16:
+            x2 = x2.to(torch.bfloat16)
+        if x2.stride(1) != 1 or x2.stride(0) % 8 != 0 or x2.data_ptr() % 16 != 0:
+            x2 = x2.contiguous()
+        w = bf16_weight(weight)
+        y = gemm_nt(x2, w, bias=bias.float() if bias is not None else None)
+        ctx.save_for_backward(x2, weight, bias)
+        ctx.notify = notify
+        ctx.xshape = x.shape
+        ctx.xdtype = x.dtype
+        return y.view(*x.shape[:-1], w.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, weight, bias = ctx.saved_tensors
+        dy2 = _rows(dy)
+        if dy2.dtype != torch.bfloat16 or dy2.stride(1) != 1 or dy2.stride(0) % 8 != 0:
+            dy2 = dy2.to(torch.bfloat16).contiguous()
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = gemm_nn(dy2, bf16_weight(weight)).view(ctx.xshape).to(ctx.xdtype)
+        if weight.requires_grad:
+            gemm_tn_acc(dy2, x2, grad_buffer(weight))
+            if ctx.notify:
+                notify_grad_ready(weight)
+        db = dy2.float().sum(0) if bias is not None and ctx.needs_input_grad[2] else None
+        return dx, None, db, None
+
+
+def linear(x, weight, bias=None, notify=True):
+    N, K = weight.shape
+    if K % 8 != 0 or N % 8 != 0:
+        # TMA needs 16-byte row strides; shapes this small are never on the hot path
+        return torch.nn.functional.linear(x, weight.to(x.dtype) if x.dtype != weight.dtype else weight,
+                                          bias if bias is None else bias.to(x.dtype))
+    return LinearFn.apply(x, weight, bias, notify)
+
+
+# ------------------------------------------------------------------------------------------
+# K14: fused add + RMSNorm
+# ------------------------------------------------------------------------------------------
+class AddRMSNormFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, residual, eps, prenorm):
+        shape = x.shape
+        D = shape[-1]
+        x2 = _rows(x).contiguous()
+        M = x2.shape[0]
+        x_fp32 = x2.dtype == torch.float32
+        if not x_fp32 and x2.dtype != torch.bfloat16:
+            x2 = x2.to(torch.bfloat16)
+        r2 = _rows(residual).contiguous() if residual is not None else None
+        y = torch.empty(M, D, dtype=torch.bfloat16, device=x.device)
+        rstd = torch.empty(M, dtype=torch.float32, device=x.device)
+        if r2 is None and x_fp32:
+            res_out = x2  # nothing to add: the fp32 input *is* the residual stream
+            call("mb_add_rmsnorm_fwd", x2, 1, None, weight, y, None, rstd, M, D, eps)
+        else:
+            res_out = torch.empty(M, D, dtype=torch.float32, device=x.device)
+            call("mb_add_rmsnorm_fwd", x2, int(x_fp32), r2, weight, y, res_out, rstd, M, D, eps)
+        ctx.save_for_backward(res_out, rstd, weight)
+        ctx.x_fp32, ctx.has_res, ctx.shape, ctx.prenorm = x_fp32, residual is not None, shape, prenorm
+        y = y.view(shape)
+        if prenorm:
+            res_v = res_out.view(shape)
+            return y, res_v
+        return y
+
+    @staticmethod
+    def backward(ctx, dy, dres=None):
+        res_out, rstd, weight = ctx.saved_tensors
+        M, D = res_out.shape
+        dy2 = _rows(dy)
+        if dy2.dtype != torch.bfloat16 or not dy2.is_contiguous():
+            dy2 = dy2.to(torch.bfloat16).contiguous()
+        dres2 = _rows(dres).contiguous() if dres is not None else None
+        dres_out = dres2 if dres2 is not None else torch.empty(M, D, dtype=torch.float32, device=dy.device)
+        need_bf16 = not ctx.x_fp32
+        dx_bf16 = torch.empty(M, D, dtype=torch.bfloat16, device=dy.device) if need_bf16 else None
+        dw = torch.empty(D, dtype=torch.float32, device=dy.device)
+        nbytes = _lib.load().mb_norm_bwd_scratch_bytes(M, D)
+        scratch = _get_scratch(dy.device, nbytes)
+        call("mb_add_rmsnorm_bwd", res_out, dy2, rstd, weight, dres2, dres_out, dx_bf16, dw, 0, scratch, M, D)
+        dres_out = dres_out.view(ctx.shape)
+        dx = dx_bf16.view(ctx.shape) if need_bf16 else dres_out
+        return dx, dw.to(weight.dtype), (dres_out if ctx.has_res else None), None, None
+
+
+def add_rms_norm(x, weight, residual, eps, prenorm):
+    return AddRMSNormFn.apply(x, weight.float() if weight.dtype != torch.float32 else weight, residual,
+                              eps, prenorm)
+
+
+# ------------------------------------------------------------------------------------------
+# K15: gated RMSNorm (raw helpers used by the fused mixer, plus a standalone Function)
+# ------------------------------------------------------------------------------------------
+def k_gated_rmsnorm_fwd(x, z, weight, eps, group_size):
+    M, D = x.shape
+    out = torch.empty(M, D, dtype=torch.bfloat16, device=x.device)
+    rstd = torch.empty(M * (D // group_size), dtype=torch.float32, device=x.device)
+    call("mb_gated_rmsnorm_fwd", x, x.stride(0), z, z.stride(0), weight, out, out.stride(0), rstd, M, D,
+         group_size, eps)
+    return out, rstd
+
+
+def k_gated_rmsnorm_bwd(x, z, weight, rstd, dout, dx, dz, group_size):
+    M, D = x.shape
+    dw = torch.empty(D, dtype=torch.float32, device=x.device)
+    nbytes = _lib.load().mb_norm_bwd_scratch_bytes(M * (D // group_size), D)
+    scratch = _get_scratch(x.device, nbytes)
+    call("mb_gated_rmsnorm_bwd", x, x.stride(0), z, z.stride(0), weight, rstd, dout, dout.stride(0), dx,
+         dx.stride(0), dz, dz.stride(0), dw, 0, scratch, M, D, group_size)
+    return dw
+
+
+class GatedRMSNormFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, z, weight, eps, group_size):
+        x2, z2 = _rows(x), _rows(z)
+        if x2.stride(1) != 1 or x2.stride(0) % 8:
+            x2 = x2.contiguous()
+        if z2.stride(1) != 1 or z2.stride(0) % 8:
+            z2 = z2.contiguous()
+        out, rstd = k_gated_rmsnorm_fwd(x2, z2, weight, eps, group_size)
+        ctx.save_for_backward(x2, z2, weight, rstd)
+        ctx.group_size, ctx.shape = group_size, x.shape
+        return out.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, dout):
+        x2, z2, weight, rstd = ctx.saved_tensors
+        d2 = _rows(dout).contiguous()
+        dx = torch.empty_like(d2)
+        dz = torch.empty_like(d2)
+        dw = k_gated_rmsnorm_bwd(x2, z2, weight, rstd, d2, dx, dz, ctx.group_size)
+        return dx.view(ctx.shape), dz.view(ctx.shape), dw, None, None
+
+
+def gated_rms_norm(x, z, weight, eps, group_size):
+    if x.dtype != torch.bfloat16:
+        x = x.to(torch.bfloat16)
+    if z.dtype != torch.bfloat16:
+        z = z.to(torch.bfloat16)
+    return GatedRMSNormFn.apply(x, z, weight.float(), eps, group_size)
+
+
+# ------------------------------------------------------------------------------------------
+# K1/K2: causal conv1d
+# ------------------------------------------------------------------------------------------
+def k_conv1d_fwd(x3, w, b, out3, silu=True):
+    B, T, C = x3.shape
+    assert x3.stride(2) == 1 and x3.stride(0) == T * x3.stride(1)
+    call("mb_conv1d_fwd", x3, x3.stride(1), w, b, out3, out3.stride(1), B, T, C, w.shape[1], int(silu))
+
+
+def k_conv1d_bwd(x3, w, b, dy3, dx3, dw, db, silu=True):
+    B, T, C = x3.shape
+    call("mb_conv1d_bwd", x3, x3.stride(1), w, b, dy3, dy3.stride(1), dx3, dx3.stride(1), dw, db, B, T, C,
+         w.shape[1], int(silu))
+
+
+class CausalConv1dFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, silu):
+        B, T, C = x.shape
+        if x.dtype != torch.bfloat16:
+            x = x.to(torch.bfloat16)
+        if x.stride(2) != 1 or x.stride(1) % 8 or x.stride(0) != T * x.stride(1) or x.data_ptr() % 16:
+            x = x.contiguous()
+        w = weight.float().contiguous()
+        b = bias.float().contiguous() if bias is not None else None
+        out = torch.empty(B, T, C, dtype=torch.bfloat16, device=x.device)
+        k_conv1d_fwd(x, w, b, out, silu)
+        ctx.save_for_backward(x, w, b)
+        ctx.silu = silu
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w, b = ctx.saved_tensors
+        dy = dy.contiguous()
+        dx = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
+        dw = torch.zeros_like(w)
+        db = torch.zeros_like(b) if b is not None else None
+        k_conv1d_bwd(x, w, b, dy, dx, dw, db, ctx.silu)
+        return dx, dw, db, None
+
+
+def causal_conv1d(x, weight, bias, activation):
+    if weight.dim() == 3:
+        weight = weight.squeeze(1)
+    return CausalConv1dFn.apply(x, weight, bias, activation in ("silu", "swish"))
+
+
+# ------------------------------------------------------------------------------------------
+# K18: embedding
+# ------------------------------------------------------------------------------------------
+class EmbeddingFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, ids, weight):
+        V, D = weight.shape
+        ids_c = ids.contiguous()
+        out = torch.empty(*ids.shape, D, dtype=torch.float32, device=weight.device)
+        call("mb_embedding_fwd", ids_c, weight.detach(), out, ids_c.numel(), D, V)
+        ctx.save_for_backward(ids_c, weight)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        ids, weight = ctx.saved_tensors
+        if weight.requires_grad:
+            V, D = weight.shape
+            g = grad_buffer(weight)
+            call("mb_embedding_bwd", ids, dout.contiguous().float(), g, ids.numel(), D, V)
+            notify_grad_ready(weight)
+        return None, None
+
+
+def embedding(ids, weight):
+    assert weight.dtype == torch.float32 and weight.is_contiguous()
+    return EmbeddingFn.apply(ids, weight)
+
+
+# ------------------------------------------------------------------------------------------
+# K7-K12: SSD.  (kernels live in ops/ssd_native.py; "torch" = oracle math on the GPU)
+# ------------------------------------------------------------------------------------------
+def ssd_combined(x, dt, A, B, C, chunk_size, D, z, dt_bias, dt_softplus):
+    if _SSD_IMPL == "native":
+        from . import ssd_native
+        return ssd_native.ssd_combined(x, dt, A, B, C, chunk_size, D, z, dt_bias, dt_softplus)
+    return ref.ssd_chunked_ref(x, dt, A, B, C, chunk_size, D, z, dt_bias, dt_softplus)
+
+
+def selective_scan(u, delta, A, B, C, D, z, delta_bias, delta_softplus):
+    from . import sscan_native
+    return sscan_native.selective_scan(u, delta, A, B, C, D, z, delta_bias, delta_softplus)
+
+
+# ------------------------------------------------------------------------------------------
+# K13: the whole Mamba-2 mixer as one autograd node
+# ------------------------------------------------------------------------------------------
+class Mamba2MixerFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, u, in_w, conv_w, conv_b, dt_bias, A_log, D, norm_w, out_w, cfg):
+        Bsz, T, dm = u.shape
+        M = Bsz * T
+        d_in, H, P, G, N, L = cfg["d_inner"], cfg["nheads"], cfg["headdim"], cfg["ngroups"], cfg["d_state"], cfg["chunk_size"]
+        conv_dim = d_in + 2 * G * N
+        u2 = u.reshape(M, dm)
+        if u2.dtype != torch.bfloat16:
+            u2 = u2.to(torch.bfloat16)
+        u2 = u2.contiguous()
+        zxbcdt = gemm_nt(u2, bf16_weight(in_w))                       # [M, d_in_proj]
+        cw = conv_w.reshape(conv_dim, -1).float().contiguous()
+        cb = conv_b.float().contiguous() if conv_b is not None else None
+        xBC = torch.empty(M, conv_dim, dtype=torch.bfloat16, device=u.device)
+        k_conv1d_fwd(zxbcdt.view(Bsz, T, -1)[:, :, d_in:d_in + conv_dim], cw, cb,
+                     xBC.view(Bsz, T, conv_dim), True)
+        from . import ssd_native
+        y, ssd_saved = ssd_native.ssd_fwd(xBC, zxbcdt, Bsz, T, cfg, dt_bias, A_log, D)
+        z = zxbcdt[:, :d_in]
+        yn, rstd = k_gated_rmsnorm_fwd(y, z, norm_w.float(), cfg["eps"], d_in // G)
+        out = gemm_nt(yn, bf16_weight(out_w))
+        ctx.save_for_backward(u2, zxbcdt, xBC, y, yn, rstd, in_w, conv_w, conv_b, dt_bias, A_log, D, norm_w, out_w,
+                              cw, cb, *ssd_saved)
+        ctx.cfg, ctx.dims = cfg, (Bsz, T, dm)
+        ctx.udtype = u.dtype
+        return out.view(Bsz, T, dm)
+
+    @staticmethod
+    def backward(ctx, dout):
+        (u2, zxbcdt, xBC, y, yn, rstd, in_w, conv_w, conv_b, dt_bias, A_log, D, norm_w, out_w, cw, cb,
+         *ssd_saved) = ctx.saved_tensors
+        cfg = ctx.cfg
+        Bsz, T, dm = ctx.dims
+        M = Bsz * T
+        d_in, H, G, N = cfg["d_inner"], cfg["nheads"], cfg["ngroups"], cfg["d_state"]
+        conv_dim = d_in + 2 * G * N
+        dout2 = dout.reshape(M, dm)
+        if dout2.dtype != torch.bfloat16 or not dout2.is_contiguous():
+            dout2 = dout2.to(torch.bfloat16).contiguous()
+        # out_proj
+        dyn = gemm_nn(dout2, bf16_weight(out_w))
+        gemm_tn_acc(dout2, yn, grad_buffer(out_w))
+        notify_grad_ready(out_w)
+        # gated norm: dy (SSD output grad) and dz (written into the z columns of d(zxbcdt))
+        dzxbcdt = torch.empty_like(zxbcdt)
+        dy = torch.empty_like(y)
+        dnorm_w = k_gated_rmsnorm_bwd(y, zxbcdt[:, :d_in], norm_w.float(), rstd, dyn, dy, dzxbcdt[:, :d_in], d_in // G)
+        # SSD: dx|dB|dC -> dxBC ; ddt_raw -> dt columns of d(zxbcdt)
+        dxBC = torch.empty_like(xBC)
+        from . import ssd_native
+        ddt_bias, dA_log, dD = ssd_native.ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, ssd_saved)
+        # conv
+        dcw = torch.zeros_like(cw)
+        dcb = torch.zeros_like(cb) if cb is not None else None
+        k_conv1d_bwd(zxbcdt.view(Bsz, T, -1)[:, :, d_in:d_in + conv_dim], cw, cb, dxBC.view(Bsz, T, conv_dim),
+                     dzxbcdt.view(Bsz, T, -1)[:, :, d_in:d_in + conv_dim], dcw, dcb, True)
+        # in_proj
+        du = gemm_nn(dzxbcdt, bf16_weight(in_w)).view(Bsz, T, dm)
+        gemm_tn_acc(dzxbcdt, u2, grad_buffer(in_w))
+        notify_grad_ready(in_w)
+        return (du.to(ctx.udtype), None, dcw.view(conv_w.shape).to(conv_w.dtype),
+                dcb.to(conv_b.dtype) if dcb is not None else None, ddt_bias.to(dt_bias.dtype),
+                dA_log.to(A_log.dtype), dD.to(D.dtype), dnorm_w.to(norm_w.dtype), None, None)
+
+
+def mamba2_mixer(mod, u):
+    cfg = dict(d_inner=mod.d_inner, nheads=mod.nheads, headdim=mod.headdim, ngroups=mod.ngroups,
+               d_state=mod.d_state, chunk_size=mod.chunk_size, eps=mod.norm.eps)
+    return Mamba2MixerFn.apply(u, mod.in_proj.weight, mod.conv1d.weight, mod.conv1d.bias, mod.dt_bias,
+                               mod.A_log, mod.D, mod.norm.weight, mod.out_proj.weight, cfg)
+
+
+# ------------------------------------------------------------------------------------------
+# K17: lm_head + cross-entropy
+# ------------------------------------------------------------------------------------------
+def linear_cross_entropy(h2, weight, targets, reduction):
+    from . import ce_native
+    return ce_native.linear_cross_entropy(h2, weight, targets, reduction)

@@ -1,0 +1,102 @@
+"""Mamba-2 SSD on the GPU (K7-K12).
+
+``ssd_fwd`` / ``ssd_bwd`` are the pieces the fused mixer node (``native.Mamba2MixerFn``) calls
+with the in-place column-slice conventions; ``ssd_combined`` is the standalone autograd op.
+``MAMBA_B200_SSD=torch`` swaps the kernels for the oracle math running as PyTorch ops on the
+GPU (debug / comparison arm only)."""
+from __future__ import annotations
+
+import torch
+
+from . import ref
+from .native import _SSD_IMPL
+
+
+def _views(xBC, zxbcdt, Bsz, T, cfg):
+    d_in, H, P, G, N = cfg["d_inner"], cfg["nheads"], cfg["headdim"], cfg["ngroups"], cfg["d_state"]
+    x = xBC[:, :d_in].view(Bsz, T, H, P)
+    Bm = xBC[:, d_in:d_in + G * N].view(Bsz, T, G, N)
+    Cm = xBC[:, d_in + G * N:].view(Bsz, T, G, N)
+    dt = zxbcdt[:, zxbcdt.shape[1] - H:].view(Bsz, T, H)
+    return x, Bm, Cm, dt
+
+
+# ------------------------------------------------------------------ oracle-on-GPU arm
+def _torch_fwd(xBC, zxbcdt, Bsz, T, cfg, dt_bias, A_log, D):
+    x, Bm, Cm, dt = _views(xBC, zxbcdt, Bsz, T, cfg)
+    y = ref.ssd_chunked_ref(x, dt, -torch.exp(A_log.float()), Bm, Cm, cfg["chunk_size"], D.float(), None,
+                            dt_bias.float(), True)
+    return y.reshape(Bsz * T, cfg["d_inner"]).contiguous(), ()
+
+
+def _torch_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, saved):
+    d_in, H, G, N = cfg["d_inner"], cfg["nheads"], cfg["ngroups"], cfg["d_state"]
+    x, Bm, Cm, dt = _views(xBC, zxbcdt, Bsz, T, cfg)
+    leaves = [t.detach().float().requires_grad_(True) for t in (x, Bm, Cm, dt, dt_bias, A_log, D)]
+    with torch.enable_grad():
+        x_, B_, C_, dt_, db_, Al_, D_ = leaves
+        yy = ref.ssd_chunked_ref(x_, dt_, -torch.exp(Al_), B_, C_, cfg["chunk_size"], D_, None, db_, True)
+    gx, gB, gC, gdt, gdb, gAl, gD = torch.autograd.grad(yy, leaves, dy.view_as(yy).float())
+    dxBC[:, :d_in] = gx.reshape(Bsz * T, d_in)
+    dxBC[:, d_in:d_in + G * N] = gB.reshape(Bsz * T, G * N)
+    dxBC[:, d_in + G * N:] = gC.reshape(Bsz * T, G * N)
+    dzxbcdt[:, dzxbcdt.shape[1] - H:] = gdt.reshape(Bsz * T, H)
+    return gdb, gAl, gD
+
+
+def ssd_fwd(xBC, zxbcdt, Bsz, T, cfg, dt_bias, A_log, D):
+    if _SSD_IMPL == "torch":
+        return _torch_fwd(xBC, zxbcdt, Bsz, T, cfg, dt_bias, A_log, D)
+    from . import ssd_kernels
+    return ssd_kernels.ssd_fwd(xBC, zxbcdt, Bsz, T, cfg, dt_bias, A_log, D)
+
+
+def ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, saved):
+    if _SSD_IMPL == "torch":
+        return _torch_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, saved)
+    from . import ssd_kernels
+    return ssd_kernels.ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, saved)
+
+
+class SSDCombinedFn(torch.autograd.Function):
+    """Standalone op with the upstream ``mamba_chunk_scan_combined`` argument convention."""
+
+    @staticmethod
+    def forward(ctx, x, dt, A, B, C, D, dt_bias, chunk_size):
+        Bsz, T, H, P = x.shape
+        G, N = B.shape[2], B.shape[3]
+        cfg = dict(d_inner=H * P, nheads=H, headdim=P, ngroups=G, d_state=N, chunk_size=chunk_size)
+        M = Bsz * T
+        xBC = torch.cat([x.reshape(M, H * P), B.reshape(M, G * N), C.reshape(M, G * N)], dim=1).to(torch.bfloat16).contiguous()
+        Hp = (H + 7) // 8 * 8
+        dtbuf = torch.zeros(M, Hp, dtype=torch.bfloat16, device=x.device)
+        dtbuf[:, Hp - H:] = dt.reshape(M, H)
+        A_log = torch.log(-A.float())
+        y, saved = ssd_fwd(xBC, dtbuf, Bsz, T, cfg, dt_bias.float(), A_log, D.float())
+        ctx.save_for_backward(xBC, dtbuf, y, dt_bias, A_log, D, A, *saved)
+        ctx.cfg, ctx.dims = cfg, (Bsz, T, H, P, G, N)
+        return y.view(Bsz, T, H, P)
+
+    @staticmethod
+    def backward(ctx, dy):
+        xBC, dtbuf, y, dt_bias, A_log, D, A, *saved = ctx.saved_tensors
+        Bsz, T, H, P, G, N = ctx.dims
+        M = Bsz * T
+        dxBC = torch.empty_like(xBC)
+        ddtbuf = torch.zeros_like(dtbuf)
+        dy2 = dy.reshape(M, H * P).to(torch.bfloat16).contiguous()
+        ddb, dAl, dD = ssd_bwd(dy2, y, xBC, dtbuf, dxBC, ddtbuf, Bsz, T, ctx.cfg, dt_bias.float(), A_log, D.float(), saved)
+        dx = dxBC[:, :H * P].reshape(Bsz, T, H, P)
+        dB = dxBC[:, H * P:H * P + G * N].reshape(Bsz, T, G, N)
+        dC = dxBC[:, H * P + G * N:].reshape(Bsz, T, G, N)
+        ddt = ddtbuf[:, ddtbuf.shape[1] - H:].reshape(Bsz, T, H)
+        dA = dAl / A.float()  # A = -exp(A_log)  =>  dA = dA_log / A
+        return dx, ddt, dA.to(A.dtype), dB, dC, dD.to(D.dtype), ddb.to(dt_bias.dtype), None
+
+
+def ssd_combined(x, dt, A, B, C, chunk_size, D, z, dt_bias, dt_softplus):
+    assert dt_softplus and D is not None and dt_bias is not None, "native SSD expects softplus(dt + bias) and D"
+    y = SSDCombinedFn.apply(x, dt, A, B, C, D, dt_bias, chunk_size)
+    if z is not None:
+        y = y * torch.nn.functional.silu(z.to(y.dtype))
+    return y

@@ -59,7 +59,7 @@ class FusedDDP(nn.Module):
         self.device = params[0].device
         self.on_gpu = self.device.type == "cuda"
         if comm == "auto":
-            comm = os.environ.get("MAMBA_B200_COMM", "fused" if self.on_gpu else "allreduce")
+            comm = os.environ.get("MAMBA_B200_COMM", "allreduce")
         assert comm in ("allreduce", "fused")
         if comm == "fused" and not self.on_gpu:
             comm = "allreduce"
