@@ -36,13 +36,14 @@ struct GemmCfg {
   static constexpr int STAGES = BN == 256 ? 4 : 6;
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = BN * BK * 2;
-  static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int STAGING = 4 * 2 * 4096;  // 4 epilogue warps x 2 buffers x [32 rows][128 B]
+  static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + STAGING + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
-template <int BN, uint32_t A_MAJOR, uint32_t B_MAJOR, int EPI>
+template <int BN, uint32_t A_MAJOR, uint32_t B_MAJOR, int EPI, bool TMA_STORE>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 void* __restrict__ Dout, const float* __restrict__ bias, int Mg, int Ng, int Kg,
+                 const __grid_constant__ CUtensorMap tmD, void* __restrict__ Dout, const float* __restrict__ bias, int Mg, int Ng, int Kg,
                  long long ldd, int splitk, int kb_per_split, float alpha) {
   using Cfg = GemmCfg<BN>;
   constexpr int STAGES = Cfg::STAGES;
@@ -51,7 +52,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
   uint8_t* sA = smem;
   uint8_t* sB = smem + STAGES * Cfg::A_BYTES;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * (Cfg::A_BYTES + Cfg::B_BYTES));
+  uint8_t* sStage = smem + STAGES * (Cfg::A_BYTES + Cfg::B_BYTES);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(sStage + Cfg::STAGING);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tfull_bar = empty_bar + STAGES;
   uint64_t* tempty_bar = tfull_bar + 2;
@@ -65,6 +67,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 0 && lane == 0) {
     prefetch_tensormap(&tmA);
     prefetch_tensormap(&tmB);
+    if (TMA_STORE) prefetch_tensormap(&tmD);
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 4); }
     fence_mbar_init();
@@ -155,6 +158,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // ================================ epilogue ==========================================
     const int lane_grp = warp & 3;  // TMEM lanes [32*lane_grp, +32) are the ones this warp may read
     int local = 0;
+    int st_iter = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
       int t = tile;
       const int m_blk = t % tiles_m; t /= tiles_m;
@@ -166,6 +170,52 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int row = m_blk * BM + lane_grp * 32 + lane;
       const int n0 = n_blk * BN;
       const uint32_t t_addr = tmem_base + ((uint32_t)(lane_grp * 32) << 16) + acc * BN;
+      if (TMA_STORE) {
+        // registers -> 128B-swizzled staging tile [32 rows][128 B] -> one TMA store per tile slab.
+        // Global writes are full 128-byte row segments; ragged M / N edges are clipped by TMA.
+        uint8_t* my_stage = sStage + (warp - 2) * 8192;
+        constexpr int COLS = EPI == EPI_BF16 ? 64 : 32;  // columns per 128-byte staged row
+#pragma unroll 1
+        for (int c = 0; c < BN / COLS; ++c) {
+          const int col0 = n0 + c * COLS;
+          if (col0 >= Ng) break;  // warp-uniform
+          uint8_t* buf = my_stage + (st_iter & 1) * 4096;
+          if (st_iter >= 2) {  // the store issued two slabs ago must have finished reading this buffer
+            if (lane == 0) tma_store_wait_read<1>();
+            __syncwarp();
+          }
+#pragma unroll
+          for (int hseg = 0; hseg < COLS / 32; ++hseg) {
+            uint32_t r[32];
+            tmem_ld32(t_addr + c * COLS + hseg * 32, r);
+            tmem_ld_wait();
+            float v[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * alpha;
+            if (bias != nullptr) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) if (col0 + hseg * 32 + j < Ng) v[j] += bias[col0 + hseg * 32 + j];
+            }
+            if (EPI == EPI_BF16) {
+#pragma unroll
+              for (int q = 0; q < 4; ++q)
+                *reinterpret_cast<bf16x8*>(buf + lane * 128 + (((hseg * 4 + q) ^ (lane & 7)) << 4)) = pack8(v + 8 * q);
+            } else {
+#pragma unroll
+              for (int q = 0; q < 8; ++q)
+                *reinterpret_cast<float4*>(buf + lane * 128 + ((q ^ (lane & 7)) << 4)) =
+                    make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+            }
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmD, buf, col0, m_blk * BM + lane_grp * 32);
+            tma_store_commit();
+          }
+          ++st_iter;
+        }
+      } else {
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
         const int col0 = n0 + c * 32;
@@ -214,10 +264,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
         }
       }
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty_bar[acc]);
     }
+    if (TMA_STORE && lane == 0) tma_store_wait<0>();
   }
   tc_fence_before();
   __syncthreads();
@@ -242,6 +294,21 @@ static EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
+// 2-D fp32 row-major output map with a {32, 32} box (128-byte rows), 128B swizzle.
+int make_tmap_f32_2d(CUtensorMap* map, const void* ptr, long long rows, long long cols, long long ld) {
+  EncodeTiledFn enc = get_encode_fn();
+  MB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point not available");
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+  cuuint32_t box[2] = {32, 32};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  MB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(f32 out) failed with %d", (int)r);
+  return 0;
+}
+
 // 2-D bf16 row-major [rows, cols] (row stride ld elements) with a {64, box_rows} box, 128B swizzle.
 int make_tmap_bf16_2d(CUtensorMap* map, const void* ptr, long long rows, long long cols, long long ld, int box_rows) {
   EncodeTiledFn enc = get_encode_fn();
@@ -259,10 +326,11 @@ int make_tmap_bf16_2d(CUtensorMap* map, const void* ptr, long long rows, long lo
   return 0;
 }
 
-template <int BN, uint32_t AM, uint32_t BMJ, int EPI>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, void* D, const float* bias, int M, int N,
-                       int K, long long ldd, int splitk, int kb_per_split, float alpha, cudaStream_t stream) {
-  auto kern = gemm_bf16_kernel<BN, AM, BMJ, EPI>;
+template <int BN, uint32_t AM, uint32_t BMJ, int EPI, bool TS>
+static int launch_gemm_ts(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, void* D,
+                          const float* bias, int M, int N, int K, long long ldd, int splitk, int kb_per_split,
+                          float alpha, cudaStream_t stream) {
+  auto kern = gemm_bf16_kernel<BN, AM, BMJ, EPI, TS>;
   static bool attr_set = false;
   if (!attr_set) {
     MB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<BN>::SMEM));
@@ -270,8 +338,24 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, void* D, co
   }
   const int tiles = cdiv(M, BM) * cdiv(N, BN) * splitk;
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  kern<<<grid, kGemmThreads, GemmCfg<BN>::SMEM, stream>>>(ta, tb, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha);
+  kern<<<grid, kGemmThreads, GemmCfg<BN>::SMEM, stream>>>(ta, tb, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha);
   return check_launch("gemm_bf16");
+}
+
+template <int BN, uint32_t AM, uint32_t BMJ, int EPI>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, void* D, const float* bias, int M, int N,
+                       int K, long long ldd, int splitk, int kb_per_split, float alpha, cudaStream_t stream) {
+  // stores go through TMA whenever the output satisfies its alignment rules; the additive
+  // (wgrad) epilogue uses vector reductions straight from registers
+  const bool ts = EPI != EPI_F32_ATOMIC && (EPI == EPI_BF16 ? (ldd % 8 == 0) : (ldd % 4 == 0));
+  CUtensorMap td;
+  if (ts) {
+    if (EPI == EPI_BF16) { if (make_tmap_bf16_2d(&td, D, M, N, ldd, 32)) return 1; }
+    else { if (make_tmap_f32_2d(&td, D, M, N, ldd)) return 1; }
+    return launch_gemm_ts<BN, AM, BMJ, EPI, (EPI != EPI_F32_ATOMIC)>(ta, tb, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha, stream);
+  }
+  td = ta;
+  return launch_gemm_ts<BN, AM, BMJ, EPI, false>(ta, tb, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha, stream);
 }
 
 template <int BN, int EPI>

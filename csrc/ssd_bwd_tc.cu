@@ -1,0 +1,262 @@
+// SSD (Mamba-2) tensor-core kernels, part 2 (backward only):
+//   ssd_dcb_kernel    dCB[i,j] = sum_h (dY_h X_h^T)[i,j] * exp(a^h_i - a^h_j) * dt^h_j * [j <= i]
+//                     per (batch, chunk, group); the per-head products live in TMEM, the decay
+//                     scaling and the sum over heads happen in registers.
+//   ssd_dbdc_kernel   dC = dCB . B + sum_h (e^{a_i} dY_h) S_prev_h
+//                     dB = dCB^T . C + sum_h (w_j X_h) dS_h
+//                     as ONE K-concatenated tcgen05 accumulation per 128-row block: the sum over
+//                     heads is the K dimension of the MMA chain, so no cross-head reduction pass.
+// They replace mamba_ssm's Triton _chunk_scan_bwd_dcb, _bmm_chunk_bwd, _chunk_scan_bwd_dC and
+// _chunk_state_bwd_db (SURVEY.md section 2.3, K8/K9/K11/K12 backward variants).
+#include "ssd_tc.cuh"
+#include "../include/mamba_b200.h"
+
+namespace mb {
+namespace ssd {
+
+constexpr int kThreadsB = 256;
+
+constexpr int kDcbSmem = 2 * (128 * 128) + 2 * kL * 4 + 64 + 1024;
+
+__global__ void __launch_bounds__(kThreadsB, 2)
+ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restrict__ x, long long ldx,
+               const float* __restrict__ dtv, const float* __restrict__ av, bf16* __restrict__ dcb, int T, int H,
+               int G, int nc) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align1024(smem_raw);
+  uint8_t* sDY = smem;
+  uint8_t* sX = smem + 128 * 128;
+  float* s_a = reinterpret_cast<float*>(smem + 2 * 128 * 128);
+  float* s_dt = s_a + kL;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(s_dt + kL);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 1);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int blk = blockIdx.x % 3;
+  const int bc = blockIdx.x / 3;
+  const int b = bc / nc, c = bc % nc;
+  const int g = blockIdx.y;
+  const int hpg = H / G;
+  const int ri0 = blk == 0 ? 0 : 128;
+  const int cj0 = blk == 2 ? 128 : 0;
+  const int valid = min(kL, T - c * kL);
+  const size_t row_base = (size_t)b * T + (size_t)c * kL;
+
+  if (tid == 0) { mbar_init(bar, 1); fence_mbar_init(); }
+  if (warp == 0) { tmem_alloc(tmem_slot, 128); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  uint32_t phase = 0;
+
+  const int lg = warp & 3, half = warp >> 2;
+  const int r = lg * 32 + lane;
+  const int ri = ri0 + r;
+  const uint32_t lane_sel = (uint32_t)(lg * 32) << 16;
+  const int warp_row_max = ri0 + lg * 32 + 31;
+  float acc[64];
+#pragma unroll
+  for (int j = 0; j < 64; ++j) acc[j] = 0.f;
+
+  for (int hh = 0; hh < hpg; ++hh) {
+    const int h = g * hpg + hh;
+    const size_t sbase = ((size_t)bc * H + h) * kL;
+    s_a[tid] = av[sbase + tid];
+    s_dt[tid] = dtv[sbase + tid];
+    load_tile<1, false>(sDY, dy + (row_base + ri0) * lddy + h * kP, lddy, 128, max(0, min(128, valid - ri0)),
+                        NoScale(), tid, kThreadsB);
+    load_tile<1, false>(sX, x + (row_base + cj0) * ldx + h * kP, ldx, 128, max(0, min(128, valid - cj0)),
+                        NoScale(), tid, kThreadsB);
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (tid == 0) {
+      tc_fence_after();
+      constexpr uint32_t idesc = make_idesc_bf16(128, 128, MAJOR_K, MAJOR_K);
+      const uint32_t a_addr = smem_u32(sDY), b_addr = smem_u32(sX);
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks)
+        mma_bf16_ss(tmem, desc_kmajor(a_addr, 128, 0, ks), desc_kmajor(b_addr, 128, 0, ks), idesc, ks > 0 ? 1u : 0u);
+      mma_commit(bar);
+    }
+    mbar_wait(bar, phase);
+    phase ^= 1;
+    tc_fence_after();
+    const float a_i = s_a[ri];
+#pragma unroll
+    for (int ch = 0; ch < 2; ++ch) {
+      const int k0 = half * 64 + ch * 32;
+      if (cj0 + k0 > warp_row_max) continue;  // warp-uniform: block entirely above the diagonal
+      uint32_t v[32];
+      tmem_ld32(tmem + lane_sel + k0, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int cj = cj0 + k0 + j;
+        if (cj <= ri) acc[ch * 32 + j] += __uint_as_float(v[j]) * __expf(fminf(a_i - s_a[cj], 0.f)) * s_dt[cj];
+      }
+    }
+    tc_fence_before();
+    __syncthreads();
+  }
+  bf16* dst = dcb + (((size_t)bc * G + g) * kL + ri) * kL + cj0 + half * 64;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) st8(dst + 8 * q, pack8(acc + 8 * q));
+  if (warp == 0) tmem_dealloc(tmem, 128);
+}
+
+// ------------------------------------------------------------------------------------------
+constexpr int kDbdcStage = 128 * 128 + 64 * 2 * 128;  // A tile 16 KB + B tile 16 KB
+constexpr int kDbdcSmem = 2 * kDbdcStage + 64 + 1024;
+
+template <bool IS_DB>
+__global__ void __launch_bounds__(kThreadsB, 2)
+ssd_dbdc_kernel(const bf16* __restrict__ dcb,                       // [B,nc,G,256,256]
+                const bf16* __restrict__ bc_op, long long ldbc,     // dC: Bm base ; dB: Cm base (group 0 column)
+                const bf16* __restrict__ act, long long ldact,      // dC: dy ; dB: x
+                const bf16* __restrict__ st,                        // dC: S_prev bf16 ; dB: dS bf16   [B,nc,H,P,N]
+                const float* __restrict__ dtv, const float* __restrict__ av,
+                bf16* __restrict__ outp, long long ldo,             // dC / dB column base of group 0 in dxBC
+                int T, int H, int G, int nc) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align1024(smem_raw);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * kDbdcStage);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int rb = blockIdx.x & 1;
+  const int bc = blockIdx.x >> 1;
+  const int b = bc / nc, c = bc % nc;
+  const int g = blockIdx.y;
+  const int hpg = H / G;
+  const int m0 = rb * 128;  // output row block (i for dC, j for dB)
+  const int valid = min(kL, T - c * kL);
+  const size_t row_base = (size_t)b * T + (size_t)c * kL;
+  const bf16* G_base = dcb + ((size_t)bc * G + g) * kL * kL;
+
+  if (tid == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); fence_mbar_init(); }
+  if (warp == 0) { tmem_alloc(tmem_slot, 128); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  // part 1: K = j in [0, (rb+1)*128) for dC ; K = i in [rb*128, 256) for dB   (64 per stage)
+  const int k_begin = IS_DB ? m0 : 0;
+  const int k_end = IS_DB ? kL : m0 + 128;
+  const int n_part1 = (k_end - k_begin) / 64;
+  const int n_stages = n_part1 + hpg;
+
+  for (int s = 0; s < n_stages; ++s) {
+    const int buf = s & 1;
+    const int use = s >> 1;
+    if (use > 0) mbar_wait(&bars[buf], (use - 1) & 1);  // MMAs that read this buffer have retired
+    uint8_t* sA = smem + buf * kDbdcStage;
+    uint8_t* sB = sA + 128 * 128;
+    bool a_mn;
+    if (s < n_part1) {
+      const int kk = k_begin + s * 64;
+      const int kvalid = max(0, min(64, valid - kk));
+      if (!IS_DB) {
+        // A = G[m0 + r, kk .. kk+63]  (K-major, 128 rows) ; B = Bm[kk + krow, n]  (MN-major, 64 k-rows)
+        load_tile<1, false>(sA, G_base + (size_t)m0 * kL + kk, kL, 128, 128, NoScale(), tid, kThreadsB);
+        a_mn = false;
+      } else {
+        // A = G[kk + krow, m0 .. m0+127]  (MN-major: 64 k-rows x 2 atoms)
+        load_tile<2, false>(sA, G_base + (size_t)kk * kL + m0, kL, 64, 64, NoScale(), tid, kThreadsB);
+        a_mn = true;
+      }
+      load_tile<2, false>(sB, bc_op + (row_base + kk) * ldbc + g * kN, ldbc, 64, kvalid, NoScale(), tid, kThreadsB);
+    } else {
+      const int h = g * hpg + (s - n_part1);
+      const size_t sbase = ((size_t)bc * H + h) * kL;
+      const float a_last = av[sbase + kL - 1];
+      auto scale = [&](int row, int /*blk*/) {
+        const float a = av[sbase + m0 + row];
+        return IS_DB ? __expf(a_last - a) * dtv[sbase + m0 + row] : __expf(a);
+      };
+      load_tile<1, true>(sA, act + (row_base + m0) * ldact + h * kP, ldact, 128, max(0, min(128, valid - m0)), scale,
+                         tid, kThreadsB);
+      a_mn = false;
+      load_tile<2, false>(sB, st + ((size_t)bc * H + h) * kP * kN, kN, kP, kP, NoScale(), tid, kThreadsB);
+    }
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (tid == 0) {
+      tc_fence_after();
+      const uint32_t a_addr = smem_u32(sA), b_addr = smem_u32(sB);
+      const uint32_t idesc = make_idesc_bf16(128, kN, a_mn ? MAJOR_MN : MAJOR_K, MAJOR_MN);
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks) {
+        const uint64_t da = a_mn ? desc_mnmajor(a_addr, 64, ks) : desc_kmajor(a_addr, 128, 0, ks);
+        mma_bf16_ss(tmem, da, desc_mnmajor(b_addr, 64, ks), idesc, (s > 0 || ks > 0) ? 1u : 0u);
+      }
+      mma_commit(&bars[buf]);
+    }
+  }
+  {
+    const int s_last = n_stages - 1;
+    mbar_wait(&bars[s_last & 1], (s_last >> 1) & 1);  // MMAs retire in order: the last commit covers all
+    tc_fence_after();
+  }
+  const int lg = warp & 3, half = warp >> 2;
+  const int r = lg * 32 + lane;
+  const int mi = m0 + r;
+#pragma unroll
+  for (int ch = 0; ch < 2; ++ch) {
+    const int col = half * 64 + ch * 32;
+    uint32_t v[32];
+    tmem_ld32(tmem + ((uint32_t)(lg * 32) << 16) + col, v);
+    tmem_ld_wait();
+    if (mi < valid) {
+      float f[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+      bf16* dst = outp + (row_base + mi) * ldo + g * kN + col;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) st8(dst + 8 * q, pack8(f + 8 * q));
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 128);
+}
+
+}  // namespace ssd
+}  // namespace mb
+using namespace mb;
+using namespace mb::ssd;
+
+extern "C" int mb_ssd_bwd_dcb(const void* dy, long long lddy, const void* x, long long ldx, const float* dt,
+                              const float* a, void* dcb, int B, int T, int H, int G, int P, int N, int L,
+                              cudaStream_t stream) {
+  MB_REQUIRE(L == kL && P == kP && N == kN, "ssd_bwd_dcb: needs chunk=256, headdim=64, d_state=128");
+  const int nc = cdiv(T, L);
+  static bool once = false;
+  if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_dcb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDcbSmem)); once = true; }
+  dim3 grid(B * nc * 3, G);
+  ssd_dcb_kernel<<<grid, kThreadsB, kDcbSmem, stream>>>((const bf16*)dy, lddy, (const bf16*)x, ldx, dt, a, (bf16*)dcb, T, H, G, nc);
+  return check_launch("ssd_bwd_dcb");
+}
+
+extern "C" int mb_ssd_bwd_dbdc(const void* dcb, const void* Bm, const void* Cm, long long ldbc, const void* dy,
+                               long long lddy, const void* x, long long ldx, const void* sprev_bf16,
+                               const void* ds_bf16, const float* dt, const float* a, void* dB, void* dC,
+                               long long ldo, int B, int T, int H, int G, int P, int N, int L,
+                               cudaStream_t stream) {
+  MB_REQUIRE(L == kL && P == kP && N == kN, "ssd_bwd_dbdc: needs chunk=256, headdim=64, d_state=128");
+  const int nc = cdiv(T, L);
+  static bool once = false;
+  if (!once) {
+    MB_CUDA(cudaFuncSetAttribute(ssd_dbdc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDbdcSmem));
+    MB_CUDA(cudaFuncSetAttribute(ssd_dbdc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDbdcSmem));
+    once = true;
+  }
+  dim3 grid(B * nc * 2, G);
+  ssd_dbdc_kernel<false><<<grid, kThreadsB, kDbdcSmem, stream>>>((const bf16*)dcb, (const bf16*)Bm, ldbc, (const bf16*)dy, lddy,
+                                                                 (const bf16*)sprev_bf16, dt, a, (bf16*)dC, ldo, T, H, G, nc);
+  if (check_launch("ssd_bwd_dbdc/dC")) return 1;
+  ssd_dbdc_kernel<true><<<grid, kThreadsB, kDbdcSmem, stream>>>((const bf16*)dcb, (const bf16*)Cm, ldbc, (const bf16*)x, ldx,
+                                                                (const bf16*)ds_bf16, dt, a, (bf16*)dB, ldo, T, H, G, nc);
+  return check_launch("ssd_bwd_dbdc/dB");
+}

@@ -1,0 +1,242 @@
+// SSD (Mamba-2) support kernels that are not GEMM-shaped: K7 (dt softplus + chunk cumsum), K10
+// (inter-chunk state passing, forward and reverse) and the backward "finalize" pass that turns
+// the per-token partials produced by the tcgen05 kernels into d(dt_raw), dA_log, d(dt_bias).
+// Replaces the Triton kernels of mamba_ssm/ops/triton/ssd_chunk_state.py::_chunk_cumsum_* and
+// ssd_state_passing.py.  All fp32.
+//
+// Layouts:  dt, a (= cumsum of dt*A inside the chunk):  [B, nc, H, L] fp32
+//           states / dstates:                           [B, nc, H, P, N] fp32
+//           S_prev / dS operand copies:                 [B, nc, H, P, N] bf16
+#include "common.cuh"
+#include "../include/mamba_b200.h"
+
+namespace mb {
+
+// one block = one (b, c); thread t = token c*L + t (L == blockDim.x == 256 or 128 or 64)
+__global__ void ssd_prep_kernel(const bf16* __restrict__ dt_raw, long long ld_dt,
+                                const float* __restrict__ dt_bias, const float* __restrict__ A_log,
+                                float* __restrict__ dt_out, float* __restrict__ a_out, int T, int H, int L,
+                                int nc) {
+  extern __shared__ float sm[];  // [H][L] dA, then scanned in place
+  const int b = blockIdx.x / nc, c = blockIdx.x % nc;
+  const int t = threadIdx.x;
+  const int tok = c * L + t;
+  const bool valid = tok < T;
+  const bf16* src = dt_raw + ((size_t)b * T + tok) * ld_dt;
+  float* dt_o = dt_out + ((size_t)(b * nc + c) * H) * L;
+  float* a_o = a_out + ((size_t)(b * nc + c) * H) * L;
+  for (int h = 0; h < H; ++h) {
+    float dt = 0.f;
+    if (valid) dt = softplus_f(__bfloat162float(src[h]) + dt_bias[h]);
+    dt_o[(size_t)h * L + t] = dt;
+    sm[h * L + t] = dt * (-__expf(A_log[h]));
+  }
+  __syncthreads();
+  // inclusive scan over t for each h: warp w handles heads w, w+nw, ...
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  const int per = L / 32;  // consecutive elements per lane
+  for (int h = warp; h < H; h += nw) {
+    float* row = sm + h * L;
+    float run = 0.f;
+    float loc[8];
+    for (int i = 0; i < per; ++i) { run += row[lane * per + i]; loc[i] = run; }
+    float incl = run;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      float v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    const float excl = incl - run;
+    for (int i = 0; i < per; ++i) a_o[(size_t)h * L + lane * per + i] = loc[i] + excl;
+  }
+}
+
+// Forward recurrence over chunks.  One thread = 4 consecutive elements of the (P*N) state.
+__global__ void ssd_state_passing_fwd_kernel(const float* __restrict__ states, const float* __restrict__ a,
+                                             bf16* __restrict__ sprev_bf16, float* __restrict__ final_state,
+                                             int nc, int H, int PN, int L) {
+  const int bh = blockIdx.y;  // b * H + h
+  const int b = bh / H, h = bh % H;
+  const int e = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (e >= PN) return;
+  float4 prev = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int c = 0; c < nc; ++c) {
+    const size_t base = ((size_t)(b * nc + c) * H + h) * PN + e;
+    bf162 lo = __floats2bfloat162_rn(prev.x, prev.y), hi = __floats2bfloat162_rn(prev.z, prev.w);
+    *reinterpret_cast<bf162*>(sprev_bf16 + base) = lo;
+    *reinterpret_cast<bf162*>(sprev_bf16 + base + 2) = hi;
+    const float decay = __expf(a[((size_t)(b * nc + c) * H + h) * L + (L - 1)]);
+    const float4 s = *reinterpret_cast<const float4*>(states + base);
+    prev.x = decay * prev.x + s.x; prev.y = decay * prev.y + s.y;
+    prev.z = decay * prev.z + s.z; prev.w = decay * prev.w + s.w;
+  }
+  if (final_state != nullptr) *reinterpret_cast<float4*>(final_state + (size_t)bh * PN + e) = prev;
+}
+
+// Reverse recurrence.  dstates_direct[c] = gradient reaching the state that ENTERS chunk c through
+// the C.S_prev term.  Outputs: ds_bf16[c] = total gradient of chunk c's own contribution S_c
+// (== total gradient of the state entering chunk c+1), and da_last[b,c,h] += sum(g * decay * S_prev).
+__global__ void ssd_state_passing_bwd_kernel(const float* __restrict__ dstates_direct,
+                                             const bf16* __restrict__ sprev_bf16, const float* __restrict__ a,
+                                             bf16* __restrict__ ds_bf16, float* __restrict__ da_last, int nc,
+                                             int H, int PN, int L) {
+  const int bh = blockIdx.y;
+  const int b = bh / H, h = bh % H;
+  const int e = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  const bool active = e < PN;
+  float4 g = make_float4(0.f, 0.f, 0.f, 0.f);  // gradient of the state entering chunk c+1
+  __shared__ float red[32];
+  for (int c = nc - 1; c >= 0; --c) {
+    const size_t base = ((size_t)(b * nc + c) * H + h) * PN + e;
+    const float decay = __expf(a[((size_t)(b * nc + c) * H + h) * L + (L - 1)]);
+    float part = 0.f;
+    if (active) {
+      *reinterpret_cast<bf162*>(ds_bf16 + base) = __floats2bfloat162_rn(g.x, g.y);
+      *reinterpret_cast<bf162*>(ds_bf16 + base + 2) = __floats2bfloat162_rn(g.z, g.w);
+      const float2 p0 = __bfloat1622float2(*reinterpret_cast<const bf162*>(sprev_bf16 + base));
+      const float2 p1 = __bfloat1622float2(*reinterpret_cast<const bf162*>(sprev_bf16 + base + 2));
+      part = decay * (g.x * p0.x + g.y * p0.y + g.z * p1.x + g.w * p1.y);
+      const float4 d = *reinterpret_cast<const float4*>(dstates_direct + base);
+      g.x = d.x + decay * g.x; g.y = d.y + decay * g.y; g.z = d.z + decay * g.z; g.w = d.w + decay * g.w;
+    }
+    part = warp_sum(part);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = part;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      float v = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
+      v = warp_sum(v);
+      if (threadIdx.x == 0 && v != 0.f) atomicAdd(da_last + (size_t)(b * nc + c) * H + h, v);
+    }
+    __syncthreads();
+  }
+}
+
+// Backward finalize.  One block = one (b, c), thread t = token.  For every head:
+//   rowpart_t = sum_p dY[t,p] * y_ssm[t,p]   (y_ssm = y - D x, stored by forward; d a_t from Y_off and M)
+//   da_t      = rowpart_t - dt_t * (ddt1_t + ddt2_t)  (+ da_last at t = L-1, + sum_s dt_s ddt2_s at L-1)
+//   ddA_t     = suffix-sum_{s >= t} da_s ;  ddt_t = ddt1_t + ddt2_t + A_h * ddA_t
+//   draw_t    = ddt_t * sigmoid(raw_t + bias_h) -> bf16 into the dt columns of d(zxbcdt)
+//   dA_log_h += A_h * sum_t dt_t * ddA_t ;  ddt_bias_h += sum_t draw_t
+__global__ void ssd_bwd_finalize_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restrict__ y,
+                                        long long ldy, const bf16* __restrict__ dt_raw, long long ld_dt,
+                                        const float* __restrict__ dt, const float* __restrict__ ddt1,
+                                        const float* __restrict__ ddt2, const float* __restrict__ da_last,
+                                        const float* __restrict__ dt_bias, const float* __restrict__ A_log,
+                                        bf16* __restrict__ draw_out,
+                                        long long ld_draw, float* __restrict__ dA_log, float* __restrict__ ddt_bias,
+                                        int T, int H, int P, int L, int nc) {
+  __shared__ float wsum[8];
+  __shared__ float red3[2][8];
+  const int b = blockIdx.x / nc, c = blockIdx.x % nc;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5, nw = blockDim.x >> 5;
+  const int tok = c * L + t;
+  const bool valid = tok < T;
+  const size_t row = (size_t)b * T + tok;
+  for (int h = 0; h < H; ++h) {
+    const size_t sidx = ((size_t)(b * nc + c) * H + h) * L + t;
+    const float A = -__expf(A_log[h]);
+    const float dtv = dt[sidx];
+    float rowpart = 0.f;
+    if (valid) {
+      const bf16* pdy = dy + row * lddy + h * P;
+      const bf16* py = y + row * ldy + h * P;
+      for (int p = 0; p < P; p += 8) {
+        float a8[8], b8[8];
+        unpack8(ld8(pdy + p), a8); unpack8(ld8(py + p), b8);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) rowpart += a8[j] * b8[j];
+      }
+    }
+    const float d1 = ddt1[sidx], d2 = ddt2[sidx];
+    float da = rowpart - dtv * (d1 + d2);
+    // a_last receives: state-passing term and sum_s dt_s * ddt2_s  (w_s = exp(a_last - a_s) dt_s)
+    float q = dtv * d2;
+    q = warp_sum(q);
+    if (lane == 0) wsum[warp] = q;
+    __syncthreads();
+    if (t == L - 1) {
+      float tot = 0.f;
+      for (int w = 0; w < nw; ++w) tot += wsum[w];
+      da += tot + da_last[(size_t)(b * nc + c) * H + h];
+    }
+    __syncthreads();
+    // suffix sum over t (inclusive): reverse inclusive scan
+    float incl = da;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      float v = __shfl_down_sync(0xffffffffu, incl, o);
+      if (lane + o < 32) incl += v;
+    }
+    if (lane == 0) wsum[warp] = incl;  // total of this warp
+    __syncthreads();
+    float after = 0.f;
+    for (int w = warp + 1; w < nw; ++w) after += wsum[w];
+    const float ddA = incl + after;
+    const float ddt = d1 + d2 + A * ddA;
+    float draw = 0.f;
+    if (valid) {
+      const float raw = __bfloat162float(dt_raw[row * ld_dt + h]) + dt_bias[h];
+      draw = ddt * sigmoid_f(raw);
+      draw_out[row * ld_draw + h] = __float2bfloat16(draw);
+    }
+    float r0 = warp_sum(dtv * ddA), r1 = warp_sum(draw);
+    __syncthreads();
+    if (lane == 0) { red3[0][warp] = r0; red3[1][warp] = r1; }
+    __syncthreads();
+    if (t == 0) {
+      float s0 = 0.f, s1 = 0.f;
+      for (int w = 0; w < nw; ++w) { s0 += red3[0][w]; s1 += red3[1][w]; }
+      atomicAdd(dA_log + h, A * s0);
+      atomicAdd(ddt_bias + h, s1);
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace mb
+using namespace mb;
+
+extern "C" int mb_ssd_prep(const void* dt_raw, long long ld_dt, const float* dt_bias, const float* A_log,
+                           float* dt_out, float* a_out, int B, int T, int H, int L, cudaStream_t stream) {
+  MB_REQUIRE(L == 64 || L == 128 || L == 256, "ssd_prep: chunk size %d not in {64,128,256}", L);
+  const int nc = cdiv(T, L);
+  const size_t smem = (size_t)H * L * sizeof(float);
+  MB_REQUIRE(smem <= 200 * 1024, "ssd_prep: H*L too large for shared memory");
+  if (smem > 48 * 1024) MB_CUDA(cudaFuncSetAttribute(ssd_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  ssd_prep_kernel<<<B * nc, L, smem, stream>>>((const bf16*)dt_raw, ld_dt, dt_bias, A_log, dt_out, a_out, T, H, L, nc);
+  return check_launch("ssd_prep");
+}
+
+extern "C" int mb_ssd_state_passing_fwd(const float* states, const float* a, void* sprev_bf16,
+                                        float* final_state, int B, int nc, int H, int PN, int L,
+                                        cudaStream_t stream) {
+  MB_REQUIRE(PN % 4 == 0, "ssd_state_passing_fwd: P*N must be a multiple of 4");
+  dim3 grid(cdiv(PN / 4, 256), B * H);
+  ssd_state_passing_fwd_kernel<<<grid, 256, 0, stream>>>(states, a, (bf16*)sprev_bf16, final_state, nc, H, PN, L);
+  return check_launch("ssd_state_passing_fwd");
+}
+
+extern "C" int mb_ssd_state_passing_bwd(const float* dstates_direct, const void* sprev_bf16, const float* a,
+                                        void* ds_bf16, float* da_last, int B, int nc, int H, int PN, int L,
+                                        cudaStream_t stream) {
+  MB_REQUIRE(PN % 4 == 0, "ssd_state_passing_bwd: P*N must be a multiple of 4");
+  MB_CUDA(cudaMemsetAsync(da_last, 0, (size_t)B * nc * H * sizeof(float), stream));
+  dim3 grid(cdiv(PN / 4, 256), B * H);
+  ssd_state_passing_bwd_kernel<<<grid, 256, 0, stream>>>(dstates_direct, (const bf16*)sprev_bf16, a, (bf16*)ds_bf16,
+                                                         da_last, nc, H, PN, L);
+  return check_launch("ssd_state_passing_bwd");
+}
+
+extern "C" int mb_ssd_bwd_finalize(const void* dy, long long lddy, const void* y_ssm, long long ldy,
+                                   const void* dt_raw, long long ld_dt, const float* dt, const float* ddt1,
+                                   const float* ddt2, const float* da_last, const float* dt_bias,
+                                   const float* A_log, void* draw_out, long long ld_draw, float* dA_log,
+                                   float* ddt_bias, int B, int T, int H, int P, int L, cudaStream_t stream) {
+  MB_REQUIRE(L == 64 || L == 128 || L == 256, "ssd_bwd_finalize: chunk size %d not in {64,128,256}", L);
+  MB_REQUIRE(P % 8 == 0, "ssd_bwd_finalize: headdim must be a multiple of 8");
+  const int nc = cdiv(T, L);
+  ssd_bwd_finalize_kernel<<<B * nc, L, 0, stream>>>((const bf16*)dy, lddy, (const bf16*)y_ssm, ldy,
+                                                    (const bf16*)dt_raw, ld_dt, dt, ddt1, ddt2, da_last, dt_bias,
+                                                    A_log, (bf16*)draw_out, ld_draw, dA_log, ddt_bias, T, H, P, L, nc);
+  return check_launch("ssd_bwd_finalize");
+}

@@ -65,6 +65,40 @@ int mb_gemm_bf16(const void* A, long long lda, int a_major, const void* B, long 
                  void* D, long long ldd, int d_mode, const float* bias, int M, int N, int K,
                  float alpha, cudaStream_t stream);
 
+/* ---- K7-K12: Mamba-2 SSD chunked scan (mamba_ssm Triton ssd_* kernels, forward + backward) ----
+ * Layouts: dt, a = cumsum(dt*A) per chunk: fp32 [B, nc, H, L]; states: fp32 [B, nc, H, P, N];
+ * bf16 state operand copies: [B, nc, H, P, N]; x | B | C are column slices of the conv output. */
+int mb_ssd_prep(const void* dt_raw, long long ld_dt, const float* dt_bias, const float* A_log,
+                float* dt_out, float* a_out, int B, int T, int H, int L, cudaStream_t stream);
+int mb_ssd_chunk_state(const void* arow, long long lda, const void* bop, long long ldb, const float* dt,
+                       const float* a, float* out, int dstate, int B, int T, int H, int G, int P, int N,
+                       int L, cudaStream_t stream);
+int mb_ssd_state_passing_fwd(const float* states, const float* a, void* sprev_bf16, float* final_state,
+                             int B, int nc, int H, int PN, int L, cudaStream_t stream);
+int mb_ssd_state_passing_bwd(const float* dstates_direct, const void* sprev_bf16, const float* a,
+                             void* ds_bf16, float* da_last, int B, int nc, int H, int PN, int L,
+                             cudaStream_t stream);
+int mb_ssd_chunk_scan_fwd(const void* Cm, const void* Bm, long long ldbc, const void* x, long long ldx,
+                          const void* sprev_bf16, const float* dt, const float* a, const float* D, void* y,
+                          void* y_ssm, long long ldy, int B, int T, int H, int G, int P, int N, int L,
+                          cudaStream_t stream);
+int mb_ssd_chunk_scan_bwd_dx(const void* Bm, const void* Cm, long long ldbc, const void* dy, long long lddy,
+                             const void* ds_bf16, const float* dt, const float* a, const float* D, void* dx,
+                             long long lddx, const void* x, long long ldx, float* ddt1, float* ddt2,
+                             float* dD, int B, int T, int H, int G, int P, int N, int L, cudaStream_t stream);
+int mb_ssd_bwd_dcb(const void* dy, long long lddy, const void* x, long long ldx, const float* dt,
+                   const float* a, void* dcb, int B, int T, int H, int G, int P, int N, int L,
+                   cudaStream_t stream);
+int mb_ssd_bwd_dbdc(const void* dcb, const void* Bm, const void* Cm, long long ldbc, const void* dy,
+                    long long lddy, const void* x, long long ldx, const void* sprev_bf16,
+                    const void* ds_bf16, const float* dt, const float* a, void* dB, void* dC, long long ldo,
+                    int B, int T, int H, int G, int P, int N, int L, cudaStream_t stream);
+int mb_ssd_bwd_finalize(const void* dy, long long lddy, const void* y_ssm, long long ldy,
+                        const void* dt_raw, long long ld_dt, const float* dt, const float* ddt1,
+                        const float* ddt2, const float* da_last, const float* dt_bias, const float* A_log,
+                        void* draw_out, long long ld_draw, float* dA_log, float* ddt_bias, int B, int T, int H,
+                        int P, int L, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -30,7 +30,7 @@ def native_enabled() -> bool:
 
 
 @contextlib.contextmanager
-def native(enabled: bool):
+def native_mode(enabled: bool):
     prev = _state["enabled"]
     _state["enabled"] = enabled
     try:

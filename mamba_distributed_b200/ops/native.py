@@ -21,7 +21,7 @@ import torch
 from . import _lib, ref
 from ._lib import call
 
-_SSD_IMPL = os.environ.get("MAMBA_B200_SSD", "torch")      # "native" | "torch"
+_SSD_IMPL = os.environ.get("MAMBA_B200_SSD", "native")     # "native" | "torch"
 _GEMM_IMPL = os.environ.get("MAMBA_B200_GEMM", "native")   # "native" | "cublas" (comparison arm)
 _CE_IMPL = os.environ.get("MAMBA_B200_CE", "native")       # "native" | "chunked"
 

@@ -44,15 +44,24 @@ def _torch_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D
     return gdb, gAl, gD
 
 
-def ssd_fwd(xBC, zxbcdt, Bsz, T, cfg, dt_bias, A_log, D):
+def _use_torch(cfg):
+    """The tensor-core kernels are specialised for chunk 256 / headdim 64 / d_state 128 (every
+    benchmark config); other geometries run the oracle math on the GPU."""
     if _SSD_IMPL == "torch":
+        return True
+    from . import ssd_kernels
+    return not ssd_kernels.supported(cfg)
+
+
+def ssd_fwd(xBC, zxbcdt, Bsz, T, cfg, dt_bias, A_log, D):
+    if _use_torch(cfg):
         return _torch_fwd(xBC, zxbcdt, Bsz, T, cfg, dt_bias, A_log, D)
     from . import ssd_kernels
     return ssd_kernels.ssd_fwd(xBC, zxbcdt, Bsz, T, cfg, dt_bias, A_log, D)
 
 
 def ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, saved):
-    if _SSD_IMPL == "torch":
+    if _use_torch(cfg):
         return _torch_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, saved)
     from . import ssd_kernels
     return ssd_kernels.ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, saved)
