@@ -29,14 +29,21 @@ int check_launch(const char* what);            // cudaGetLastError -> set_error;
   } while (0)
 
 // ---- small math -------------------------------------------------------------------------------
-__device__ __forceinline__ float silu_f(float x) { return x / (1.f + __expf(-x)); }
+// sigmoid with one MUFU.EX2 + one MUFU.RCP (no IEEE division sequence)
+__device__ __forceinline__ float sigmoid_f(float x) { return __frcp_rn(1.f + __expf(-x)); }
+__device__ __forceinline__ float silu_f(float x) { return x * sigmoid_f(x); }
 // d/dx silu(x) = s + x*s*(1-s), s = sigmoid(x)
 __device__ __forceinline__ float dsilu_f(float x) {
-  float s = 1.f / (1.f + __expf(-x));
+  const float s = sigmoid_f(x);
   return s * (1.f + x * (1.f - s));
 }
+// silu and its derivative from a single sigmoid evaluation
+__device__ __forceinline__ void silu_both(float x, float& f, float& df) {
+  const float s = sigmoid_f(x);
+  f = x * s;
+  df = s * (1.f + x * (1.f - s));
+}
 __device__ __forceinline__ float softplus_f(float x) { return x > 20.f ? x : log1pf(__expf(x)); }
-__device__ __forceinline__ float sigmoid_f(float x) { return 1.f / (1.f + __expf(-x)); }
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

@@ -42,21 +42,31 @@ conv1d_fwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __rest
       for (int j = 0; j < 8; ++j) win[k + 1][j] = 0.f;
     }
   }
-  for (int t = t0; t < t1; ++t) {
+  constexpr int U = 8;  // tokens loaded ahead per thread (memory-level parallelism)
+  for (int tb = t0; tb < t1; tb += U) {
+    bf16x8 raw[U];
 #pragma unroll
-    for (int k = 0; k < W - 1; ++k)
+    for (int u = 0; u < U; ++u)
+      if (tb + u < t1) raw[u] = ld8(xb + (size_t)(tb + u) * ldx);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) win[k][j] = win[k + 1][j];
-    unpack8(ld8(xb + (size_t)t * ldx), win[W - 1]);
-    float o[8];
+    for (int u = 0; u < U; ++u) {
+      const int t = tb + u;
+      if (t >= t1) break;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      float a = bs[j];
+      for (int k = 0; k < W - 1; ++k)
 #pragma unroll
-      for (int k = 0; k < W; ++k) a += wt[j][k] * win[k][j];
-      o[j] = SILU ? silu_f(a) : a;
+        for (int j = 0; j < 8; ++j) win[k][j] = win[k + 1][j];
+      unpack8(raw[u], win[W - 1]);
+      float o[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float a = bs[j];
+#pragma unroll
+        for (int k = 0; k < W; ++k) a += wt[j][k] * win[k][j];
+        o[j] = SILU ? silu_f(a) : a;
+      }
+      st8(yb + (size_t)t * ldy, pack8(o));
     }
-    st8(yb + (size_t)t * ldy, pack8(o));
   }
 }
 
@@ -95,45 +105,58 @@ conv1d_bwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __rest
     if (t >= 0) unpack8(ld8(xb + (size_t)t * ldx), win[k + 1]);
   }
   const int tend = t1 + (W - 1);  // g of the W-1 tokens after the tile feeds dx of the tile's tail
-  for (int t = t0; t < tend; ++t) {
+  constexpr int U = 8;
+  for (int tb = t0; tb < tend; tb += U) {
+    bf16x8 rx[U], rg[U];
 #pragma unroll
-    for (int k = 0; k < W - 1; ++k)
-#pragma unroll
-      for (int j = 0; j < 8; ++j) { win[k][j] = win[k + 1][j]; gw[k][j] = gw[k + 1][j]; }
-    if (t < T) {
-      float g[8];
-      unpack8(ld8(xb + (size_t)t * ldx), win[W - 1]);
-      unpack8(ld8(gb + (size_t)t * lddy), g);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        if (SILU) {
-          float a = bs[j];
-#pragma unroll
-          for (int k = 0; k < W; ++k) a += wt[j][k] * win[k][j];
-          g[j] *= dsilu_f(a);
-        }
-        gw[W - 1][j] = g[j];
-        if (t < t1) {  // this tile owns the weight-gradient contribution of token t
-          dba[j] += g[j];
-#pragma unroll
-          for (int k = 0; k < W; ++k) dwa[j][k] += g[j] * win[k][j];
-        }
+    for (int u = 0; u < U; ++u)
+      if (tb + u < tend && tb + u < T) {
+        rx[u] = ld8(xb + (size_t)(tb + u) * ldx);
+        rg[u] = ld8(gb + (size_t)(tb + u) * lddy);
       }
-    } else {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) { gw[W - 1][j] = 0.f; win[W - 1][j] = 0.f; }
-    }
-    const int s = t - (W - 1);  // dx[s] = sum_k w[k] * g[s + (W-1) - k] = sum_k w[k] * gw[W-1-k]
-    if (s >= t0 && s < t1) {
-      float o[8];
+    for (int u = 0; u < U; ++u) {
+      const int t = tb + u;
+      if (t >= tend) break;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float a = 0.f;
+      for (int k = 0; k < W - 1; ++k)
 #pragma unroll
-        for (int k = 0; k < W; ++k) a += wt[j][k] * gw[W - 1 - k][j];
-        o[j] = a;
+        for (int j = 0; j < 8; ++j) { win[k][j] = win[k + 1][j]; gw[k][j] = gw[k + 1][j]; }
+      if (t < T) {
+        float g[8];
+        unpack8(rx[u], win[W - 1]);
+        unpack8(rg[u], g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          if (SILU) {
+            float a = bs[j];
+#pragma unroll
+            for (int k = 0; k < W; ++k) a += wt[j][k] * win[k][j];
+            g[j] *= dsilu_f(a);
+          }
+          gw[W - 1][j] = g[j];
+          if (t < t1) {  // this tile owns the weight-gradient contribution of token t
+            dba[j] += g[j];
+#pragma unroll
+            for (int k = 0; k < W; ++k) dwa[j][k] += g[j] * win[k][j];
+          }
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { gw[W - 1][j] = 0.f; win[W - 1][j] = 0.f; }
       }
-      st8(dxb + (size_t)s * lddx, pack8(o));
+      const int s_ = t - (W - 1);  // dx[s] = sum_k w[k] * g[s + (W-1) - k] = sum_k w[k] * gw[W-1-k]
+      if (s_ >= t0 && s_ < t1) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float a = 0.f;
+#pragma unroll
+          for (int k = 0; k < W; ++k) a += wt[j][k] * gw[W - 1 - k][j];
+          o[j] = a;
+        }
+        st8(dxb + (size_t)s_ * lddx, pack8(o));
+      }
     }
   }
 #pragma unroll

@@ -148,14 +148,23 @@ add_rmsnorm_bwd_kernel(const float* __restrict__ r, const bf16* __restrict__ dy,
   }
 }
 
-// dw[col] (+)= sum_p partial[p][col]
+// dw[col] (+)= sum_p partial[p][col].   Block = 32 columns x 32 row-lanes; rows strided by 32.
 __global__ void colsum_partials_kernel(const float* __restrict__ partial, float* __restrict__ dw,
                                        int P, int D, int accumulate) {
-  const int col = blockIdx.x * blockDim.x + threadIdx.x;
-  if (col >= D) return;
+  __shared__ float red[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int col = blockIdx.x * 32 + tx;
   float s = 0.f;
-  for (int p = 0; p < P; ++p) s += partial[(size_t)p * D + col];
-  dw[col] = accumulate ? dw[col] + s : s;
+  if (col < D)
+    for (int p = ty; p < P; p += 32) s += partial[(size_t)p * D + col];
+  red[ty][tx] = s;
+  __syncthreads();
+  if (ty == 0 && col < D) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) t += red[i][tx];
+    dw[col] = accumulate ? dw[col] + t : t;
+  }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -260,11 +269,12 @@ gated_rmsnorm_bwd_kernel(const bf16* __restrict__ x, int ldx, const bf16* __rest
         ld8f(weight + col, w);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          const float sg = silu_f(zz[j]);
+          float sg, dsg;
+          silu_both(zz[j], sg, dsg);
           const float xh = xv[j] * sg * rstd;
           const float dxs = (go[j] * w[j] - xh * c) * rstd;
           ox[j] = dxs * sg;
-          oz[j] = dxs * xv[j] * dsilu_f(zz[j]);
+          oz[j] = dxs * xv[j] * dsg;
         }
         st8(dx + (size_t)m * lddx + col, pack8(ox));
         st8(dz + (size_t)m * lddz + col, pack8(oz));
@@ -347,7 +357,7 @@ extern "C" int mb_add_rmsnorm_bwd(const float* r, const void* dy, const float* r
         r, (const bf16*)dy, rstd, weight, dres_in, dres_out, (bf16*)dx_bf16, scratch, M, D);
   });
   if (check_launch("add_rmsnorm_bwd")) return 1;
-  colsum_partials_kernel<<<cdiv(D, 256), 256, 0, stream>>>(scratch, dw, grid, D, dw_accumulate);
+  colsum_partials_kernel<<<cdiv(D, 32), 1024, 0, stream>>>(scratch, dw, grid, D, dw_accumulate);
   return check_launch("add_rmsnorm_bwd/colsum");
 }
 
@@ -384,6 +394,6 @@ extern "C" int mb_gated_rmsnorm_bwd(const void* x, int ldx, const void* z, int l
         (bf16*)dz, lddz, scratch, M, G, group_size);
   });
   if (check_launch("gated_rmsnorm_bwd")) return 1;
-  colsum_partials_kernel<<<cdiv(D, 256), 256, 0, stream>>>(scratch, dw, grid, D, dw_accumulate);
+  colsum_partials_kernel<<<cdiv(D, 32), 1024, 0, stream>>>(scratch, dw, grid, D, dw_accumulate);
   return check_launch("gated_rmsnorm_bwd/colsum");
 }

@@ -16,7 +16,7 @@ namespace ssd {
 
 constexpr int kThreadsB = 256;
 
-constexpr int kDcbSmem = 2 * (128 * 128) + 2 * kL * 4 + 64 + 1024;
+constexpr int kDcbSmem = 2 * 2 * (128 * 128) + 2 * 2 * kL * 4 + 64 + 1024;  // double-buffered per-head tiles
 
 __global__ void __launch_bounds__(kThreadsB, 2)
 ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restrict__ x, long long ldx,
@@ -24,11 +24,8 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
                int G, int nc) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align1024(smem_raw);
-  uint8_t* sDY = smem;
-  uint8_t* sX = smem + 128 * 128;
-  float* s_a = reinterpret_cast<float*>(smem + 2 * 128 * 128);
-  float* s_dt = s_a + kL;
-  uint64_t* bar = reinterpret_cast<uint64_t*>(s_dt + kL);
+  float* s_ad = reinterpret_cast<float*>(smem + 2 * 2 * 128 * 128);  // [2][a(256) | dt(256)]
+  uint64_t* bar = reinterpret_cast<uint64_t*>(s_ad + 2 * 2 * kL);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 1);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -59,15 +56,28 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
 #pragma unroll
   for (int j = 0; j < 64; ++j) acc[j] = 0.f;
 
-  for (int hh = 0; hh < hpg; ++hh) {
+  auto prefetch_head = [&](int hh) {
     const int h = g * hpg + hh;
-    const size_t sbase = ((size_t)bc * H + h) * kL;
-    s_a[tid] = av[sbase + tid];
-    s_dt[tid] = dtv[sbase + tid];
-    load_tile<1, false>(sDY, dy + (row_base + ri0) * lddy + h * kP, lddy, 128, max(0, min(128, valid - ri0)),
+    const int bsel = hh & 1;
+    const size_t sb = ((size_t)bc * H + h) * kL;
+    const uint32_t ad = smem_u32(s_ad + bsel * 2 * kL);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(ad + tid * 4), "l"(av + sb + tid) : "memory");
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(ad + (kL + tid) * 4), "l"(dtv + sb + tid) : "memory");
+    uint8_t* t0 = smem + bsel * 2 * 128 * 128;
+    load_tile<1, false>(t0, dy + (row_base + ri0) * lddy + h * kP, lddy, 128, max(0, min(128, valid - ri0)),
                         NoScale(), tid, kThreadsB);
-    load_tile<1, false>(sX, x + (row_base + cj0) * ldx + h * kP, ldx, 128, max(0, min(128, valid - cj0)),
-                        NoScale(), tid, kThreadsB);
+    load_tile<1, false>(t0 + 128 * 128, x + (row_base + cj0) * ldx + h * kP, ldx, 128,
+                        max(0, min(128, valid - cj0)), NoScale(), tid, kThreadsB);
+    cp_async_commit();
+  };
+  prefetch_head(0);
+  for (int hh = 0; hh < hpg; ++hh) {
+    uint8_t* sDY = smem + (hh & 1) * 2 * 128 * 128;
+    uint8_t* sX = sDY + 128 * 128;
+    const float* s_a = s_ad + (hh & 1) * 2 * kL;
+    const float* s_dt = s_a + kL;
+    if (hh + 1 < hpg) { prefetch_head(hh + 1); cp_async_wait<1>(); }
+    else cp_async_wait<0>();
     fence_proxy_async_smem();
     __syncthreads();
     if (tid == 0) {
@@ -180,6 +190,8 @@ ssd_dbdc_kernel(const bf16* __restrict__ dcb,                       // [B,nc,G,2
       a_mn = false;
       load_tile<2, false>(sB, st + ((size_t)bc * H + h) * kP * kN, kN, kP, kP, NoScale(), tid, kThreadsB);
     }
+    cp_async_commit();
+    cp_async_wait<0>();
     fence_proxy_async_smem();
     __syncthreads();
     if (tid == 0) {

@@ -56,9 +56,11 @@ ssd_outer_kernel(const bf16* __restrict__ arow, long long lda, const bf16* __res
 
   const size_t row0 = (size_t)b * T + (size_t)c * kL;
   auto scale = [&](int row, int blk) { return s_scale[blk * kL + row]; };
+  load_tile<2, false>(sB, bop + row0 * ldb + g * kN, ldb, kL, valid, NoScale(), tid, kThreads);  // async
   if (hpc == 2) load_tile<2, true>(sA, arow + row0 * lda + h0 * kP, lda, kL, valid, scale, tid, kThreads);
   else load_tile<1, true>(sA, arow + row0 * lda + h0 * kP, lda, kL, valid, scale, tid, kThreads);
-  load_tile<2, false>(sB, bop + row0 * ldb + g * kN, ldb, kL, valid, NoScale(), tid, kThreads);
+  cp_async_commit();
+  cp_async_wait<0>();
   fence_proxy_async_smem();
   __syncthreads();
 
@@ -102,9 +104,9 @@ ssd_outer_kernel(const bf16* __restrict__ arow, long long lda, const bf16* __res
 // ------------------------------------------------------------------------------------------
 constexpr int kScanSmem = 128 * 2 * 128   /* sR  row operand  [128][2 kblk]            32 KB */
                         + kL * 2 * 128    /* sC  col operand  [256][2 kblk]; later G   64 KB */
-                        + kL * 128        /* sV  X_h / dY_h   [256][1 atom]            32 KB */
-                        + kP * 2 * 128    /* sS  S_prev_h / dS_h [64][2 kblk]          16 KB */
-                        + 2 * kL * 4 + 64 + 1024;
+                        + 2 * kL * 128    /* sV  X_h / dY_h   [256][1 atom]  x2 buffers 64 KB */
+                        + 2 * kP * 2 * 128/* sS  S_prev_h / dS_h [64][2 kblk] x2       32 KB */
+                        + 2 * 2 * kL * 4 + 64 + 1024;
 
 template <bool BWD>
 __global__ void __launch_bounds__(kThreads, 1)
@@ -119,11 +121,10 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
   uint8_t* sR = smem;
   uint8_t* sC = sR + 128 * 2 * 128;
   uint8_t* sG = sC;  // aliases the column operand once CB is in TMEM
-  uint8_t* sV = sC + kL * 2 * 128;
-  uint8_t* sS = sV + kL * 128;
-  float* s_a = reinterpret_cast<float*>(sS + kP * 2 * 128);
-  float* s_dt = s_a + kL;
-  uint64_t* bar = reinterpret_cast<uint64_t*>(s_dt + kL);
+  uint8_t* sV0 = sC + kL * 2 * 128;          // two buffers: the next head's tiles stream in (cp.async)
+  uint8_t* sS0 = sV0 + 2 * kL * 128;         // while the current head is being scaled / multiplied
+  float* s_ad = reinterpret_cast<float*>(sS0 + 2 * kP * 2 * 128);  // [2 buffers][a(256) | dt(256)]
+  uint64_t* bar = reinterpret_cast<uint64_t*>(s_ad + 2 * 2 * kL);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 1);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -152,6 +153,22 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
                       NoScale(), tid, kThreads);
   load_tile<2, false>(sC, colop + (row_base + c0) * ldbc + g * kN, ldbc, ncols, max(0, min(ncols, valid - c0)),
                       NoScale(), tid, kThreads);
+  cp_async_commit();
+  auto prefetch_head = [&](int hh) {
+    const int h = h_first + hh;
+    const int bsel = hh & 1;
+    const size_t sb = ((size_t)bc * H + h) * kL;
+    const uint32_t ad = smem_u32(s_ad + bsel * 2 * kL);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(ad + tid * 4), "l"(av + sb + tid) : "memory");
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(ad + (kL + tid) * 4), "l"(dtv + sb + tid) : "memory");
+    load_tile<1, false>(sV0 + bsel * kL * 128, vsrc + (row_base + c0) * ldv + h * kP, ldv, ncols,
+                        max(0, min(ncols, valid - c0)), NoScale(), tid, kThreads);
+    load_tile<2, false>(sS0 + bsel * kP * 2 * 128, ssrc + ((size_t)bc * H + h) * kP * kN, kN, kP, kP, NoScale(), tid,
+                        kThreads);
+    cp_async_commit();
+  };
+  prefetch_head(0);
+  cp_async_wait<1>();  // row / column operands have landed (head 0's tiles may still be in flight)
   fence_proxy_async_smem();
   __syncthreads();
   if (tid == 0) {
@@ -177,11 +194,12 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
   for (int hh = 0; hh < hgs; ++hh) {
     const int h = h_first + hh;
     const size_t sbase = ((size_t)bc * H + h) * kL;
-    s_a[tid] = av[sbase + tid];
-    s_dt[tid] = dtv[sbase + tid];
-    load_tile<1, false>(sV, vsrc + (row_base + c0) * ldv + h * kP, ldv, ncols, max(0, min(ncols, valid - c0)),
-                        NoScale(), tid, kThreads);
-    load_tile<2, false>(sS, ssrc + ((size_t)bc * H + h) * kP * kN, kN, kP, kP, NoScale(), tid, kThreads);
+    uint8_t* sV = sV0 + (hh & 1) * kL * 128;
+    uint8_t* sS = sS0 + (hh & 1) * kP * 2 * 128;
+    const float* s_a = s_ad + (hh & 1) * 2 * kL;
+    const float* s_dt = s_a + kL;
+    if (hh + 1 < hgs) { prefetch_head(hh + 1); cp_async_wait<1>(); }
+    else cp_async_wait<0>();
     __syncthreads();
 
     // ---- G = CB o decay o mask (o dt_j in FWD) -> bf16 K-major operand ----

@@ -111,7 +111,7 @@ __global__ void ssd_state_passing_bwd_kernel(const float* __restrict__ dstates_d
   }
 }
 
-// Backward finalize.  One block = one (b, c), thread t = token.  For every head:
+// Backward finalize.  One block = one (b, c, head), thread t = token:
 //   rowpart_t = sum_p dY[t,p] * y_ssm[t,p]   (y_ssm = y - D x, stored by forward; d a_t from Y_off and M)
 //   da_t      = rowpart_t - dt_t * (ddt1_t + ddt2_t)  (+ da_last at t = L-1, + sum_s dt_s ddt2_s at L-1)
 //   ddA_t     = suffix-sum_{s >= t} da_s ;  ddt_t = ddt1_t + ddt2_t + A_h * ddA_t
@@ -132,7 +132,8 @@ __global__ void ssd_bwd_finalize_kernel(const bf16* __restrict__ dy, long long l
   const int tok = c * L + t;
   const bool valid = tok < T;
   const size_t row = (size_t)b * T + tok;
-  for (int h = 0; h < H; ++h) {
+  {
+    const int h = blockIdx.y;
     const size_t sidx = ((size_t)(b * nc + c) * H + h) * L + t;
     const float A = -__expf(A_log[h]);
     const float dtv = dt[sidx];
@@ -235,7 +236,7 @@ extern "C" int mb_ssd_bwd_finalize(const void* dy, long long lddy, const void* y
   MB_REQUIRE(L == 64 || L == 128 || L == 256, "ssd_bwd_finalize: chunk size %d not in {64,128,256}", L);
   MB_REQUIRE(P % 8 == 0, "ssd_bwd_finalize: headdim must be a multiple of 8");
   const int nc = cdiv(T, L);
-  ssd_bwd_finalize_kernel<<<B * nc, L, 0, stream>>>((const bf16*)dy, lddy, (const bf16*)y_ssm, ldy,
+  ssd_bwd_finalize_kernel<<<dim3(B * nc, H), L, 0, stream>>>((const bf16*)dy, lddy, (const bf16*)y_ssm, ldy,
                                                     (const bf16*)dt_raw, ld_dt, dt, ddt1, ddt2, da_last, dt_bias,
                                                     A_log, (bf16*)draw_out, ld_draw, dA_log, ddt_bias, T, H, P, L, nc);
   return check_launch("ssd_bwd_finalize");

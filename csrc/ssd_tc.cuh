@@ -25,31 +25,62 @@ struct NoScale {
 };
 
 // Cooperative global -> swizzled smem copy of a [rows x 64*NBLK] bf16 tile (row stride ld).
-// Rows >= valid_rows are zero-filled.  `scale(row, blk)` multiplies every element of that
-// (row, 64-column block); pass NoScale for a plain copy.
+// Rows >= valid_rows are zero-filled.
+//   SCALED = false : cp.async (LDGSTS) 16-byte copies — asynchronous, no register staging, any
+//                    number in flight; the caller must cp_async_wait_all() (or wait_group) before
+//                    the tile is consumed.  Lets the next head's tiles stream in behind the math.
+//   SCALED = true  : `scale(row, blk)` multiplies every element of that (row, 64-column block);
+//                    loads are issued 8 deep per thread before the first is consumed.
+__device__ __forceinline__ void cp_async16(uint32_t saddr, const void* g, bool pred) {
+  const int sz = pred ? 16 : 0;  // src-size 0 => destination is zero-filled
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(saddr), "l"(g), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 template <int NBLK, bool SCALED, class ScaleFn>
 __device__ __forceinline__ void load_tile(uint8_t* sdst, const bf16* __restrict__ g, long long ld, int rows,
                                           int valid_rows, ScaleFn scale, int tid, int nthreads) {
   const int total = rows * NBLK * 8;
-  for (int idx = tid; idx < total; idx += nthreads) {
-    const int c = idx & 7;
-    const int blk = (idx >> 3) % NBLK;
-    const int row = idx / (8 * NBLK);
-    bf16x8 v;
-    if (row < valid_rows) {
-      v = ld8(g + (size_t)row * ld + blk * 64 + c * 8);
-      if (SCALED) {
-        float f[8];
-        unpack8(v, f);
-        const float s = scale(row, blk);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) f[j] *= s;
-        v = pack8(f);
-      }
-    } else {
-      v.v[0] = v.v[1] = v.v[2] = v.v[3] = __floats2bfloat162_rn(0.f, 0.f);
+  if (!SCALED) {
+    const uint32_t sbase = smem_u32(sdst);
+    for (int idx = tid; idx < total; idx += nthreads) {
+      const int c = idx & 7;
+      const int blk = (idx >> 3) % NBLK;
+      const int row = idx / (8 * NBLK);
+      const bool ok = row < valid_rows;
+      const bf16* src = g + (size_t)(ok ? row : 0) * ld + blk * 64 + c * 8;
+      cp_async16(sbase + blk * rows * 128 + row * 128 + ((c ^ (row & 7)) << 4), src, ok);
     }
-    *reinterpret_cast<bf16x8*>(sdst + (size_t)blk * rows * 128 + row * 128 + ((c ^ (row & 7)) << 4)) = v;
+    return;
+  }
+  constexpr int U = 8;
+  for (int base = tid; base < total; base += nthreads * U) {
+    bf16x8 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int idx = base + u * nthreads;
+      const int c = idx & 7;
+      const int blk = (idx >> 3) % NBLK;
+      const int row = idx / (8 * NBLK);
+      if (idx < total && row < valid_rows) v[u] = ld8(g + (size_t)row * ld + blk * 64 + c * 8);
+      else v[u].v[0] = v[u].v[1] = v[u].v[2] = v[u].v[3] = __floats2bfloat162_rn(0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int idx = base + u * nthreads;
+      if (idx >= total) break;
+      const int c = idx & 7;
+      const int blk = (idx >> 3) % NBLK;
+      const int row = idx / (8 * NBLK);
+      float f[8];
+      unpack8(v[u], f);
+      const float sc = row < valid_rows ? scale(row, blk) : 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] *= sc;
+      *reinterpret_cast<bf16x8*>(sdst + (size_t)blk * rows * 128 + row * 128 + ((c ^ (row & 7)) << 4)) = pack8(f);
+    }
   }
 }
 
