@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <string.h>
 
 namespace mb {
 
@@ -69,8 +70,19 @@ __device__ __forceinline__ bf16x8 pack8(const float* f) {
   for (int i = 0; i < 4; ++i) p.v[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
   return p;
 }
-__device__ __forceinline__ bf16x8 ld8(const bf16* p) { return *reinterpret_cast<const bf16x8*>(p); }
-__device__ __forceinline__ void st8(bf16* p, const bf16x8& v) { *reinterpret_cast<bf16x8*>(p) = v; }
+// Forced 128-bit accesses: a plain struct copy of bf16x8 is scalarised by nvcc into four 32-bit
+// LDG/STG (seen in SASS), which quarters the bytes in flight per instruction.
+__device__ __forceinline__ bf16x8 ld8(const bf16* p) {
+  const uint4 t = *reinterpret_cast<const uint4*>(p);
+  bf16x8 r;
+  memcpy(&r, &t, 16);
+  return r;
+}
+__device__ __forceinline__ void st8(bf16* p, const bf16x8& v) {
+  uint4 t;
+  memcpy(&t, &v, 16);
+  *reinterpret_cast<uint4*>(p) = t;
+}
 __device__ __forceinline__ void ld8f(const float* p, float* f) {
   float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
   f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;

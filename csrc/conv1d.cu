@@ -15,7 +15,7 @@ constexpr int kConvThreads = 128;
 constexpr int kConvTile = 64;  // tokens per block
 
 template <int W, bool SILU>
-__global__ void __launch_bounds__(kConvThreads)
+__global__ void __launch_bounds__(kConvThreads, 4)
 conv1d_fwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __restrict__ w,
                   const float* __restrict__ bias, bf16* __restrict__ y, long long ldy, int T, int C) {
   const int c0 = (blockIdx.x * kConvThreads + threadIdx.x) * 8;
@@ -32,40 +32,52 @@ conv1d_fwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __rest
   }
   const bf16* xb = x + ((size_t)b * T) * ldx + c0;
   bf16* yb = y + ((size_t)b * T) * ldy + c0;
-  float win[W][8];  // win[k] = x[t - (W-1) + k]
+  constexpr int U = 8;  // tokens per register batch: U loads in flight, static indexing, no window shifts
+  bf16x8 halo[W - 1];   // x[tb - (W-1) + k], packed
 #pragma unroll
   for (int k = 0; k < W - 1; ++k) {
     const int t = t0 - (W - 1) + k;
-    if (t >= 0) unpack8(ld8(xb + (size_t)t * ldx), win[k + 1]);
-    else {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) win[k + 1][j] = 0.f;
-    }
+    if (t >= 0) halo[k] = ld8(xb + (size_t)t * ldx);
+    else halo[k].v[0] = halo[k].v[1] = halo[k].v[2] = halo[k].v[3] = __floats2bfloat162_rn(0.f, 0.f);
   }
-  constexpr int U = 8;  // tokens loaded ahead per thread (memory-level parallelism)
   for (int tb = t0; tb < t1; tb += U) {
-    bf16x8 raw[U];
+    bf16x8 raw[U + W - 1];
 #pragma unroll
-    for (int u = 0; u < U; ++u)
-      if (tb + u < t1) raw[u] = ld8(xb + (size_t)(tb + u) * ldx);
+    for (int k = 0; k < W - 1; ++k) raw[k] = halo[k];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      const int t = tb + u;
-      if (t >= t1) break;
+      if (tb + u < t1) raw[W - 1 + u] = ld8(xb + (size_t)(tb + u) * ldx);
+      else raw[W - 1 + u] = raw[W - 2 + u];
+    }
 #pragma unroll
-      for (int k = 0; k < W - 1; ++k)
+    for (int k = 0; k < W - 1; ++k) halo[k] = raw[U + k];
+    float acc[U][8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) win[k][j] = win[k + 1][j];
-      unpack8(raw[u], win[W - 1]);
-      float o[8];
+    for (int u = 0; u < U; ++u)
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float a = bs[j];
+      for (int j = 0; j < 8; ++j) acc[u][j] = bs[j];
 #pragma unroll
-        for (int k = 0; k < W; ++k) a += wt[j][k] * win[k][j];
-        o[j] = SILU ? silu_f(a) : a;
+    for (int r = 0; r < U + W - 1; ++r) {  // each input row feeds up to W outputs
+      float xr[8];
+      unpack8(raw[r], xr);
+#pragma unroll
+      for (int k = 0; k < W; ++k) {
+        const int u = r - k;  // out[u] += w[k] * x[u + k]
+        if (u >= 0 && u < U) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[u][j] += wt[j][k] * xr[j];
+        }
       }
-      st8(yb + (size_t)t * ldy, pack8(o));
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (tb + u < t1) {
+        if (SILU) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[u][j] = silu_f(acc[u][j]);
+        }
+        st8(yb + (size_t)(tb + u) * ldy, pack8(acc[u]));
+      }
     }
   }
 }
