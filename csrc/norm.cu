@@ -397,3 +397,68 @@ extern "C" int mb_gated_rmsnorm_bwd(const void* x, int ldx, const void* z, int l
   colsum_partials_kernel<<<cdiv(D, 32), 1024, 0, stream>>>(scratch, dw, grid, D, dw_accumulate);
   return check_launch("gated_rmsnorm_bwd/colsum");
 }
+
+// ------------------------------------------------------------------------------------------
+// mb_add_rmsnorm_bwd_noalloc — the same backward as mb_add_rmsnorm_bwd for callers that cannot
+// hand us a scratch buffer because they cannot allocate one.
+//
+// Who that is: a host that gave the whole device to its own memory pool at start-up and has no
+// spare bytes to carve out later, or a latency-critical loop that must never call cudaMalloc /
+// cudaFree (both synchronise the device) and has no allocator of ours (or torch's) to ask.
+// For them the per-block weight-gradient partials live in a fixed array that is part of this
+// library's image: every GPU that loads libmamba_b200.so holds these 1 MiB until the process
+// exits, whether or not this entry point is ever called.
+//
+// Limits (checked; a violation returns an error and launches nothing):
+//   D % 8 == 0 and D <= kNoAllocMaxD (1024);  M > 0 fits in an int.
+// The partial rows are capped at kNoAllocMaxRows (256) blocks, so large M runs on a smaller grid
+// than the scratch-taking entry point — same result, somewhat lower bandwidth.
+//
+// Sharing: there is ONE array per device.  Every call overwrites the rows it uses (each launched
+// block writes all D columns of its own row and the reduction reads exactly those rows), so
+// nothing needs to start at zero and nothing is cleared; stale rows from an earlier, larger call
+// are never read.  Two calls whose kernels overlap on the same GPU (different streams) race on
+// the array — serialise them.
+//
+// Set-up: `g_noalloc_scratch` below is, in host code, only a handle for the symbol, not a device
+// address.  The first call on each device (with that device current, which is the device `stream`
+// must belong to) resolves the address with cudaGetSymbolAddress and caches it; make that first
+// call outside any stream capture.  No cudaMalloc, cudaFree or allocating library call is made.
+// ------------------------------------------------------------------------------------------
+namespace mb {
+constexpr int kNoAllocMaxD = 1024;
+constexpr int kNoAllocMaxRows = 256;
+static __device__ __align__(256) float g_noalloc_scratch[kNoAllocMaxRows * kNoAllocMaxD];
+static float* g_noalloc_ptr[64] = {nullptr};  // resolved device address of the array, per device
+}  // namespace mb
+
+extern "C" int mb_add_rmsnorm_bwd_noalloc(const float* r, const void* dy, const float* rstd,
+                                          const float* weight, const float* dres_in, float* dres_out,
+                                          void* dx_bf16, float* dw, int dw_accumulate, int M, int D,
+                                          cudaStream_t stream) {
+  MB_REQUIRE(D > 0 && D % 8 == 0 && D <= kNoAllocMaxD,
+             "add_rmsnorm_bwd_noalloc: D=%d outside the built-in scratch limit (multiple of 8, <= %d); "
+             "use mb_add_rmsnorm_bwd with caller scratch", D, kNoAllocMaxD);
+  MB_REQUIRE(M >= 0, "add_rmsnorm_bwd_noalloc: negative M");
+  if (M == 0) return 0;
+  int dev = 0;
+  MB_CUDA(cudaGetDevice(&dev));
+  MB_REQUIRE(dev >= 0 && dev < 64, "add_rmsnorm_bwd_noalloc: device index %d not supported", dev);
+  if (g_noalloc_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    MB_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));  // per device: the current one
+    MB_REQUIRE(p != nullptr, "add_rmsnorm_bwd_noalloc: could not resolve the scratch symbol");
+    g_noalloc_ptr[dev] = static_cast<float*>(p);
+  }
+  float* scratch = g_noalloc_ptr[dev];
+  const int nv = cdiv(D, 256);
+  int grid = cdiv(M, kWarpsPerBlock);
+  if (grid > kNoAllocMaxRows) grid = kNoAllocMaxRows;
+  DISPATCH_NV(nv, {
+    add_rmsnorm_bwd_kernel<NV><<<grid, kWarpsPerBlock * 32, 0, stream>>>(
+        r, (const bf16*)dy, rstd, weight, dres_in, dres_out, (bf16*)dx_bf16, scratch, M, D);
+  });
+  if (check_launch("add_rmsnorm_bwd_noalloc")) return 1;
+  colsum_partials_kernel<<<cdiv(D, 32), 1024, 0, stream>>>(scratch, dw, grid, D, dw_accumulate);
+  return check_launch("add_rmsnorm_bwd_noalloc/colsum");
+}

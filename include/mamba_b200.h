@@ -34,6 +34,17 @@ long long mb_norm_bwd_scratch_bytes(int rows, int D);
 int mb_add_rmsnorm_bwd(const float* r, const void* dy_bf16, const float* rstd, const float* weight,
                        const float* dres_in, float* dres_out, void* dx_bf16, float* dw,
                        int dw_accumulate, float* scratch, int M, int D, cudaStream_t stream);
+/* Same backward, no scratch argument and no allocation of any kind: the weight-gradient partials
+ * go to a 1 MiB array built into the library image (held by every GPU that loads the library).
+ * For hosts that cannot allocate — the device is owned by their own pool, or the call sits in a
+ * loop that may not hit cudaMalloc/cudaFree.  Limits: D % 8 == 0, D <= 1024 (else an error is
+ * returned).  One array per device, shared by all calls: overlapping calls on one GPU race.  The
+ * first call on a device resolves the array's address; issue it outside stream capture.
+ * (No counterpart in the reference: it has no native code and no such entry point.) */
+int mb_add_rmsnorm_bwd_noalloc(const float* r, const void* dy_bf16, const float* rstd,
+                               const float* weight, const float* dres_in, float* dres_out,
+                               void* dx_bf16, float* dw, int dw_accumulate, int M, int D,
+                               cudaStream_t stream);
 
 /* ---- K15: gated RMSNorm  y = rmsnorm(x * silu(z)) * w  (mamba_ssm RMSNormGated) ----------- */
 int mb_gated_rmsnorm_fwd(const void* x, int ldx, const void* z, int ldz, const float* weight,
