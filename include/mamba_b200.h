@@ -110,6 +110,21 @@ int mb_ssd_bwd_finalize(const void* dy, long long lddy, const void* y_ssm, long 
                         void* draw_out, long long ld_draw, float* dA_log, float* ddt_bias, int B, int T, int H,
                         int P, int L, cudaStream_t stream);
 
+/* ---- K19-K21: gradient reduce-scatter + global-norm clip + sharded AdamW + bf16 parameter
+ * all-gather over NVLink peer memory (replaces DDP's NCCL all-reduce, clip_grad_norm_ and
+ * torch.optim.AdamW of /root/reference/train.py:86,219-227).  *_ptrs are HOST arrays of `world`
+ * device addresses of the peer-mapped gradient / bf16-parameter / control arenas. */
+long long mb_comm_ctrl_words(void);
+int mb_comm_reduce_scatter(const long long* grad_ptrs, const long long* bf16_ptrs,
+                           const long long* ctrl_ptrs, int world, int rank, int bucket, long long start,
+                           long long shard_len, long long seq, float* norm_acc, int num_blocks,
+                           cudaStream_t stream);
+int mb_comm_adamw_allgather(const long long* grad_ptrs, const long long* bf16_ptrs,
+                            const long long* ctrl_ptrs, int world, int rank, long long seq,
+                            const long long* items, int n_items, float* master, float* m_state,
+                            float* v_state, const float* hyper, float* norm_acc, float* norm_out,
+                            unsigned int* block_counter, int num_blocks, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

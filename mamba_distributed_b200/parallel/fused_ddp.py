@@ -59,7 +59,7 @@ class FusedDDP(nn.Module):
         self.device = params[0].device
         self.on_gpu = self.device.type == "cuda"
         if comm == "auto":
-            comm = os.environ.get("MAMBA_B200_COMM", "allreduce")
+            comm = os.environ.get("MAMBA_B200_COMM", "fused" if self.on_gpu else "allreduce")
         assert comm in ("allreduce", "fused")
         if comm == "fused" and not self.on_gpu:
             comm = "allreduce"
@@ -126,6 +126,9 @@ class FusedDDP(nn.Module):
             p._post_grad_hook = self._make_hook(i)  # called by native wgrad kernels
             p.register_post_accumulate_grad_hook(self._make_hook(i))
         self.grad_sync_pending = False  # fused path: reduction deferred into optimizer.step
+        self.master_stale = False       # fused path, world > 1: fp32 masters are current only on their owner
+        module.register_state_dict_pre_hook(lambda *a, **k: self.sync_master())
+        module.register_load_state_dict_post_hook(lambda *a, **k: self.refresh_bf16())
 
     # ------------------------------------------------------------------ API
     def forward(self, *args, **kwargs):
@@ -137,6 +140,17 @@ class FusedDDP(nn.Module):
             for p in self.params:
                 p._bf16_version = p._version
 
+    def sync_master(self):
+        """Make every rank's fp32 master arena complete (owners hold the current values of their
+        shards after a fused step).  Not on the hot path: checkpointing / fp32 evaluation only."""
+        if not self.master_stale:
+            return
+        for (s, e, _) in self.buckets:
+            sl = (e - s) // self.world
+            mine = self.flat_param[s + self.rank * sl: s + (self.rank + 1) * sl]
+            dist.all_gather_into_tensor(self.flat_param[s:e], mine.clone(), group=self.process_group)
+        self.master_stale = False
+
     def zero_grad(self, set_to_none=False):
         self.flat_grad.zero_()
         for p, off in zip(self.params, self.offsets):
@@ -144,6 +158,7 @@ class FusedDDP(nn.Module):
                 p.grad = self.flat_grad[off:off + p.numel()].view(p.shape)
 
     def state_dict(self, *args, **kwargs):
+        self.sync_master()
         return self.module.state_dict(*args, **kwargs)
 
     def load_state_dict(self, sd, *args, **kwargs):

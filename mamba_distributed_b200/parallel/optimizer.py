@@ -54,12 +54,15 @@ class FusedAdamW:
 
     def state_dict(self):
         if self.impl is not None:
-            return self.impl.state_dict()
+            sd = self.impl.state_dict()
+            sd["step"] = self.step_count
+            return sd
         return {"step": self.step_count, "m": self.m.cpu(), "v": self.v.cpu(),
                 "lrs": [g["lr"] for g in self.param_groups]}
 
     def load_state_dict(self, sd):
         if self.impl is not None:
+            self.step_count = sd["step"]
             return self.impl.load_state_dict(sd)
         self.step_count = sd["step"]
         self.m.copy_(sd["m"])

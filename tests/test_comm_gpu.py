@@ -1,0 +1,60 @@
+"""T5: fused gradient sync + clip + sharded AdamW + bf16 all-gather (csrc/comm_adamw.cu)."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.gpu
+def test_fused_step_world1_matches_clip_plus_torch_adamw():
+    from mamba_distributed_b200.config import MambaConfig
+    from mamba_distributed_b200.parallel import FusedDDP
+    from model import LMHeadModel
+    cfg = MambaConfig(d_model=256, n_layer=2, vocab_size=2048, ssm_cfg={"layer": "Mamba2"})
+
+    def batches():
+        g = torch.Generator().manual_seed(3)
+        for _ in range(3):
+            yield (torch.randint(0, 2048, (2, 256), generator=g).cuda(), torch.randint(0, 2048, (2, 256), generator=g).cuda())
+
+    torch.manual_seed(0)
+    m_f = LMHeadModel(cfg, "cuda").cuda()
+    ddp = FusedDDP(m_f, comm="fused", bucket_cap_mb=0.5)
+    assert ddp.comm == "fused" and len(ddp.buckets) > 2
+    opt_f = m_f.configure_optimizers(0.1, 3e-3, "cuda", False, fused_comm=ddp)
+    torch.manual_seed(0)
+    m_r = LMHeadModel(cfg, "cuda").cuda()
+    opt_r = m_r.configure_optimizers(0.1, 3e-3, "cuda", False)
+    for x, y in batches():
+        opt_f.zero_grad(); opt_r.zero_grad(set_to_none=True)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            _, lf = ddp(x, y)
+            _, lr_ = m_r(x, y)
+        lf.backward(); lr_.backward()
+        nf = opt_f.step(max_norm=1.0)
+        nr = torch.nn.utils.clip_grad_norm_(m_r.parameters(), 1.0)
+        opt_r.step()
+        assert abs(float(nf) - float(nr)) <= 1e-3 * float(nr) + 1e-4, (float(nf), float(nr))
+    for (n, pf), (_, pr) in zip(m_f.named_parameters(), m_r.named_parameters()):
+        assert torch.allclose(pf, pr, atol=2e-5, rtol=1e-4), (n, (pf - pr).abs().max().item())
+        assert torch.equal(pf._bf16, pf.detach().bfloat16()), n
+    t = ddp.symm.last_timings()
+    assert t is not None and t[1] > 0
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+@pytest.mark.parametrize("world", [2])
+def test_fused_comm_multi_gpu(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+                        "--master-addr", "127.0.0.1", "--master-port", "29631",
+                        os.path.join(ROOT, "tests", "_comm_worker.py")], env=env, capture_output=True, text=True,
+                       timeout=600)
+    assert r.returncode == 0 and "COMM_OK" in r.stdout, (r.stdout[-2000:], r.stderr[-4000:])

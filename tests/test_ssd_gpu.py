@@ -50,17 +50,28 @@ def test_ssd_backward_all_grads(B, T, H, G):
     grads_ref = torch.autograd.grad(y_ref, rl, dy.float())
     names = ["dx", "ddt", "dA", "dB", "dC", "dD", "ddt_bias"]
     errs = {n: _rel(g, gr) for n, g, gr in zip(names, grads, grads_ref)}
-    # Per-token / per-element gradients: tight.  dA and ddt_bias are per-head sums over every token
-    # of d(dt*A) = suffix-sum(row-sums - column-sums of dM o M): the two halves cancel, so the
-    # 0.2 % bf16 rounding of the operands is amplified.  They are checked against the scale of the
-    # terms being summed (sum |per-token contribution|) instead of the cancelled result.
     tight = {n: e for n, e in errs.items() if n in ("dx", "dB", "dC", "dD")}
     assert all(e < 1e-2 for e in tight.values()), errs
     assert errs["ddt"] < 5e-2, errs
-    ddt_scale = grads_ref[1].abs().sum(dim=(0, 1))                       # [H]
-    assert ((grads[6].float() - grads_ref[6]).abs() <= 2e-2 * ddt_scale + 1e-3).all(), (grads[6], grads_ref[6])
-    dA_err = (grads[2].float() - grads_ref[2]).abs()
-    assert (dA_err <= 5e-2 * grads_ref[2].abs().max() + 2e-2 * grads_ref[2].abs()).all(), (grads[2], grads_ref[2])
+
+
+@pytest.mark.parametrize("B,T,H,G", [(2, 512, 4, 1), (1, 1024, 24, 1)])
+def test_ssd_backward_head_reductions(B, T, H, G):
+    """dA and d(dt_bias) are per-head sums over every token of d(dt*A) = suffix-sum(row-sums minus
+    column-sums of dM o M).  With a random upstream gradient the result is a heavily cancelled sum
+    and the 0.2 % bf16 rounding of the MMA operands dominates it; a gradient correlated with y
+    (as a real loss gradient is) gives a well-conditioned sum that pins the kernels' arithmetic."""
+    from mamba_distributed_b200.ops import ssd_native
+    x, dt, A, Bm, Cm, D, dt_bias = _mk(B, T, H, G, seed=2)
+    rl = [t.detach().float().requires_grad_(True) for t in (x, dt, A, Bm, Cm, D, dt_bias)]
+    y_ref = ref.ssd_chunked_ref(rl[0], rl[1], rl[2], rl[3], rl[4], 256, rl[5], None, rl[6], True)
+    dy = (y_ref.detach() - D.view(1, 1, H, 1) * x.float()).bfloat16()   # correlated with the SSM part of y
+    grads_ref = torch.autograd.grad(y_ref, rl, dy.float())
+    leaves = [t.clone().requires_grad_(True) for t in (x, dt, A, Bm, Cm, D, dt_bias)]
+    y = ssd_native.ssd_combined(*leaves[:5], 256, leaves[5], None, leaves[6], True)
+    grads = torch.autograd.grad(y, leaves, dy)
+    for i, n in ((2, "dA"), (6, "ddt_bias"), (1, "ddt")):
+        assert _rel(grads[i], grads_ref[i]) < 4e-2, (n, _rel(grads[i], grads_ref[i]), grads[i].flatten()[:6], grads_ref[i].flatten()[:6])
 
 
 def test_mamba2_mixer_and_model_match_torch_path():
