@@ -41,21 +41,18 @@ def _get_scratch(dev, nbytes):
 # parameters: bf16 compute copies and direct gradient accumulation
 # ------------------------------------------------------------------------------------------
 def bf16_weight(p: torch.Tensor) -> torch.Tensor:
+    """bf16 compute copy of a parameter.  Under ``FusedDDP`` it is the arena view the optimizer
+    kernel keeps current; otherwise a fresh cast per forward (no caching: torch's fused optimizers
+    update parameters without bumping ``_version``, so a cache cannot be invalidated reliably).
+    Autograd nodes keep the copy they used for their backward."""
     w = getattr(p, "_bf16", None)
     if w is not None:
         return w
     if p.dtype == torch.bfloat16:
         return p.detach()
-    cache = getattr(p, "_bf16_cache", None)
-    if cache is not None and cache[0] == p._version and cache[1].device == p.device:
-        return cache[1]
     w = torch.empty(p.shape, dtype=torch.bfloat16, device=p.device)
     src = p.detach().contiguous()
     call("mb_cast_f32_bf16", src, w, src.numel())
-    try:
-        p._bf16_cache = (p._version, w)
-    except Exception:
-        pass
     return w
 
 
@@ -138,7 +135,7 @@ class LinearFn(torch.autograd.Function):
             x2 = x2.contiguous()
         w = bf16_weight(weight)
         y = gemm_nt(x2, w, bias=bias.float() if bias is not None else None)
-        ctx.save_for_backward(x2, weight, bias)
+        ctx.save_for_backward(x2, weight, bias, w)
         ctx.notify = notify
         ctx.xshape = x.shape
         ctx.xdtype = x.dtype
@@ -146,13 +143,13 @@ class LinearFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy):
-        x2, weight, bias = ctx.saved_tensors
+        x2, weight, bias, w = ctx.saved_tensors
         dy2 = _rows(dy)
         if dy2.dtype != torch.bfloat16 or dy2.stride(1) != 1 or dy2.stride(0) % 8 != 0:
             dy2 = dy2.to(torch.bfloat16).contiguous()
         dx = None
         if ctx.needs_input_grad[0]:
-            dx = gemm_nn(dy2, bf16_weight(weight)).view(ctx.xshape).to(ctx.xdtype)
+            dx = gemm_nn(dy2, w).view(ctx.xshape).to(ctx.xdtype)
         if weight.requires_grad:
             gemm_tn_acc(dy2, x2, grad_buffer(weight))
             if ctx.notify:
@@ -384,7 +381,8 @@ class Mamba2MixerFn(torch.autograd.Function):
         if u2.dtype != torch.bfloat16:
             u2 = u2.to(torch.bfloat16)
         u2 = u2.contiguous()
-        zxbcdt = gemm_nt(u2, bf16_weight(in_w))                       # [M, d_in_proj]
+        w_in, w_out = bf16_weight(in_w), bf16_weight(out_w)
+        zxbcdt = gemm_nt(u2, w_in)                                    # [M, d_in_proj]
         cw = conv_w.reshape(conv_dim, -1).float().contiguous()
         cb = conv_b.float().contiguous() if conv_b is not None else None
         xBC = torch.empty(M, conv_dim, dtype=torch.bfloat16, device=u.device)
@@ -394,9 +392,9 @@ class Mamba2MixerFn(torch.autograd.Function):
         y, ssd_saved = ssd_native.ssd_fwd(xBC, zxbcdt, Bsz, T, cfg, dt_bias, A_log, D)
         z = zxbcdt[:, :d_in]
         yn, rstd = k_gated_rmsnorm_fwd(y, z, norm_w.float(), cfg["eps"], d_in // G)
-        out = gemm_nt(yn, bf16_weight(out_w))
+        out = gemm_nt(yn, w_out)
         ctx.save_for_backward(u2, zxbcdt, xBC, y, yn, rstd, in_w, conv_w, conv_b, dt_bias, A_log, D, norm_w, out_w,
-                              cw, cb, *ssd_saved)
+                              cw, cb, w_in, w_out, *ssd_saved)
         ctx.cfg, ctx.dims = cfg, (Bsz, T, dm)
         ctx.udtype = u.dtype
         return out.view(Bsz, T, dm)
@@ -404,7 +402,7 @@ class Mamba2MixerFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dout):
         (u2, zxbcdt, xBC, y, yn, rstd, in_w, conv_w, conv_b, dt_bias, A_log, D, norm_w, out_w, cw, cb,
-         *ssd_saved) = ctx.saved_tensors
+         w_in, w_out, *ssd_saved) = ctx.saved_tensors
         cfg = ctx.cfg
         Bsz, T, dm = ctx.dims
         M = Bsz * T
@@ -414,7 +412,7 @@ class Mamba2MixerFn(torch.autograd.Function):
         if dout2.dtype != torch.bfloat16 or not dout2.is_contiguous():
             dout2 = dout2.to(torch.bfloat16).contiguous()
         # out_proj
-        dyn = gemm_nn(dout2, bf16_weight(out_w))
+        dyn = gemm_nn(dout2, w_out)
         gemm_tn_acc(dout2, yn, grad_buffer(out_w))
         notify_grad_ready(out_w)
         # gated norm: dy (SSD output grad) and dz (written into the z columns of d(zxbcdt))
@@ -431,7 +429,7 @@ class Mamba2MixerFn(torch.autograd.Function):
         k_conv1d_bwd(zxbcdt.view(Bsz, T, -1)[:, :, d_in:d_in + conv_dim], cw, cb, dxBC.view(Bsz, T, conv_dim),
                      dzxbcdt.view(Bsz, T, -1)[:, :, d_in:d_in + conv_dim], dcw, dcb, True)
         # in_proj
-        du = gemm_nn(dzxbcdt, bf16_weight(in_w)).view(Bsz, T, dm)
+        du = gemm_nn(dzxbcdt, w_in).view(Bsz, T, dm)
         gemm_tn_acc(dzxbcdt, u2, grad_buffer(in_w))
         notify_grad_ready(in_w)
         return (du.to(ctx.udtype), None, dcw.view(conv_w.shape).to(conv_w.dtype),
