@@ -79,6 +79,7 @@ struct PeerTable {
   float* grad[kMaxWorld];
   bf16* pbf16[kMaxWorld];
   unsigned long long* ctrl[kMaxWorld];
+  float* master[kMaxWorld];  // fp32 master arenas (phase B only)
 };
 
 // ------------------------------------------------------------------------------------------ A
@@ -132,8 +133,7 @@ struct AdamArgs {
 
 __global__ void __launch_bounds__(kCommThreads)
 comm_adamw_allgather_kernel(PeerTable peers, int world, int rank, unsigned long long seq,
-                            const long long* __restrict__ items, int n_items, float* __restrict__ master,
-                            float* __restrict__ m_state, float* __restrict__ v_state, AdamArgs a,
+                            const long long* __restrict__ items, int n_items, float* __restrict__ m_state, float* __restrict__ v_state, AdamArgs a,
                             float* __restrict__ norm_acc, float* __restrict__ norm_out,
                             unsigned int* __restrict__ block_counter) {
   __shared__ float s_clip;
@@ -164,12 +164,16 @@ comm_adamw_allgather_kernel(PeerTable peers, int world, int rank, unsigned long 
   const float clip = s_clip;
   const float inv_bc1 = 1.f / a.bc1, inv_sqrt_bc2 = rsqrtf(a.bc2);
   float* grad = peers.grad[rank];
+  float* master = peers.master[rank];
 
   for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
     const long long arena_off = items[4 * it + 0];
     const long long local_off = items[4 * it + 1];
     const int count = (int)items[4 * it + 2];
-    const int grp = (int)items[4 * it + 3];
+    const int grp = (int)(items[4 * it + 3] & 0xff);
+    // parameters that kernels consume in fp32 (norm weights, conv, A_log, dt_bias, D, embedding):
+    // the owner also stores the fp32 master into every peer's master arena
+    const bool gather_fp32 = ((items[4 * it + 3] >> 8) & 1) != 0 && world > 1;
     const float lr = a.lr[grp], wd = a.wd[grp];
     const float decay = 1.f - lr * wd;
     for (int i = tid * 4; i < count; i += kCommThreads * 4) {
@@ -196,6 +200,10 @@ comm_adamw_allgather_kernel(PeerTable peers, int world, int rank, unsigned long 
       packed.y = *reinterpret_cast<const unsigned int*>(&hi);
       for (int q = 0; q < world; ++q)  // all-gather: the owner stores its shard into every rank's arena
         *reinterpret_cast<uint2*>(peers.pbf16[q] + arena_off + i) = packed;
+      if (gather_fp32) {
+        for (int q = 0; q < world; ++q)
+          if (q != rank) *reinterpret_cast<float4*>(peers.master[q] + arena_off + i) = make_float4(p[0], p[1], p[2], p[3]);
+      }
     }
   }
 
@@ -223,13 +231,14 @@ comm_adamw_allgather_kernel(PeerTable peers, int world, int rank, unsigned long 
 using namespace mb;
 
 static int fill_peers(PeerTable& t, const long long* grad_ptrs, const long long* bf16_ptrs, const long long* ctrl_ptrs,
-                      int world) {
+                      const long long* master_ptrs, int world) {
   MB_REQUIRE(world >= 1 && world <= kMaxWorld, "comm: world size %d not in [1, %d]", world, kMaxWorld);
   for (int i = 0; i < kMaxWorld; ++i) {
     const int j = i < world ? i : 0;
     t.grad[i] = reinterpret_cast<float*>(grad_ptrs[j]);
     t.pbf16[i] = reinterpret_cast<bf16*>(bf16_ptrs[j]);
     t.ctrl[i] = reinterpret_cast<unsigned long long*>(ctrl_ptrs[j]);
+    t.master[i] = master_ptrs != nullptr ? reinterpret_cast<float*>(master_ptrs[j]) : nullptr;
   }
   return 0;
 }
@@ -242,7 +251,7 @@ extern "C" int mb_comm_reduce_scatter(const long long* grad_ptrs, const long lon
                                       long long start, long long shard_len, long long seq, float* norm_acc,
                                       int num_blocks, cudaStream_t stream) {
   PeerTable t;
-  if (fill_peers(t, grad_ptrs, bf16_ptrs, ctrl_ptrs, world)) return 1;
+  if (fill_peers(t, grad_ptrs, bf16_ptrs, ctrl_ptrs, nullptr, world)) return 1;
   MB_REQUIRE(bucket >= 0 && bucket < kMaxBuckets, "comm: bucket index %d >= %d", bucket, kMaxBuckets);
   MB_REQUIRE(shard_len % 4 == 0 && start % 4 == 0, "comm: shard must be 16-byte aligned");
   if (num_blocks <= 0) num_blocks = 32;
@@ -251,21 +260,22 @@ extern "C" int mb_comm_reduce_scatter(const long long* grad_ptrs, const long lon
   return check_launch("comm_reduce_scatter");
 }
 
-// items: device int64 [n_items][4] = {arena offset, optimizer-state offset, count (multiple of 4), group}
+// items: device int64 [n_items][4] = {arena offset, optimizer-state offset, count (multiple of 4),
+//        group | (fp32_gather << 8)};  master_ptrs: HOST array of the peer-mapped fp32 master arenas
 // hyper: host float[14] = lr[4], wd[4], beta1, beta2, eps, bias_correction1, bias_correction2, max_norm
 extern "C" int mb_comm_adamw_allgather(const long long* grad_ptrs, const long long* bf16_ptrs,
-                                       const long long* ctrl_ptrs, int world, int rank, long long seq,
-                                       const long long* items, int n_items, float* master, float* m_state,
+                                       const long long* ctrl_ptrs, const long long* master_ptrs, int world,
+                                       int rank, long long seq, const long long* items, int n_items, float* m_state,
                                        float* v_state, const float* hyper, float* norm_acc, float* norm_out,
                                        unsigned int* block_counter, int num_blocks, cudaStream_t stream) {
   PeerTable t;
-  if (fill_peers(t, grad_ptrs, bf16_ptrs, ctrl_ptrs, world)) return 1;
+  if (fill_peers(t, grad_ptrs, bf16_ptrs, ctrl_ptrs, master_ptrs, world)) return 1;
   AdamArgs a;
   for (int i = 0; i < 4; ++i) { a.lr[i] = hyper[i]; a.wd[i] = hyper[4 + i]; }
   a.beta1 = hyper[8]; a.beta2 = hyper[9]; a.eps = hyper[10]; a.bc1 = hyper[11]; a.bc2 = hyper[12]; a.max_norm = hyper[13];
   if (num_blocks <= 0) num_blocks = 2 * num_sms();
   comm_adamw_allgather_kernel<<<num_blocks, kCommThreads, 0, stream>>>(t, world, rank, (unsigned long long)seq, items,
-                                                                       n_items, master, m_state, v_state, a, norm_acc,
+                                                                       n_items, m_state, v_state, a, norm_acc,
                                                                        norm_out, block_counter);
   return check_launch("comm_adamw_allgather");
 }

@@ -120,8 +120,8 @@ int mb_comm_reduce_scatter(const long long* grad_ptrs, const long long* bf16_ptr
                            long long shard_len, long long seq, float* norm_acc, int num_blocks,
                            cudaStream_t stream);
 int mb_comm_adamw_allgather(const long long* grad_ptrs, const long long* bf16_ptrs,
-                            const long long* ctrl_ptrs, int world, int rank, long long seq,
-                            const long long* items, int n_items, float* master, float* m_state,
+                            const long long* ctrl_ptrs, const long long* master_ptrs, int world, int rank,
+                            long long seq, const long long* items, int n_items, float* m_state,
                             float* v_state, const float* hyper, float* norm_acc, float* norm_out,
                             unsigned int* block_counter, int num_blocks, cudaStream_t stream);
 

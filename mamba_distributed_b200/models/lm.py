@@ -143,6 +143,7 @@ class MambaLMHeadModel(nn.Module):
             self.lm_head.weight = self.backbone.embedding.weight
             # the tied tensor's gradient is final only after the embedding backward (K18)
             self.lm_head.weight._tied_embedding = True
+            self.lm_head.weight._grad_contributions = 2  # lm_head node + embedding node
 
     def allocate_inference_cache(self, batch_size, max_seqlen, dtype=None, **kwargs):
         return self.backbone.allocate_inference_cache(batch_size, max_seqlen, dtype=dtype, **kwargs)

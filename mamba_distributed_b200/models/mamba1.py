@@ -59,6 +59,10 @@ class Mamba(nn.Module):
         self.D = nn.Parameter(torch.ones(self.d_inner, device=device))
         self.D._no_weight_decay = True
         self.out_proj = nn.Linear(self.d_inner, d_model, bias=bias, **fk)
+        # GEMM weights are consumed only through their bf16 copy on the sm_100a path (FusedAdamW
+        # then all-gathers just the bf16 values; every other tensor also gets its fp32 master)
+        for lin in (self.in_proj, self.x_proj, self.out_proj):
+            lin.weight._bf16_only = True
 
     def forward(self, hidden_states, inference_params=None):
         batch, T, _ = hidden_states.shape

@@ -74,6 +74,10 @@ class Mamba2(nn.Module):
             self.norm = RMSNormGated(self.d_ssm, eps=1e-5, norm_before_gate=norm_before_gate,
                                      group_size=self.d_ssm // ngroups, **fk)
         self.out_proj = nn.Linear(self.d_inner, d_model, bias=bias, **fk)
+        # GEMM weights are consumed only through their bf16 copy on the sm_100a path (FusedAdamW
+        # then all-gathers just the bf16 values; every other tensor also gets its fp32 master)
+        for lin in (self.in_proj, self.out_proj):
+            lin.weight._bf16_only = True
 
     # ------------------------------------------------------------------ forward
     def forward(self, u, seqlen=None, seq_idx=None, cu_seqlens=None, inference_params=None):

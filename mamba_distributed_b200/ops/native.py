@@ -10,7 +10,8 @@ Data-flow conventions (B200-first):
     ``FusedDDP`` / ``FusedAdamW`` maintain one, else a cached cast);
   * weight gradients of the big GEMMs are accumulated by the wgrad kernel's epilogue straight
     into ``p.grad`` (fp32, the flat gradient arena under ``FusedDDP``); autograd sees ``None``
-    for them and ``p._post_grad_hook`` tells the DDP wrapper the gradient is final.
+    for them; the parameter's post-accumulate-grad hook (which autograd still runs for that node)
+    tells the DDP wrapper the gradient is final.
 """
 from __future__ import annotations
 
@@ -63,9 +64,10 @@ def grad_buffer(p: torch.Tensor) -> torch.Tensor:
 
 
 def notify_grad_ready(p: torch.Tensor):
-    hook = getattr(p, "_post_grad_hook", None)
-    if hook is not None:
-        hook()
+    """Nothing to do: autograd runs the parameter's post-accumulate-grad hooks right after the
+    node that called us returns (even though we return ``None`` for the weight), which is when the
+    wgrad kernel has been enqueued.  ``FusedDDP`` listens there."""
+    return None
 
 
 # ------------------------------------------------------------------------------------------

@@ -94,11 +94,13 @@ class FusedDDP(nn.Module):
             self.symm = SymmetricArena(self.total, self.device, process_group)
             self.flat_grad = self.symm.grad
             self.flat_bf16 = self.symm.bf16
+            self.flat_param = self.symm.master
         else:
             self.flat_grad = torch.zeros(self.total, dtype=torch.float32, device=self.device)
             self.flat_bf16 = (torch.zeros(self.total, dtype=torch.bfloat16, device=self.device)
                               if self.on_gpu else None)
-        self.flat_param = torch.zeros(self.total, dtype=torch.float32, device=self.device)
+        if self.symm is None:
+            self.flat_param = torch.zeros(self.total, dtype=torch.float32, device=self.device)
         with torch.no_grad():
             for p, off in zip(self.params, self.offsets):
                 n = p.numel()
@@ -117,13 +119,17 @@ class FusedDDP(nn.Module):
             self.refresh_bf16()
 
         # ---- gradient-ready tracking
+        # autograd runs a parameter's post-accumulate hook once per autograd node that used it,
+        # after that node's backward returned — also when the node accumulated the gradient itself
+        # (our wgrad kernels write into the arena and return None).  A tied weight is used by two
+        # nodes (lm_head, embedding): ``_grad_contributions = 2`` (set by ``tie_weights``).
         self._pending = [0] * len(buckets)
-        self._bucket_need = [len(idxs) for (_, _, idxs) in buckets]
+        self._bucket_need = [sum(int(getattr(self.params[i], "_grad_contributions", 1)) for i in idxs)
+                             for (_, _, idxs) in buckets]
         self._works = []
+        self._launched = set()
         self._callback_queued = False
-        self._synced_this_backward = False
         for i, p in enumerate(self.params):
-            p._post_grad_hook = self._make_hook(i)  # called by native wgrad kernels
             p.register_post_accumulate_grad_hook(self._make_hook(i))
         self.grad_sync_pending = False  # fused path: reduction deferred into optimizer.step
         self.master_stale = False       # fused path, world > 1: fp32 masters are current only on their owner
@@ -181,6 +187,9 @@ class FusedDDP(nn.Module):
         return hook
 
     def _launch_bucket(self, b):
+        if b in self._launched:
+            return
+        self._launched.add(b)
         s, e, _ = self.buckets[b]
         if self.comm == "allreduce":
             if self.world > 1:
@@ -193,9 +202,9 @@ class FusedDDP(nn.Module):
     def _finalize(self):
         # safety net: any bucket whose hooks did not all fire (unused params) is reduced now
         for b in range(len(self.buckets)):
-            if self._pending[b] != self._bucket_need[b]:
-                self._launch_bucket(b)
+            self._launch_bucket(b)  # no-op for buckets already launched from a hook
             self._pending[b] = 0
+        self._launched.clear()
         if self.comm == "allreduce":
             for w, s, e in self._works:
                 w.wait()

@@ -26,20 +26,29 @@ class FusedAdamW:
         self.param_groups = [dict(g, lr=lr) for g in param_groups]
         self.step_count = 0
         # per-element weight decay expressed as merged arena segments
-        wd_of = {}
-        for g in self.param_groups:
+        group_of = {}
+        for gi, g in enumerate(self.param_groups):
             for p in g["params"]:
-                wd_of[id(p)] = (g["weight_decay"], g)
+                group_of[id(p)] = gi
         segs = []
+        # finer segmentation for the fused path: which tensors kernels read in fp32 (everything not
+        # marked ``_bf16_only`` by its module) and therefore need their fp32 master on every rank
+        segs_fp32 = []
         for p, off in zip(ddp.params, ddp.offsets):
-            wd, g = wd_of[id(p)]
-            gi = self.param_groups.index(g)
+            gi = group_of[id(p)]
+            fg = not getattr(p, "_bf16_only", False)
+            e2 = off + (p.numel() + 15) // 16 * 16
+            if segs_fp32 and segs_fp32[-1][2] == gi and segs_fp32[-1][3] == fg and segs_fp32[-1][1] == off:
+                segs_fp32[-1] = (segs_fp32[-1][0], e2, gi, fg)
+            else:
+                segs_fp32.append((off, e2, gi, fg))
             end = off + (p.numel() + 15) // 16 * 16
             if segs and segs[-1][2] == gi and segs[-1][1] == off:
                 segs[-1] = (segs[-1][0], end, gi)
             else:
                 segs.append((off, end, gi))
         self.segments = segs  # (start, end, group index)
+        self.segments_fp32 = segs_fp32  # (start, end, group index, fp32 master needed on every rank)
         dev = ddp.device
         if ddp.comm == "fused":
             self.impl = ddp.symm.make_optimizer(self)

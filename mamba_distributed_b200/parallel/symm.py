@@ -41,22 +41,27 @@ class SymmetricArena:
             self.grad = symm_mem.empty(total, dtype=torch.float32, device=self.device)
             self.bf16 = symm_mem.empty(total, dtype=torch.bfloat16, device=self.device)
             self.ctrl = symm_mem.empty(n_ctrl, dtype=torch.int64, device=self.device)
-            self.grad.zero_(); self.bf16.zero_(); self.ctrl.zero_()
+            self.master = symm_mem.empty(total, dtype=torch.float32, device=self.device)
+            self.grad.zero_(); self.bf16.zero_(); self.ctrl.zero_(); self.master.zero_()
             torch.cuda.synchronize(self.device)
             hg = symm_mem.rendezvous(self.grad, self.group)
             hb = symm_mem.rendezvous(self.bf16, self.group)
             hc = symm_mem.rendezvous(self.ctrl, self.group)
-            self._handles = (hg, hb, hc)
+            hm = symm_mem.rendezvous(self.master, self.group)
+            self._handles = (hg, hb, hc, hm)
             gp, bp, cp = list(hg.buffer_ptrs), list(hb.buffer_ptrs), list(hc.buffer_ptrs)
+            mp = list(hm.buffer_ptrs)
             self.multicast_ptr = int(getattr(hg, "multicast_ptr", 0) or 0)
             dist.barrier(self.group)
         else:
             self.grad = torch.zeros(total, dtype=torch.float32, device=self.device)
             self.bf16 = torch.zeros(total, dtype=torch.bfloat16, device=self.device)
             self.ctrl = torch.zeros(n_ctrl, dtype=torch.int64, device=self.device)
+            self.master = torch.zeros(total, dtype=torch.float32, device=self.device)
             gp, bp, cp = [self.grad.data_ptr()], [self.bf16.data_ptr()], [self.ctrl.data_ptr()]
+            mp = [self.master.data_ptr()]
             self.multicast_ptr = 0
-        self._gp, self._bp, self._cp = _ptr_array(gp), _ptr_array(bp), _ptr_array(cp)
+        self._gp, self._bp, self._cp, self._mp = _ptr_array(gp), _ptr_array(bp), _ptr_array(cp), _ptr_array(mp)
         self.norm_acc = torch.zeros(1, dtype=torch.float32, device=self.device)
         self.norm_out = torch.zeros(1, dtype=torch.float32, device=self.device)
         self.block_counter = torch.zeros(1, dtype=torch.int32, device=self.device)
@@ -108,11 +113,11 @@ class _ShardedAdamW:
             sl = (e - s) // world
             lo, hi = s + rank * sl, s + (rank + 1) * sl
             self.shards.append((lo, hi, local_base))
-            for (a0, a1, gi) in opt.segments:
+            for (a0, a1, gi, fp32_gather) in opt.segments_fp32:
                 x0, x1 = max(a0, lo), min(a1, hi)
                 while x0 < x1:
                     n = min(ITEM_CHUNK, x1 - x0)
-                    items.append((x0, local_base + (x0 - lo), n, gi))
+                    items.append((x0, local_base + (x0 - lo), n, gi | (int(fp32_gather) << 8)))
                     x0 += n
             local_base += sl
         assert all(it[2] % 4 == 0 and it[0] % 4 == 0 and it[1] % 4 == 0 for it in items)
@@ -144,8 +149,8 @@ class _ShardedAdamW:
         h[11], h[12] = 1.0 - b1 ** t, 1.0 - b2 ** t
         h[13] = float(max_norm) if max_norm is not None else 0.0
         call("mb_comm_adamw_allgather", ctypes.addressof(arena._gp), ctypes.addressof(arena._bp),
-             ctypes.addressof(arena._cp), arena.world, arena.rank, arena.seq, self.items, self.n_items,
-             ddp.flat_param, self.m, self.v, ctypes.addressof(h), arena.norm_acc, arena.norm_out,
+             ctypes.addressof(arena._cp), ctypes.addressof(arena._mp), arena.world, arena.rank, arena.seq,
+             self.items, self.n_items, self.m, self.v, ctypes.addressof(h), arena.norm_acc, arena.norm_out,
              arena.block_counter, 0, arena.comm_stream.cuda_stream)
         arena.ev_opt_end.record(arena.comm_stream)
         cur.wait_stream(arena.comm_stream)

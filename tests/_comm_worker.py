@@ -22,7 +22,7 @@ def run(comm, rank, world, straggle=False):
     ddp = FusedDDP(model, comm=comm, bucket_cap_mb=0.5)
     opt = model.configure_optimizers(0.1, 3e-3, "cuda", False, fused_comm=ddp)
     g = torch.Generator().manual_seed(7)
-    norms, losses = [], []
+    norms, losses, snaps = [], [], []
     for step in range(3):
         opt.zero_grad()
         for micro in range(2):
@@ -36,25 +36,78 @@ def run(comm, rank, world, straggle=False):
                 _, loss = ddp(xs, ys)
             (loss / 2).backward()
             losses.append(loss.item())
+        if comm == "fused" and step == 0 and os.environ.get("COMM_DEBUG"):
+            torch.cuda.synchronize(); ddp.symm.comm_stream.synchronize()
+            loc = ddp.flat_grad.clone()
+            gl = [torch.zeros_like(loc) for _ in range(world)]
+            dist.all_gather(gl, loc)
+            print(f"[rank {rank}] local |g|={loc.norm().item():.4f} peers |g|={[g_.norm().item() for g_ in gl]}", flush=True)
         norms.append(float(opt.step(max_norm=1.0)))
     torch.cuda.synchronize()
     ddp.sync_master()
     return ddp, norms, losses
 
 
+def synthetic_check(rank, world):
+    """Kernel-level check with analytically known values: rank r's gradient arena is filled with
+    (r + 1) * pattern; the fused step must see mean_r((r+1)) * pattern and its exact norm."""
+    torch.manual_seed(5)
+    lin = torch.nn.Sequential(*[torch.nn.Linear(512, 1024 - 8 * i, bias=True) for i in range(3)]).cuda()
+    ddp = FusedDDP(lin, comm="fused", bucket_cap_mb=0.25)
+    from mamba_distributed_b200.parallel import FusedAdamW
+    opt = FusedAdamW(ddp, [{"params": [l.weight for l in lin], "weight_decay": 0.1},
+                           {"params": [l.bias for l in lin], "weight_decay": 0.0}], lr=1e-2)
+    assert len(ddp.buckets) >= 2
+    pattern = torch.sin(torch.arange(ddp.total, device="cuda", dtype=torch.float32) * 0.37)
+    mask = torch.zeros(ddp.total, device="cuda")
+    for p_, off in zip(ddp.params, ddp.offsets):
+        mask[off:off + p_.numel()] = 1
+    pattern = pattern * mask
+    ddp.flat_grad.copy_(pattern * (rank + 1))
+    p0 = ddp.flat_param.clone()
+    torch.cuda.synchronize(); dist.barrier()
+    norm = float(opt.step(max_norm=None))
+    torch.cuda.synchronize(); dist.barrier()
+    mean_scale = sum(r + 1 for r in range(world)) / world
+    g = pattern * mean_scale
+    exp_norm = g.norm().item()
+    assert abs(norm - exp_norm) <= 1e-4 * exp_norm, (norm, exp_norm)
+    # reference AdamW (step 1: m = (1-b1) g, v = (1-b2) g^2)
+    ddp.sync_master()
+    wd = torch.zeros(ddp.total, device="cuda")
+    for (s_, e_, gi) in opt.segments:
+        wd[s_:e_] = opt.param_groups[gi]["weight_decay"]
+    exp_p = p0 * (1 - 1e-2 * wd) - 1e-2 * g / (g.abs() + 1e-8)
+    exp_p = torch.where(mask.bool(), exp_p, p0)
+    assert torch.allclose(ddp.flat_param, exp_p, atol=1e-6, rtol=1e-5), (ddp.flat_param - exp_p).abs().max()
+    assert torch.equal(ddp.flat_bf16, ddp.flat_param.bfloat16())
+    return norm
+
+
 def main():
     dist.init_process_group("nccl")
     rank, world = dist.get_rank(), dist.get_world_size()
     torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+    synthetic_check(rank, world)
     ref, norms_ref, _ = run("allreduce", rank, world)
     fused, norms_f, _ = run("fused", rank, world, straggle=True)
     assert fused.comm == "fused" and fused.symm is not None
+    # tensors that kernels read in fp32 (norms, conv, A_log, dt_bias, D, embedding) must be current on
+    # EVERY rank right after the fused step, without any explicit synchronisation
+    for n, p_ in fused.module.named_parameters():
+        if not getattr(p_, "_bf16_only", False):
+            mx, mn = p_.detach().clone(), p_.detach().clone()
+            dist.all_reduce(mx, op=dist.ReduceOp.MAX); dist.all_reduce(mn, op=dist.ReduceOp.MIN)
+            assert torch.equal(mx, mn), n
+    fused.sync_master()
     # same trajectory as the NCCL + PyTorch AdamW path (different summation order: tolerance)
     for a, b in zip(norms_f, norms_ref):
         assert abs(a - b) <= 2e-2 * abs(b) + 1e-3, (norms_f, norms_ref)
     pf, pr = fused.flat_param, ref.flat_param
-    err = (pf - pr).abs().max().item()
-    assert err < 2e-3, err
+    # Adam normalises per element, so reduction-order noise can flip individual early updates:
+    # compare in norm
+    err = ((pf - pr).norm() / pr.norm()).item()
+    assert err < 5e-3, err
     # every rank holds bit-identical bf16 parameters and fp32 masters after the fused step
     for t in (fused.flat_bf16.view(torch.int16).to(torch.int32), fused.flat_param.view(torch.int32)):
         mx, mn = t.clone(), t.clone()

@@ -170,7 +170,7 @@ def test_linear_fn_accumulates_weight_grad_in_place():
     x = torch.randn(2, 128, 768, device="cuda").bfloat16().requires_grad_(True)
     w = (torch.randn(3352, 768, device="cuda") / 28).requires_grad_(True)
     calls = []
-    w._post_grad_hook = lambda: calls.append(1)
+    w.register_post_accumulate_grad_hook(lambda p: calls.append(1))
     y = nat.linear(x, w)
     dy = torch.randn_like(y)
     y.backward(dy)
