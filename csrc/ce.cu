@@ -1,0 +1,93 @@
+// K17 (part): cross-entropy over one slab of logits, forward and gradient in a single pass pair.
+// The lm_head GEMM (csrc/gemm.cu) writes an fp32 [R, V] slab; this kernel turns it into
+//   loss[r]      = logsumexp(logits[r, :]) - logits[r, target[r]]
+//   dlogits[r,:] = (softmax(logits[r, :]) - onehot(target[r])) * scale        (bf16, in place of a
+//                  separate softmax / scatter / scale / cast sequence of ATen kernels)
+// which then feeds the dgrad and wgrad GEMMs.  Replaces ATen's log_softmax + nll_loss forward and
+// backward as reached from F.cross_entropy at /root/reference/model.py:43-46.
+// One CTA per row; the row (V = 50304 floats = 196 KB) is read twice (second read hits L2).
+#include "common.cuh"
+#include "../include/mamba_b200.h"
+
+namespace mb {
+
+constexpr int kCeThreads = 512;
+
+__global__ void __launch_bounds__(kCeThreads)
+ce_slab_kernel(const float* __restrict__ logits, long long ld, const long long* __restrict__ targets,
+               float* __restrict__ loss, bf16* __restrict__ dlogits, long long ldd, int V, float scale) {
+  __shared__ float s_m[kCeThreads / 32], s_s[kCeThreads / 32];
+  __shared__ float s_max, s_lse;
+  const int row = blockIdx.x, tid = threadIdx.x;
+  const float* lr = logits + (size_t)row * ld;
+  const int nvec = V >> 2;
+  // pass 1: online max / sum-exp
+  float m = -INFINITY, s = 0.f;
+  for (int i = tid; i < nvec; i += kCeThreads) {
+    const float4 v = *reinterpret_cast<const float4*>(lr + 4 * i);
+    const float vm = fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w));
+    if (vm > m) { s *= __expf(m - vm); m = vm; }
+    s += __expf(v.x - m) + __expf(v.y - m) + __expf(v.z - m) + __expf(v.w - m);
+  }
+  for (int i = (nvec << 2) + tid; i < V; i += kCeThreads) {
+    const float v = lr[i];
+    if (v > m) { s *= __expf(m - v); m = v; }
+    s += __expf(v - m);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float om = __shfl_xor_sync(0xffffffffu, m, o), os = __shfl_xor_sync(0xffffffffu, s, o);
+    const float nm = fmaxf(m, om);
+    s = s * __expf(m - nm) + os * __expf(om - nm);
+    m = nm;
+  }
+  if ((tid & 31) == 0) { s_m[tid >> 5] = m; s_s[tid >> 5] = s; }
+  __syncthreads();
+  if (tid == 0) {
+    float M = s_m[0], S = s_s[0];
+    for (int w = 1; w < kCeThreads / 32; ++w) {
+      const float nm = fmaxf(M, s_m[w]);
+      S = S * __expf(M - nm) + s_s[w] * __expf(s_m[w] - nm);
+      M = nm;
+    }
+    const float lse = M + __logf(S);
+    s_max = M;
+    s_lse = lse;
+    const long long t = targets[row];
+    loss[row] = (t >= 0 && t < V) ? lse - lr[t] : 0.f;
+  }
+  __syncthreads();
+  if (dlogits == nullptr) return;
+  // pass 2: gradient
+  const float lse = s_lse;
+  const long long t = targets[row];
+  bf16* dr = dlogits + (size_t)row * ldd;
+  const int nv8 = V >> 3;
+  for (int i = tid; i < nv8; i += kCeThreads) {
+    float f[8];
+    ld8f(lr + 8 * i, f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float p = __expf(f[j] - lse);
+      if (8 * i + j == t) p -= 1.f;
+      f[j] = p * scale;
+    }
+    st8(dr + 8 * i, pack8(f));
+  }
+  for (int i = (nv8 << 3) + tid; i < V; i += kCeThreads) {
+    float p = __expf(lr[i] - lse);
+    if (i == t) p -= 1.f;
+    dr[i] = __float2bfloat16(p * scale);
+  }
+}
+
+}  // namespace mb
+using namespace mb;
+
+extern "C" int mb_ce_slab(const float* logits, long long ld, const long long* targets, float* loss,
+                          void* dlogits_bf16, long long ldd, int R, int V, float scale, cudaStream_t stream) {
+  MB_REQUIRE(ld % 4 == 0 && (dlogits_bf16 == nullptr || ldd % 8 == 0), "ce_slab: row strides must keep 16-byte alignment");
+  if (R == 0) return 0;
+  ce_slab_kernel<<<R, kCeThreads, 0, stream>>>(logits, ld, targets, loss, (bf16*)dlogits_bf16, ldd, V, scale);
+  return check_launch("ce_slab");
+}

@@ -71,6 +71,12 @@ int mb_embedding_bwd(const long long* ids, const float* dout, float* dw, int M, 
                      cudaStream_t stream);
 int mb_cast_f32_bf16(const float* in, void* out_bf16, long long n, cudaStream_t stream);
 
+/* ---- K17: cross-entropy over a slab of lm_head logits: per-row loss and, in the same launch,
+ *      (softmax - onehot) * scale in bf16 for the dgrad / wgrad GEMMs (ATen log_softmax + nll_loss
+ *      fwd/bwd behind F.cross_entropy, /root/reference/model.py:43-46) ------------------------- */
+int mb_ce_slab(const float* logits, long long ld, const long long* targets, float* loss,
+               void* dlogits_bf16, long long ldd, int R, int V, float scale, cudaStream_t stream);
+
 /* ---- K16: bf16 GEMM on tcgen05/TMEM/TMA (cuBLAS behind nn.Linear) ------------------------- */
 int mb_gemm_bf16(const void* A, long long lda, int a_major, const void* B, long long ldb, int b_major,
                  void* D, long long ldd, int d_mode, const float* bias, int M, int N, int K,

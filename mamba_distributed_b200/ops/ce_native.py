@@ -2,14 +2,15 @@
 
 The reference computes ``F.cross_entropy(lm_head(h))`` on fully materialised logits
 (/root/reference/model.py:35-46: 3.3 GB bf16 + 6.6 GB fp32 per micro-batch at B=32, T=1024).
-Here rows are processed in slabs: logits slab (tcgen05 GEMM, fp32 out) -> log-sum-exp / target
-gather -> (p - onehot) in bf16 -> dgrad and wgrad GEMMs, all inside forward, so only an
-``[R, V]`` slab ever exists.  Backward just scales the stored ``dh`` / ``dW`` by the incoming
+Here rows are processed in slabs: logits slab (tcgen05 GEMM, fp32 out) -> one kernel
+(``csrc/ce.cu``) computing the per-row loss and (p - onehot) * scale in bf16 -> dgrad and wgrad
+GEMMs, all inside forward, so only an ``[R, V]`` slab ever exists.  Backward just scales the stored ``dh`` / ``dW`` by the incoming
 scalar gradient."""
 from __future__ import annotations
 
 import torch
 
+from ._lib import call
 from .native import bf16_weight, gemm_nn, gemm_nt, gemm_tn_acc, grad_buffer, notify_grad_ready
 
 SLAB_ROWS = 4096
@@ -28,18 +29,18 @@ class LinearCrossEntropyFn(torch.autograd.Function):
         dh = torch.empty(M, d, dtype=torch.bfloat16, device=h2.device) if need_grad else None
         dW = torch.zeros(V, d, dtype=torch.float32, device=h2.device) if need_grad else None
         scale = 1.0 / M if reduction == "mean" else 1.0
+        targets = targets.contiguous()
+        R = min(SLAB_ROWS, M)
+        logits = torch.empty(R, V, dtype=torch.float32, device=h2.device)
+        pb = torch.empty(R, V, dtype=torch.bfloat16, device=h2.device) if need_grad else None
         for s in range(0, M, SLAB_ROWS):
             e = min(M, s + SLAB_ROWS)
-            logits = gemm_nt(h2[s:e], w, out_dtype=torch.float32)
-            t = targets[s:e]
-            lse = torch.logsumexp(logits, dim=1)
-            losses[s:e] = lse - logits.gather(1, t[:, None]).squeeze(1)
+            r = e - s
+            gemm_nt(h2[s:e], w, out=logits[:r])                      # tcgen05 GEMM, fp32 slab
+            call("mb_ce_slab", logits, V, targets[s:e], losses[s:e], pb, V, r, V, scale)
             if need_grad:
-                p = logits.sub_(lse[:, None]).exp_()
-                p.scatter_add_(1, t[:, None], torch.full((e - s, 1), -1.0, device=p.device))
-                pb = p.mul_(scale).to(torch.bfloat16)
-                gemm_nn(pb, w, out=dh[s:e])
-                gemm_tn_acc(pb, h2[s:e], dW)
+                gemm_nn(pb[:r], w, out=dh[s:e])                      # dh   = (p - onehot) W
+                gemm_tn_acc(pb[:r], h2[s:e], dW)                     # dW  += (p - onehot)^T h
         ctx.need = need_grad
         if need_grad:
             ctx.save_for_backward(dh, dW, weight)

@@ -182,3 +182,26 @@ def test_linear_fn_accumulates_weight_grad_in_place():
     _close(w.grad, exp_dw, 5e-2, 2e-2, "dW")
     _close(x.grad, 2 * (dy.float() @ wb), 1e-1, 3e-2, "dx")
     assert len(calls) == 2
+
+
+@pytest.mark.parametrize("M,V,d", [(300, 50304, 256), (4500, 1024, 128)])
+@pytest.mark.parametrize("reduction", ["mean", "sum"])
+def test_linear_cross_entropy_fwd_bwd(M, V, d, reduction):
+    from mamba_distributed_b200.ops import ce_native
+    torch.manual_seed(0)
+    h = (torch.randn(M, d, device="cuda")).bfloat16().requires_grad_(True)
+    w = (torch.randn(V, d, device="cuda") * 0.05).requires_grad_(True)
+    t = torch.randint(0, V, (M,), device="cuda")
+    loss = ce_native.linear_cross_entropy(h, w, t, reduction)
+    (loss * 0.5).backward()
+    hr = h.detach().float().requires_grad_(True)
+    wr = w.detach().bfloat16().float().requires_grad_(True)
+    loss_ref = F.cross_entropy(hr @ wr.t(), t, reduction=reduction)
+    (loss_ref * 0.5).backward()
+    assert abs(loss.item() - loss_ref.item()) <= 2e-3 * abs(loss_ref.item()) + 1e-3
+    _close(h.grad, hr.grad, 2e-2 * hr.grad.abs().max().item(), 3e-2, "dh")
+    _close(w.grad, wr.grad, 2e-2 * wr.grad.abs().max().item(), 3e-2, "dW")
+    with torch.no_grad():
+        per_tok = ce_native.linear_cross_entropy(h.detach(), w.detach(), t, "none")
+    exp = F.cross_entropy(hr.detach() @ wr.detach().t(), t, reduction="none")
+    _close(per_tok, exp, 5e-3, 5e-3, "per-token")
