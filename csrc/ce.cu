@@ -13,6 +13,9 @@ namespace mb {
 
 constexpr int kCeThreads = 512;
 
+// exp(m - nm) with the empty-partial case (m = -inf, possibly nm = -inf too) mapped to 0, not NaN
+__device__ __forceinline__ float scale_to(float m, float nm) { return m == -INFINITY ? 0.f : __expf(m - nm); }
+
 __global__ void __launch_bounds__(kCeThreads)
 ce_slab_kernel(const float* __restrict__ logits, long long ld, const long long* __restrict__ targets,
                float* __restrict__ loss, bf16* __restrict__ dlogits, long long ldd, int V, float scale) {
@@ -38,7 +41,7 @@ ce_slab_kernel(const float* __restrict__ logits, long long ld, const long long* 
   for (int o = 16; o > 0; o >>= 1) {
     const float om = __shfl_xor_sync(0xffffffffu, m, o), os = __shfl_xor_sync(0xffffffffu, s, o);
     const float nm = fmaxf(m, om);
-    s = s * __expf(m - nm) + os * __expf(om - nm);
+    s = s * scale_to(m, nm) + os * scale_to(om, nm);
     m = nm;
   }
   if ((tid & 31) == 0) { s_m[tid >> 5] = m; s_s[tid >> 5] = s; }
@@ -47,7 +50,7 @@ ce_slab_kernel(const float* __restrict__ logits, long long ld, const long long* 
     float M = s_m[0], S = s_s[0];
     for (int w = 1; w < kCeThreads / 32; ++w) {
       const float nm = fmaxf(M, s_m[w]);
-      S = S * __expf(M - nm) + s_s[w] * __expf(s_m[w] - nm);
+      S = S * scale_to(M, nm) + s_s[w] * scale_to(s_m[w], nm);
       M = nm;
     }
     const float lse = M + __logf(S);

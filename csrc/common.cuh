@@ -30,8 +30,14 @@ int check_launch(const char* what);            // cudaGetLastError -> set_error;
   } while (0)
 
 // ---- small math -------------------------------------------------------------------------------
-// sigmoid with one MUFU.EX2 + one MUFU.RCP (no IEEE division sequence)
-__device__ __forceinline__ float sigmoid_f(float x) { return __frcp_rn(1.f + __expf(-x)); }
+// sigmoid with one MUFU.EX2 + one MUFU.RCP.  (__frcp_rn / operator/ expand to an IEEE-rounded
+// multi-instruction sequence; rcp.approx is a single MUFU op, 1 ulp-ish, plenty for an activation.)
+__device__ __forceinline__ float rcp_approx(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ float sigmoid_f(float x) { return rcp_approx(1.f + __expf(-x)); }
 __device__ __forceinline__ float silu_f(float x) { return x * sigmoid_f(x); }
 // d/dx silu(x) = s + x*s*(1-s), s = sigmoid(x)
 __device__ __forceinline__ float dsilu_f(float x) {

@@ -84,7 +84,7 @@ conv1d_fwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __rest
 
 // Backward.  dw / dbias are accumulated with one fp32 atomic per (block, channel, tap).
 template <int W, bool SILU>
-__global__ void __launch_bounds__(kConvThreads, 3)
+__global__ void __launch_bounds__(kConvThreads)
 conv1d_bwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __restrict__ w,
                   const float* __restrict__ bias, const bf16* __restrict__ dy, long long lddy,
                   bf16* __restrict__ dx, long long lddx, float* __restrict__ dw,

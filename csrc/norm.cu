@@ -359,7 +359,7 @@ gated_rmsnorm_bwd_rows_kernel(const bf16* __restrict__ x, int ldx, const bf16* _
   }
 }
 
-constexpr int kDwRows = 128;  // rows per strip
+constexpr int kDwRows = 32;  // rows per strip (more strips -> more loads in flight; 8 atomics per strip-thread)
 __global__ void __launch_bounds__(128)
 gated_rmsnorm_bwd_dw_kernel(const bf16* __restrict__ x, int ldx, const bf16* __restrict__ z, int ldz,
                             const float* __restrict__ rstd_in, const bf16* __restrict__ dout, int ldo,

@@ -101,9 +101,17 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
       tmem_ld32(tmem + lane_sel + k0, v);
       tmem_ld_wait();
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const int cj = cj0 + k0 + j;
-        if (cj <= ri) acc[ch * 32 + j] += __uint_as_float(v[j]) * __expf(fminf(a_i - s_a[cj], 0.f)) * s_dt[cj];
+      for (int q = 0; q < 8; ++q) {  // branch-free, 128-bit broadcast loads of a_j / dt_j
+        const float4 a4 = *reinterpret_cast<const float4*>(s_a + cj0 + k0 + 4 * q);
+        const float4 d4 = *reinterpret_cast<const float4*>(s_dt + cj0 + k0 + 4 * q);
+        const float aj[4] = {a4.x, a4.y, a4.z, a4.w}, dj[4] = {d4.x, d4.y, d4.z, d4.w};
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          const int cj = cj0 + k0 + 4 * q + t;
+          const float val = __uint_as_float(v[4 * q + t]) * __expf(fminf(a_i - aj[t], 0.f)) * dj[t];
+          const unsigned keep = (cj <= ri) ? 0xffffffffu : 0u;
+          acc[ch * 32 + 4 * q + t] += __uint_as_float(__float_as_uint(val) & keep);
+        }
       }
     }
     tc_fence_before();

@@ -19,18 +19,19 @@ constexpr int kThreads = 256;
 // ------------------------------------------------------------------------------------------
 // outer-product kernel: out[(hh,p), n] = sum_t arow[t, (hh,p)] * scale_hh[t] * bop[t, n]
 // ------------------------------------------------------------------------------------------
-constexpr int kOuterSmem = 2 * (kL * 2 * 128) + 2 * kL * 4 + 64 + 1024;
+constexpr int kOuterHalf = 128;  // K rows staged per pass: 2 passes keep smem at 64 KB -> 3 CTAs / SM
+constexpr int kOuterSmem = 2 * (kOuterHalf * 2 * 128) + 2 * kL * 4 + 64 + 1024;
 
 template <bool DSTATE>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads, 3)
 ssd_outer_kernel(const bf16* __restrict__ arow, long long lda, const bf16* __restrict__ bop, long long ldb,
                  const float* __restrict__ dtv, const float* __restrict__ av, float* __restrict__ out, int T,
                  int H, int G, int nc, int hpc) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align1024(smem_raw);
-  uint8_t* sA = smem;                       // [256 k-rows][2 atoms]  MN-major A
-  uint8_t* sB = smem + kL * 2 * 128;        // [256 k-rows][2 atoms]  MN-major B
-  float* s_scale = reinterpret_cast<float*>(smem + 2 * kL * 2 * 128);  // [2][256]
+  uint8_t* sA = smem;                                // [128 k-rows][2 atoms]  MN-major A
+  uint8_t* sB = smem + kOuterHalf * 2 * 128;         // [128 k-rows][2 atoms]  MN-major B
+  float* s_scale = reinterpret_cast<float*>(smem + 2 * kOuterHalf * 2 * 128);  // [2][256]
   uint64_t* bar = reinterpret_cast<uint64_t*>(s_scale + 2 * kL);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 1);
 
@@ -53,35 +54,39 @@ ssd_outer_kernel(const bf16* __restrict__ arow, long long lda, const bf16* __res
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
-
   const size_t row0 = (size_t)b * T + (size_t)c * kL;
-  auto scale = [&](int row, int blk) { return s_scale[blk * kL + row]; };
-  load_tile<2, false>(sB, bop + row0 * ldb + g * kN, ldb, kL, valid, NoScale(), tid, kThreads);  // async
-  if (hpc == 2) load_tile<2, true>(sA, arow + row0 * lda + h0 * kP, lda, kL, valid, scale, tid, kThreads);
-  else load_tile<1, true>(sA, arow + row0 * lda + h0 * kP, lda, kL, valid, scale, tid, kThreads);
-  cp_async_commit();
-  cp_async_wait<0>();
-  fence_proxy_async_smem();
-  __syncthreads();
 
-  if (tid == 0) {
-    tc_fence_after();
-    constexpr uint32_t idesc = make_idesc_bf16(128, kN, MAJOR_MN, MAJOR_MN);
-    const uint32_t a_addr = smem_u32(sA), b_addr = smem_u32(sB);
+  for (int half = 0; half < kL / kOuterHalf; ++half) {
+    const int k0 = half * kOuterHalf;
+    const int v = max(0, min(kOuterHalf, valid - k0));
+    auto scale = [&](int row, int blk) { return s_scale[blk * kL + k0 + row]; };
+    load_tile<2, false>(sB, bop + (row0 + k0) * ldb + g * kN, ldb, kOuterHalf, v, NoScale(), tid, kThreads);  // async
+    cp_async_commit();
+    if (hpc == 2) load_tile<2, true>(sA, arow + (row0 + k0) * lda + h0 * kP, lda, kOuterHalf, v, scale, tid, kThreads);
+    else load_tile<1, true>(sA, arow + (row0 + k0) * lda + h0 * kP, lda, kOuterHalf, v, scale, tid, kThreads);
+    cp_async_wait<0>();
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (tid == 0) {
+      tc_fence_after();
+      constexpr uint32_t idesc = make_idesc_bf16(128, kN, MAJOR_MN, MAJOR_MN);
+      const uint32_t a_addr = smem_u32(sA), b_addr = smem_u32(sB);
 #pragma unroll
-    for (int k = 0; k < kL / 16; ++k)
-      mma_bf16_ss(tmem, desc_mnmajor(a_addr, kL, k), desc_mnmajor(b_addr, kL, k), idesc, k > 0 ? 1u : 0u);
-    mma_commit(bar);
+      for (int k = 0; k < kOuterHalf / 16; ++k)
+        mma_bf16_ss(tmem, desc_mnmajor(a_addr, kOuterHalf, k), desc_mnmajor(b_addr, kOuterHalf, k), idesc,
+                    (half > 0 || k > 0) ? 1u : 0u);
+      mma_commit(bar);
+    }
+    mbar_wait(bar, half & 1);  // operands consumed: smem may be refilled / accumulator readable
+    tc_fence_after();
   }
-  mbar_wait(bar, 0);
-  tc_fence_after();
 
-  const int lg = warp & 3, half = warp >> 2;
+  const int lg = warp & 3, colhalf = warp >> 2;
   const int r = lg * 32 + lane;
   const int hh = r / kP, p = r % kP;
 #pragma unroll
   for (int ch = 0; ch < 2; ++ch) {
-    const int col = half * 64 + ch * 32;
+    const int col = colhalf * 64 + ch * 32;
     uint32_t v[32];
     tmem_ld32(tmem + ((uint32_t)(lg * 32) << 16) + col, v);
     tmem_ld_wait();
@@ -100,16 +105,31 @@ ssd_outer_kernel(const bf16* __restrict__ arow, long long lda, const bf16* __res
 }
 
 // ------------------------------------------------------------------------------------------
-// scan kernel (FWD: y ; BWD: dx, ddt partials)
+// scan kernel (FWD: y ; BWD: dx, ddt partials) — warp-specialised, software-pipelined over heads
+//
+//   warps 0-7   "scale"     read the CB tile from TMEM, apply decay / mask / dt, write the bf16
+//                           operand G one 128-column half-tile at a time into a 2-slot smem ring
+//   warps 8-11  "epilogue"  read the finished accumulators of the previous head from TMEM, add the
+//                           skip terms, store y / dx; then prefetch (cp.async) the tiles of head+2
+//   warp 12     "mma"       one lane issues tcgen05.mma: C.S^T (per head) and G.X (per half-tile);
+//                           tcgen05.commit frees G slots and publishes accumulators
+// Accumulators are double-buffered in TMEM (CB 256 cols + 2 x (64 + 64)), per-head tiles in smem, so
+// head h+1 is being scaled while head h is multiplied and head h-1 is written out.
 // ------------------------------------------------------------------------------------------
-constexpr int kScanSmem = 128 * 2 * 128   /* sR  row operand  [128][2 kblk]            32 KB */
-                        + kL * 2 * 128    /* sC  col operand  [256][2 kblk]; later G   64 KB */
-                        + 2 * kL * 128    /* sV  X_h / dY_h   [256][1 atom]  x2 buffers 64 KB */
-                        + 2 * kP * 2 * 128/* sS  S_prev_h / dS_h [64][2 kblk] x2       32 KB */
-                        + 2 * 2 * kL * 4 + 64 + 1024;
+#ifdef MB_SSD_TIMING
+__device__ long long g_tlog[2048];
+__device__ int g_tmeta[2048];
+__device__ int g_tcount = 0;
+#endif
+constexpr int kScanThreads = 13 * 32;
+constexpr int kScanSmem = 128 * 2 * 128     /* sR  row operand  [128][2 kblk]               32 KB */
+                        + 2 * (128 * 128 * 2) /* sG ring: 2 x [128][128] bf16 (aliases sC)     64 KB */
+                        + 2 * kL * 128      /* sV  X_h / dY_h   [256][1 atom]   x2 buffers   64 KB */
+                        + 2 * kP * 2 * 128  /* sS  S_prev_h / dS_h [64][2 kblk] x2           32 KB */
+                        + 2 * 2 * kL * 4 + 128 + 1024;
 
 template <bool BWD>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kScanThreads, 1)
 ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, long long ldbc,
                 const bf16* __restrict__ vsrc, long long ldv, const bf16* __restrict__ ssrc,
                 const float* __restrict__ dtv, const float* __restrict__ av, const float* __restrict__ Dp,
@@ -119,13 +139,19 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align1024(smem_raw);
   uint8_t* sR = smem;
-  uint8_t* sC = sR + 128 * 2 * 128;
-  uint8_t* sG = sC;  // aliases the column operand once CB is in TMEM
-  uint8_t* sV0 = sC + kL * 2 * 128;          // two buffers: the next head's tiles stream in (cp.async)
-  uint8_t* sS0 = sV0 + 2 * kL * 128;         // while the current head is being scaled / multiplied
-  float* s_ad = reinterpret_cast<float*>(sS0 + 2 * kP * 2 * 128);  // [2 buffers][a(256) | dt(256)]
-  uint64_t* bar = reinterpret_cast<uint64_t*>(s_ad + 2 * 2 * kL);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 1);
+  uint8_t* sG = sR + 128 * 2 * 128;   // ring of two 32 KB half-tiles; holds the column operand first
+  uint8_t* sC = sG;
+  uint8_t* sV0 = sG + 2 * 32768;
+  uint8_t* sS0 = sV0 + 2 * kL * 128;
+  float* s_ad = reinterpret_cast<float*>(sS0 + 2 * kP * 2 * 128);  // [2][a(256) | dt(256)]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_ad + 2 * 2 * kL);
+  uint64_t* cb_bar = bars;            // 1
+  uint64_t* g_full = bars + 1;        // [2]  256 scale threads arrive
+  uint64_t* g_empty = bars + 3;       // [2]  tcgen05.commit
+  uint64_t* acc_full = bars + 5;      // [2]  tcgen05.commit
+  uint64_t* acc_empty = bars + 7;     // [2]  128 epilogue threads arrive
+  uint64_t* tiles_full = bars + 9;    // [2]  128 epilogue threads arrive after their cp.async landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int rh = blockIdx.x & 1;
@@ -133,189 +159,274 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
   const int b = bc / nc, c = bc % nc;
   const int h_first = blockIdx.y * hgs;
   const int g = h_first / (H / G);
-  const int valid = min(kL, T - c * kL);        // valid tokens in this chunk
-  const int r0 = rh * 128;                      // first row of this CTA
-  const int c0 = BWD ? rh * 128 : 0;            // first column
+  const int valid = min(kL, T - c * kL);
+  const int r0 = rh * 128;
+  const int c0 = BWD ? rh * 128 : 0;
   const int ncols = BWD ? (2 - rh) * 128 : (rh + 1) * 128;
+  const int nhalves = ncols >> 7;
   const size_t row_base = (size_t)b * T + (size_t)c * kL;
 
-  if (tid == 0) { mbar_init(bar, 1); fence_mbar_init(); }
-  if (warp == 0) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem = *tmem_slot;
-  const uint32_t tCB = tmem, tOff = tmem + 256, tDiag = tmem + 320;
-  uint32_t phase = 0;
+  if (tid == 0) {
+    mbar_init(cb_bar, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&g_full[i], 256); mbar_init(&g_empty[i], 1); mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_empty[i], 128); mbar_init(&tiles_full[i], 128);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 12) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
 
-  // ---- CB (or its transpose) for this row half: [128 x ncols], K = d_state ----
-  load_tile<2, false>(sR, rowop + (row_base + r0) * ldbc + g * kN, ldbc, 128, max(0, min(128, valid - r0)),
-                      NoScale(), tid, kThreads);
-  load_tile<2, false>(sC, colop + (row_base + c0) * ldbc + g * kN, ldbc, ncols, max(0, min(ncols, valid - c0)),
-                      NoScale(), tid, kThreads);
-  cp_async_commit();
-  auto prefetch_head = [&](int hh) {
+  // per-head tiles: a | dt (2 KB), V tile [ncols][64], state tile [64][128]; issued by `nthr` threads
+  auto prefetch_head = [&](int hh, int t, int nthr) {
     const int h = h_first + hh;
     const int bsel = hh & 1;
     const size_t sb = ((size_t)bc * H + h) * kL;
     const uint32_t ad = smem_u32(s_ad + bsel * 2 * kL);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(ad + tid * 4), "l"(av + sb + tid) : "memory");
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(ad + (kL + tid) * 4), "l"(dtv + sb + tid) : "memory");
+    for (int i = t; i < kL; i += nthr) {
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(ad + i * 4), "l"(av + sb + i) : "memory");
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(ad + (kL + i) * 4), "l"(dtv + sb + i) : "memory");
+    }
     load_tile<1, false>(sV0 + bsel * kL * 128, vsrc + (row_base + c0) * ldv + h * kP, ldv, ncols,
-                        max(0, min(ncols, valid - c0)), NoScale(), tid, kThreads);
-    load_tile<2, false>(sS0 + bsel * kP * 2 * 128, ssrc + ((size_t)bc * H + h) * kP * kN, kN, kP, kP, NoScale(), tid,
-                        kThreads);
+                        max(0, min(ncols, valid - c0)), NoScale(), t, nthr);
+    load_tile<2, false>(sS0 + bsel * kP * 2 * 128, ssrc + ((size_t)bc * H + h) * kP * kN, kN, kP, kP, NoScale(), t, nthr);
     cp_async_commit();
   };
-  prefetch_head(0);
-  cp_async_wait<1>();  // row / column operands have landed (head 0's tiles may still be in flight)
+
+  // ---- prologue: row / column operands, heads 0 and 1, CB (or its transpose) into TMEM ----
+  load_tile<2, false>(sR, rowop + (row_base + r0) * ldbc + g * kN, ldbc, 128, max(0, min(128, valid - r0)),
+                      NoScale(), tid, kScanThreads);
+  load_tile<2, false>(sC, colop + (row_base + c0) * ldbc + g * kN, ldbc, ncols, max(0, min(ncols, valid - c0)),
+                      NoScale(), tid, kScanThreads);
+  cp_async_commit();
+  prefetch_head(0, tid, kScanThreads);
+  if (hgs > 1) prefetch_head(1, tid, kScanThreads);
+  cp_async_wait<0>();
   fence_proxy_async_smem();
+  tc_fence_before();
   __syncthreads();
-  if (tid == 0) {
-    tc_fence_after();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tCB = tmem;
+  if (warp == 12 && lane == 0) {
     const uint32_t idesc = make_idesc_bf16(128, ncols, MAJOR_K, MAJOR_K);
     const uint32_t a_addr = smem_u32(sR), b_addr = smem_u32(sC);
 #pragma unroll
     for (int k = 0; k < kN / 16; ++k)
       mma_bf16_ss(tCB, desc_kmajor(a_addr, 128, k >> 2, k & 3), desc_kmajor(b_addr, ncols, k >> 2, k & 3), idesc,
                   k > 0 ? 1u : 0u);
-    mma_commit(bar);
+    mma_commit(cb_bar);
   }
-  mbar_wait(bar, phase);
-  phase ^= 1;
+  mbar_wait(cb_bar, 0);  // CB complete: the column operand is dead, its smem becomes the G ring
   tc_fence_after();
 
-  const int lg = warp & 3, half = warp >> 2;
-  const int r = lg * 32 + lane;       // local row
-  const int ri = r0 + r;              // row inside the chunk
-  const uint32_t lane_sel = (uint32_t)(lg * 32) << 16;
-  const int warp_row_min = r0 + lg * 32, warp_row_max = warp_row_min + 31;
-
-  for (int hh = 0; hh < hgs; ++hh) {
-    const int h = h_first + hh;
-    const size_t sbase = ((size_t)bc * H + h) * kL;
-    uint8_t* sV = sV0 + (hh & 1) * kL * 128;
-    uint8_t* sS = sS0 + (hh & 1) * kP * 2 * 128;
-    const float* s_a = s_ad + (hh & 1) * 2 * kL;
-    const float* s_dt = s_a + kL;
-    if (hh + 1 < hgs) { prefetch_head(hh + 1); cp_async_wait<1>(); }
-    else cp_async_wait<0>();
-    __syncthreads();
-
-    // ---- G = CB o decay o mask (o dt_j in FWD) -> bf16 K-major operand ----
-    const float a_i = s_a[ri];
-    const int cols_per_thread = ncols >> 1;
-    for (int k0 = half * cols_per_thread; k0 < (half + 1) * cols_per_thread; k0 += 32) {
-      const int cj0 = c0 + k0;
-      const bool skip = BWD ? (cj0 + 31 < warp_row_min) : (cj0 > warp_row_max);  // warp-uniform
-      float f[32];
-      if (!skip) {
-        uint32_t v[32];
-        tmem_ld32(tCB + lane_sel + k0, v);
-        tmem_ld_wait();
+#ifdef MB_SSD_TIMING
+  const bool tprint = blockIdx.x == 5 && blockIdx.y == 0 && !BWD;
+  const long long t_start = clock64();
+#define TMARK(role, hh, what) if (tprint && lane == 0) { int i_ = atomicAdd(&g_tcount, 1); if (i_ < 2048) { g_tlog[i_] = clock64() - t_start; g_tmeta[i_] = (warp << 16) | ((hh) << 8) | (what[0]); } }
+#else
+#define TMARK(role, hh, what)
+#endif
+  if (warp < 8) {
+    // =================================== scale warps ===================================
+    const int lg = warp & 3, sub = warp >> 2;      // 32-row lane group, 64-column sub-block of the half-tile
+    const int r = lg * 32 + lane, ri = r0 + r;
+    const uint32_t lane_sel = (uint32_t)(lg * 32) << 16;
+    const int warp_row_min = r0 + lg * 32, warp_row_max = warp_row_min + 31;
+    int unit = 0;
+    for (int hh = 0; hh < hgs; ++hh) {
+      if (hh >= 2) mbar_wait(&tiles_full[hh & 1], ((hh >> 1) - 1) & 1);
+      TMARK("scale", hh, "tiles_ready");
+      const float* s_a = s_ad + (hh & 1) * 2 * kL;
+      const float* s_dt = s_a + kL;
+      const float a_i = s_a[ri];
+      for (int half = 0; half < nhalves; ++half, ++unit) {
+        const int slot = unit & 1, use = unit >> 1;
+        if (use > 0) mbar_wait(&g_empty[slot], (use - 1) & 1);
+        TMARK("scale", hh, "slot_free");
+        uint8_t* gdst = sG + slot * 32768 + (size_t)sub * (128 * 128) + r * 128;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int cj = cj0 + j;
-          float val;
-          if (BWD) val = (cj >= ri) ? __uint_as_float(v[j]) * __expf(fminf(s_a[cj] - a_i, 0.f)) : 0.f;
-          else val = (cj <= ri) ? __uint_as_float(v[j]) * __expf(fminf(a_i - s_a[cj], 0.f)) * s_dt[cj] : 0.f;
-          f[j] = val;
+        for (int kq = 0; kq < 2; ++kq) {
+          const int kcol = half * 128 + sub * 64 + kq * 32;  // column inside the CB tile
+          const int cj0 = c0 + kcol;
+          const bool skip = BWD ? (cj0 + 31 < warp_row_min) : (cj0 > warp_row_max);  // warp-uniform
+          uint32_t pk[16];  // 32 bf16 results, packed as soon as they are produced
+          if (!skip) {
+            uint32_t v[32];
+            tmem_ld32(tCB + lane_sel + kcol, v);
+            tmem_ld_wait();
+            // branch-free (the causal mask is a bit mask) and in groups of 4 columns whose a_j / dt_j
+            // come from one 128-bit broadcast load each: keeps ~16 independent exp chains in flight
+            // without holding 4 x 32 fp32 values live
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+              const float4 a4 = *reinterpret_cast<const float4*>(s_a + cj0 + 4 * q);
+              float4 d4 = make_float4(1.f, 1.f, 1.f, 1.f);
+              if (!BWD) d4 = *reinterpret_cast<const float4*>(s_dt + cj0 + 4 * q);
+              const float aj[4] = {a4.x, a4.y, a4.z, a4.w}, dj[4] = {d4.x, d4.y, d4.z, d4.w};
+              float o4[4];
+#pragma unroll
+              for (int t = 0; t < 4; ++t) {
+                const int cj = cj0 + 4 * q + t;
+                const float e = __expf(fminf(BWD ? aj[t] - a_i : a_i - aj[t], 0.f));
+                const float val = __uint_as_float(v[4 * q + t]) * e * dj[t];
+                const unsigned keep = (BWD ? (cj >= ri) : (cj <= ri)) ? 0xffffffffu : 0u;
+                o4[t] = __uint_as_float(__float_as_uint(val) & keep);
+              }
+              const bf162 lo = __floats2bfloat162_rn(o4[0], o4[1]), hi = __floats2bfloat162_rn(o4[2], o4[3]);
+              pk[2 * q] = *reinterpret_cast<const uint32_t*>(&lo);
+              pk[2 * q + 1] = *reinterpret_cast<const uint32_t*>(&hi);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) pk[j] = 0u;
+          }
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+            *reinterpret_cast<uint4*>(gdst + (((kq * 4 + q) ^ (r & 7)) << 4)) =
+                make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
         }
-      } else {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] = 0.f;
+        fence_proxy_async_smem();
+        mbar_arrive(&g_full[slot]);
+        TMARK("scale", hh, "half_done");
       }
-      uint8_t* gblk = sG + (size_t)(k0 >> 6) * (128 * 128) + r * 128;
-      const int ch0 = (k0 & 63) >> 3;
-#pragma unroll
-      for (int q = 0; q < 4; ++q)
-        *reinterpret_cast<bf16x8*>(gblk + (((ch0 + q) ^ (r & 7)) << 4)) = pack8(f + 8 * q);
     }
-    fence_proxy_async_smem();
-    tc_fence_before();
-    __syncthreads();
-
-    if (tid == 0) {
+  } else if (warp < 12) {
+    // =================================== epilogue warps ===================================
+    const int et = tid - 256;                      // 0..127
+    const int lg = warp & 3;
+    const int r = lg * 32 + lane, ri = r0 + r;
+    const uint32_t lane_sel = (uint32_t)(lg * 32) << 16;
+    for (int hh = 0; hh < hgs; ++hh) {
+      const int h = h_first + hh;
+      const int acc = hh & 1;
+      if (hh >= 1 && hh + 1 < hgs) {  // the prefetch issued last iteration (head hh+1) has to land and be published
+        cp_async_wait<0>();
+        fence_proxy_async_smem();
+        mbar_arrive(&tiles_full[(hh + 1) & 1]);
+      }
+      TMARK("epi", hh, "wait_acc");
+      mbar_wait(&acc_full[acc], (hh >> 1) & 1);
       tc_fence_after();
-      const uint32_t r_addr = smem_u32(sR), s_addr = smem_u32(sS), g_addr = smem_u32(sG), v_addr = smem_u32(sV);
-      constexpr uint32_t idesc_off = make_idesc_bf16(128, kP, MAJOR_K, MAJOR_K);
-      constexpr uint32_t idesc_diag = make_idesc_bf16(128, kP, MAJOR_K, MAJOR_MN);
-#pragma unroll
-      for (int k = 0; k < kN / 16; ++k)  // (C | B)[128 x 128] . (S_prev | dS)[64 x 128]^T
-        mma_bf16_ss(tOff, desc_kmajor(r_addr, 128, k >> 2, k & 3), desc_kmajor(s_addr, kP, k >> 2, k & 3),
-                    idesc_off, k > 0 ? 1u : 0u);
-      for (int k = 0; k < ncols / 16; ++k)  // G[128 x ncols] . V[ncols x 64]
-        mma_bf16_ss(tDiag, desc_kmajor(g_addr, 128, k >> 2, k & 3), desc_mnmajor(v_addr, ncols, k), idesc_diag,
-                    k > 0 ? 1u : 0u);
-      mma_commit(bar);
-    }
-    mbar_wait(bar, phase);
-    phase ^= 1;
-    tc_fence_after();
-
-    // ---- epilogue: this thread owns row ri, 32 of the 64 head-dim columns ----
-    {
-      const int p0 = half * 32;
-      uint32_t vo[32], vd[32];
-      tmem_ld32(tOff + lane_sel + p0, vo);
-      tmem_ld32(tDiag + lane_sel + p0, vd);
-      tmem_ld_wait();
+      TMARK("epi", hh, "acc_ready");
+      const float* s_a = s_ad + acc * 2 * kL;
+      const float* s_dt = s_a + kL;
+      const uint8_t* sV = sV0 + acc * kL * 128;
+      const uint32_t tOff = tmem + 256 + acc * 128, tDiag = tOff + 64;
+      const size_t sbase = ((size_t)bc * H + h) * kL;
+      const float a_i = s_a[ri];
       const float Dh = Dp[h];
-      const int vrow = ri - c0;  // row of this token inside sV
-      float xv[32];
+      const int vrow = ri - c0;
+      float s1 = 0.f, s2 = 0.f, sd = 0.f;
+      const float dt_i = s_dt[ri];
+      const float el = __expf(s_a[kL - 1] - a_i);
+      const float ea = __expf(a_i);
 #pragma unroll
-      for (int q = 0; q < 4; ++q)
-        unpack8(*reinterpret_cast<const bf16x8*>(sV + vrow * 128 + ((((p0 >> 3) + q) ^ (vrow & 7)) << 4)), xv + 8 * q);
-      float o[32];
-      if (!BWD) {
-        const float ea = __expf(a_i);
+      for (int ph = 0; ph < 2; ++ph) {
+        const int p0 = ph * 32;
+        uint32_t vo[32], vd[32];
+        tmem_ld32(tOff + lane_sel + p0, vo);
+        tmem_ld32(tDiag + lane_sel + p0, vd);
+        tmem_ld_wait();
+        float xv[32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) o[j] = ea * __uint_as_float(vo[j]) + __uint_as_float(vd[j]);
-        // the state-space part alone (without the D x skip) is kept for backward: d a_t needs
-        // sum_p dy (y - D x), which would cancel catastrophically if formed from the rounded y
-        if (ri < valid) {
-          bf16* dst2 = out2 + (row_base + ri) * ldo + h * kP + p0;
+        for (int q = 0; q < 4; ++q)
+          unpack8(*reinterpret_cast<const bf16x8*>(sV + vrow * 128 + ((((p0 >> 3) + q) ^ (vrow & 7)) << 4)), xv + 8 * q);
+        float o[32];
+        if (!BWD) {
 #pragma unroll
-          for (int q = 0; q < 4; ++q) st8(dst2 + 8 * q, pack8(o + 8 * q));
-        }
+          for (int j = 0; j < 32; ++j) o[j] = ea * __uint_as_float(vo[j]) + __uint_as_float(vd[j]);
+          if (ri < valid) {  // y_ssm = y - D x is kept for backward (see ssd_bwd_finalize)
+            bf16* dst2 = out2 + (row_base + ri) * ldo + h * kP + p0;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) o[j] += Dh * xv[j];
-      } else {
-        const float dt_i = s_dt[ri];
-        const float el = __expf(s_a[kL - 1] - a_i);
-        const float w = el * dt_i;
-        float s1 = 0.f, s2 = 0.f, sd = 0.f;
-        if (ri < valid) {
-          const bf16* xr = xsrc + (row_base + ri) * ldx + h * kP + p0;
+            for (int q = 0; q < 4; ++q) st8(dst2 + 8 * q, pack8(o + 8 * q));
+          }
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            float xx[8];
-            unpack8(ld8(xr + 8 * q), xx);
+          for (int j = 0; j < 32; ++j) o[j] += Dh * xv[j];
+        } else {
+          if (ri < valid) {
+            const bf16* xr = xsrc + (row_base + ri) * ldx + h * kP + p0;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              s1 += xx[j] * __uint_as_float(vd[8 * q + j]);
-              s2 += xx[j] * __uint_as_float(vo[8 * q + j]);
-              sd += xx[j] * xv[8 * q + j];  // dD_h = sum dy . x
+            for (int q = 0; q < 4; ++q) {
+              float xx[8];
+              unpack8(ld8(xr + 8 * q), xx);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                s1 += xx[j] * __uint_as_float(vd[8 * q + j]);
+                s2 += xx[j] * __uint_as_float(vo[8 * q + j]);
+                sd += xx[j] * xv[8 * q + j];  // dD_h = sum dy . x
+              }
             }
           }
-          atomicAdd(ddt1 + sbase + ri, s1);
-          atomicAdd(ddt2 + sbase + ri, el * s2);
+          const float w = el * dt_i;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) o[j] = dt_i * __uint_as_float(vd[j]) + w * __uint_as_float(vo[j]) + Dh * xv[j];
+        }
+        if (ri < valid) {
+          bf16* dst = outp + (row_base + ri) * ldo + h * kP + p0;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) st8(dst + 8 * q, pack8(o + 8 * q));
+        }
+      }
+      if (BWD) {
+        if (ri < valid) {  // one thread owns a (b, c, h, row): plain stores, no pre-zeroing needed
+          ddt1[sbase + ri] = s1;
+          ddt2[sbase + ri] = el * s2;
+        } else if (ri < kL) {
+          ddt1[sbase + ri] = 0.f;
+          ddt2[sbase + ri] = 0.f;
         }
         sd = warp_sum(sd);
         if (lane == 0) atomicAdd(dD + h, sd);
-#pragma unroll
-        for (int j = 0; j < 32; ++j) o[j] = dt_i * __uint_as_float(vd[j]) + w * __uint_as_float(vo[j]) + Dh * xv[j];
       }
-      if (ri < valid) {
-        bf16* dst = outp + (row_base + ri) * ldo + h * kP + p0;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) st8(dst + 8 * q, pack8(o + 8 * q));
-      }
+      tc_fence_before();
+      mbar_arrive(&acc_empty[acc]);
+      TMARK("epi", hh, "epi_done");
+      if (hh + 2 < hgs) prefetch_head(hh + 2, et, 128);  // slot hh&1 is free: everything of head hh retired
     }
-    tc_fence_before();
-    __syncthreads();
+    cp_async_wait<0>();
+  } else if (lane == 0) {
+    // =================================== MMA issuer ===================================
+    const uint32_t r_addr = smem_u32(sR);
+    constexpr uint32_t idesc_off = make_idesc_bf16(128, kP, MAJOR_K, MAJOR_K);
+    constexpr uint32_t idesc_diag = make_idesc_bf16(128, kP, MAJOR_K, MAJOR_MN);
+    int unit = 0;
+    for (int hh = 0; hh < hgs; ++hh) {
+      const int acc = hh & 1;
+      if (hh >= 2) {
+        mbar_wait(&acc_empty[acc], ((hh >> 1) - 1) & 1);
+        mbar_wait(&tiles_full[acc], ((hh >> 1) - 1) & 1);
+      }
+      tc_fence_after();
+      const uint32_t tOff = tmem + 256 + acc * 128, tDiag = tOff + 64;
+      const uint32_t s_addr = smem_u32(sS0 + acc * kP * 2 * 128), v_addr = smem_u32(sV0 + acc * kL * 128);
+#pragma unroll
+      for (int k = 0; k < kN / 16; ++k)  // (C | B)[128 x 128] . (S_prev | dS)[64 x 128]^T
+        mma_bf16_ss(tOff, desc_kmajor(r_addr, 128, k >> 2, k & 3), desc_kmajor(s_addr, kP, k >> 2, k & 3), idesc_off,
+                    k > 0 ? 1u : 0u);
+      for (int half = 0; half < nhalves; ++half, ++unit) {
+        const int slot = unit & 1;
+        mbar_wait(&g_full[slot], (unit >> 1) & 1);
+        tc_fence_after();
+        const uint32_t g_addr = smem_u32(sG + slot * 32768);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)  // G half-tile [128 x 128] . V[128 x 64]
+          mma_bf16_ss(tDiag, desc_kmajor(g_addr, 128, k >> 2, k & 3), desc_mnmajor(v_addr, ncols, half * 8 + k),
+                      idesc_diag, (half > 0 || k > 0) ? 1u : 0u);
+        mma_commit(&g_empty[slot]);
+      }
+      mma_commit(&acc_full[acc]);
+    }
   }
-  if (warp == 0) tmem_dealloc(tmem, 512);
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 12) tmem_dealloc(tmem, 512);
+#ifdef MB_SSD_TIMING
+  if (tprint && tid == 0) {
+    const int n = min(g_tcount, 2048);
+    for (int i = 0; i < n; ++i) printf("T %d %d %c %lld\n", g_tmeta[i] >> 16, (g_tmeta[i] >> 8) & 255, (char)(g_tmeta[i] & 255), g_tlog[i]);
+    g_tcount = 0;
+  }
+#endif
 }
 
 static int pick_head_group(int heads_per_group) {
@@ -367,7 +478,7 @@ extern "C" int mb_ssd_chunk_scan_fwd(const void* Cm, const void* Bm, long long l
   static bool once = false;
   if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_scan_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kScanSmem)); once = true; }
   dim3 grid(B * nc * 2, H / hgs);
-  ssd_scan_kernel<false><<<grid, kThreads, kScanSmem, stream>>>((const bf16*)Cm, (const bf16*)Bm, ldbc, (const bf16*)x, ldx,
+  ssd_scan_kernel<false><<<grid, kScanThreads, kScanSmem, stream>>>((const bf16*)Cm, (const bf16*)Bm, ldbc, (const bf16*)x, ldx,
                                                                 (const bf16*)sprev_bf16, dt, a, D, (bf16*)y, ldy, (bf16*)y_ssm,
                                                                 nullptr, 0, nullptr, nullptr, nullptr, T, H, G, nc, hgs);
   return check_launch("ssd_chunk_scan_fwd");
@@ -375,7 +486,7 @@ extern "C" int mb_ssd_chunk_scan_fwd(const void* Cm, const void* Bm, long long l
 
 // dx[s,h,:] = dt_s sum_{t>=s} (B_s.C_t) exp(a_t - a_s) dy_t + exp(a_last - a_s) dt_s B_s dS^T + D_h dy_s
 // ddt1[s] += sum_p x (M-part / dt_s),  ddt2[s] += exp(a_last - a_s) sum_p x (B dS^T),  dD[h] += sum dy.x
-// (ddt1, ddt2, dD are pre-zeroed by the caller)
+// (dD is pre-zeroed by the caller; ddt1 / ddt2 are fully overwritten)
 extern "C" int mb_ssd_chunk_scan_bwd_dx(const void* Bm, const void* Cm, long long ldbc, const void* dy, long long lddy,
                                         const void* ds_bf16, const float* dt, const float* a, const float* D,
                                         void* dx, long long lddx, const void* x, long long ldx, float* ddt1,
@@ -387,7 +498,7 @@ extern "C" int mb_ssd_chunk_scan_bwd_dx(const void* Bm, const void* Cm, long lon
   static bool once = false;
   if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_scan_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kScanSmem)); once = true; }
   dim3 grid(B * nc * 2, H / hgs);
-  ssd_scan_kernel<true><<<grid, kThreads, kScanSmem, stream>>>((const bf16*)Bm, (const bf16*)Cm, ldbc, (const bf16*)dy, lddy,
+  ssd_scan_kernel<true><<<grid, kScanThreads, kScanSmem, stream>>>((const bf16*)Bm, (const bf16*)Cm, ldbc, (const bf16*)dy, lddy,
                                                                (const bf16*)ds_bf16, dt, a, D, (bf16*)dx, lddx, nullptr,
                                                                (const bf16*)x, ldx, ddt1, ddt2, dD, T, H, G, nc, hgs);
   return check_launch("ssd_chunk_scan_bwd_dx");

@@ -19,7 +19,8 @@ LIB_PATH = os.path.join(LIB_DIR, "libmamba_b200.so")
 
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-         "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-I", INCLUDE, "-I", CSRC]
+         "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-I", INCLUDE, "-I", CSRC] + \
+    os.environ.get("MB_NVCC_EXTRA", "").split()
 
 
 def _sources():
