@@ -1,0 +1,337 @@
+// K4 / K5 / K23: Mamba-1 selective scan (forward, backward) and the single-token state update.
+//
+// Replaces mamba_ssm's csrc/selective_scan CUDA kernels and the Triton selective_state_update
+// (SURVEY.md section 2.3 rows K4, K5, K23).  This is the literal-compatibility path: the
+// reference's `MambaConfig(d_model=768, vocab_size=50304)` builds Mamba-1 mixers.
+//
+//   h_t[d,n] = exp(dt_t[d] A[d,n]) h_{t-1}[d,n] + dt_t[d] B_t[n] u_t[d]
+//   y_t[d]   = (sum_n C_t[n] h_t[d,n] + D[d] u_t[d]) * silu(z_t[d]),   dt = softplus(delta + bias)
+//
+// Layout is channel-last ([B, T, Dn] activations, [B, T, N] for B/C, all possibly strided column
+// slices), N = 16.  No tensor-core content: a first-order recurrence.  Parallelisation: time is cut
+// into tiles of 64 tokens; one half-warp owns one channel of one (batch, tile) with one lane per
+// state n, so the state history of a tile lives in registers (needed by backward) and the sum
+// over n is four shuffles.  Tile-entry states come from a carry pass:
+//   fwd:  pass 1 per tile (decay product, local end state) -> sequential carry over tiles ->
+//         pass 2 per tile produces y (and keeps the tile-entry states for backward)
+//   bwd:  tiles in parallel using the stored entry states; the gradient flowing between tiles
+//         (dh at the tile boundary) is resolved with the same two-pass scheme in reverse.
+#include "common.cuh"
+#include "../include/mamba_b200.h"
+
+namespace mb {
+
+constexpr int kSN = 16;        // d_state
+constexpr int kSTile = 64;     // tokens per tile
+constexpr int kSChan = 8;      // channels per block (8 half-warps = 128 threads)
+
+struct SScanArgs {
+  const bf16* u; long long ldu;
+  const bf16* delta; long long ldd;
+  const float* A;               // [Dn, N]
+  const bf16* Bm; long long ldb;
+  const bf16* Cm; long long ldc;
+  const float* D;               // [Dn] or null
+  const bf16* z; long long ldz; // or null
+  const float* delta_bias;      // [Dn] or null
+  int Bsz, T, Dn, ntiles, softplus;
+};
+
+__device__ __forceinline__ float half_warp_sum(float v) {
+#pragma unroll
+  for (int o = 8; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// pass 1: per (b, tile, d, n): P = prod_t exp(dt_t A), S = local end state from zero
+__global__ void __launch_bounds__(kSChan * kSN)
+sscan_local_kernel(SScanArgs a, float* __restrict__ P, float* __restrict__ S) {
+  const int n = threadIdx.x & (kSN - 1), dl = threadIdx.x >> 4;
+  const int d = blockIdx.x * kSChan + dl;
+  const int tile = blockIdx.y, b = blockIdx.z;
+  if (d >= a.Dn) return;
+  const float An = a.A[d * kSN + n];
+  const float bias = a.delta_bias ? a.delta_bias[d] : 0.f;
+  const int t0 = tile * kSTile, t1 = min(t0 + kSTile, a.T);
+  float h = 0.f, lp = 0.f;
+  for (int t = t0; t < t1; ++t) {
+    const size_t row = (size_t)b * a.T + t;
+    float dt = __bfloat162float(a.delta[row * a.ldd + d]) + bias;
+    if (a.softplus) dt = softplus_f(dt);
+    const float uu = __bfloat162float(a.u[row * a.ldu + d]);
+    const float Bn = __bfloat162float(a.Bm[row * a.ldb + n]);
+    const float la = dt * An;
+    lp += la;
+    h = __expf(la) * h + dt * Bn * uu;
+  }
+  const size_t o = (((size_t)b * a.ntiles + tile) * a.Dn + d) * kSN + n;
+  P[o] = lp;  // log of the decay product (kept in log space: no underflow surprises)
+  S[o] = h;
+}
+
+// carry: hin[tile] = state entering the tile  (forward order), one thread per (b, d, n)
+__global__ void sscan_carry_fwd_kernel(const float* __restrict__ P, const float* __restrict__ S, float* __restrict__ hin,
+                                       int Bsz, int ntiles, int DnN) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Bsz * DnN) return;
+  const int b = i / DnN, e = i % DnN;
+  float h = 0.f;
+  for (int c = 0; c < ntiles; ++c) {
+    const size_t o = ((size_t)b * ntiles + c) * DnN + e;
+    hin[o] = h;
+    h = __expf(P[o]) * h + S[o];
+  }
+}
+
+// pass 2: output.  One half-warp per channel, lane = n.
+__global__ void __launch_bounds__(kSChan * kSN)
+sscan_fwd_kernel(SScanArgs a, const float* __restrict__ hin, bf16* __restrict__ y, long long ldy) {
+  const int n = threadIdx.x & (kSN - 1), dl = threadIdx.x >> 4;
+  const int d = blockIdx.x * kSChan + dl;
+  const int tile = blockIdx.y, b = blockIdx.z;
+  if (d >= a.Dn) return;
+  const float An = a.A[d * kSN + n];
+  const float bias = a.delta_bias ? a.delta_bias[d] : 0.f;
+  const float Dd = a.D ? a.D[d] : 0.f;
+  const int t0 = tile * kSTile, t1 = min(t0 + kSTile, a.T);
+  float h = hin[(((size_t)b * a.ntiles + tile) * a.Dn + d) * kSN + n];
+  for (int t = t0; t < t1; ++t) {
+    const size_t row = (size_t)b * a.T + t;
+    float dt = __bfloat162float(a.delta[row * a.ldd + d]) + bias;
+    if (a.softplus) dt = softplus_f(dt);
+    const float uu = __bfloat162float(a.u[row * a.ldu + d]);
+    const float Bn = __bfloat162float(a.Bm[row * a.ldb + n]);
+    const float Cn = __bfloat162float(a.Cm[row * a.ldc + n]);
+    h = __expf(dt * An) * h + dt * Bn * uu;
+    float yy = half_warp_sum(Cn * h);
+    if (n == 0) {
+      yy += Dd * uu;
+      if (a.z) yy *= silu_f(__bfloat162float(a.z[row * a.ldz + d]));
+      y[row * ldy + d] = __float2bfloat16(yy);
+    }
+  }
+}
+
+// Backward, pass 1: per tile, with dh entering from the right assumed zero, compute the local
+// gradient that leaves the tile on the left: G = dh_{t0-1 <- tile} and the decay product (log).
+// Needs only C, dy, z, dt: dh_{t} = C_t dyy_t + exp(dt_{t+1} A) dh_{t+1}.
+__global__ void __launch_bounds__(kSChan * kSN)
+sscan_bwd_local_kernel(SScanArgs a, const bf16* __restrict__ dy, long long lddy, const float* __restrict__ hin,
+                       float* __restrict__ Gl) {
+  const int n = threadIdx.x & (kSN - 1), dl = threadIdx.x >> 4;
+  const int d = blockIdx.x * kSChan + dl;
+  const int tile = blockIdx.y, b = blockIdx.z;
+  if (d >= a.Dn) return;
+  const float An = a.A[d * kSN + n];
+  const float bias = a.delta_bias ? a.delta_bias[d] : 0.f;
+  const float Dd = a.D ? a.D[d] : 0.f;
+  const int t0 = tile * kSTile, t1 = min(t0 + kSTile, a.T);
+  // gradient w.r.t. the state *entering* the tile, from the tile's own outputs only
+  float g = 0.f;  // dL/dh_t accumulated right-to-left
+  for (int t = t1 - 1; t >= t0; --t) {
+    const size_t row = (size_t)b * a.T + t;
+    float dt = __bfloat162float(a.delta[row * a.ldd + d]) + bias;
+    if (a.softplus) dt = softplus_f(dt);
+    float dyy = __bfloat162float(dy[row * lddy + d]);
+    if (a.z) {
+      // y = (ssm + D u) * silu(z): the part flowing into the SSM output is dy * silu(z)
+      dyy *= silu_f(__bfloat162float(a.z[row * a.ldz + d]));
+    }
+    const float Cn = __bfloat162float(a.Cm[row * a.ldc + n]);
+    g = (g + Cn * dyy) * __expf(dt * An);  // after this line g = dL/dh_{t-1} contribution through h_t
+  }
+  (void)Dd;
+  Gl[(((size_t)b * a.ntiles + tile) * a.Dn + d) * kSN + n] = g;
+}
+
+// reverse carry: gin[tile] = dL/dh at the tile's right boundary (gradient w.r.t. the state leaving
+// the tile), given each tile's local left-going gradient and decay product.
+__global__ void sscan_carry_bwd_kernel(const float* __restrict__ P, const float* __restrict__ Gl, float* __restrict__ gin,
+                                       int Bsz, int ntiles, int DnN) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Bsz * DnN) return;
+  const int b = i / DnN, e = i % DnN;
+  float g = 0.f;  // gradient w.r.t. the state leaving the last tile = 0
+  for (int c = ntiles - 1; c >= 0; --c) {
+    const size_t o = ((size_t)b * ntiles + c) * DnN + e;
+    gin[o] = g;
+    g = Gl[o] + __expf(P[o]) * g;  // gradient w.r.t. the state entering tile c
+  }
+}
+
+// Backward, pass 2: everything.  Recomputes the tile's states from hin (kept in registers), then
+// walks right-to-left starting from gin.
+__global__ void __launch_bounds__(kSChan * kSN)
+sscan_bwd_kernel(SScanArgs a, const bf16* __restrict__ dy, long long lddy, const float* __restrict__ hin,
+                 const float* __restrict__ gin, bf16* __restrict__ du, long long lddu, bf16* __restrict__ ddelta,
+                 long long lddd, float* __restrict__ dA, float* __restrict__ dBf, float* __restrict__ dCf,
+                 float* __restrict__ dD, bf16* __restrict__ dz, long long lddz, float* __restrict__ dbias) {
+  const int n = threadIdx.x & (kSN - 1), dl = threadIdx.x >> 4;
+  const int d = blockIdx.x * kSChan + dl;
+  const int tile = blockIdx.y, b = blockIdx.z;
+  if (d >= a.Dn) return;
+  const float An = a.A[d * kSN + n];
+  const float bias = a.delta_bias ? a.delta_bias[d] : 0.f;
+  const float Dd = a.D ? a.D[d] : 0.f;
+  const int t0 = tile * kSTile, t1 = min(t0 + kSTile, a.T);
+  const size_t o = (((size_t)b * a.ntiles + tile) * a.Dn + d) * kSN + n;
+  float hist[kSTile + 1];
+  hist[0] = hin[o];
+#pragma unroll
+  for (int i = 0; i < kSTile; ++i) {
+    const int t = t0 + i;
+    float h = hist[i];
+    if (t < t1) {
+      const size_t row = (size_t)b * a.T + t;
+      float dt = __bfloat162float(a.delta[row * a.ldd + d]) + bias;
+      if (a.softplus) dt = softplus_f(dt);
+      const float uu = __bfloat162float(a.u[row * a.ldu + d]);
+      const float Bn = __bfloat162float(a.Bm[row * a.ldb + n]);
+      h = __expf(dt * An) * h + dt * Bn * uu;
+    }
+    hist[i + 1] = h;
+  }
+  float g = gin[o];  // dL/dh_{t1-1} coming from the right
+  float dA_acc = 0.f, dD_acc = 0.f, db_acc = 0.f;
+#pragma unroll
+  for (int i = kSTile - 1; i >= 0; --i) {
+    const int t = t0 + i;
+    if (t < t1) {
+      const size_t row = (size_t)b * a.T + t;
+      const float raw = __bfloat162float(a.delta[row * a.ldd + d]) + bias;
+      const float dt = a.softplus ? softplus_f(raw) : raw;
+      const float uu = __bfloat162float(a.u[row * a.ldu + d]);
+      const float Bn = __bfloat162float(a.Bm[row * a.ldb + n]);
+      const float Cn = __bfloat162float(a.Cm[row * a.ldc + n]);
+      const float dyv = __bfloat162float(dy[row * lddy + d]);
+      float sz = 1.f, dsz = 0.f, zz = 0.f;
+      if (a.z) { zz = __bfloat162float(a.z[row * a.ldz + d]); silu_both(zz, sz, dsz); }
+      const float dyy = dyv * sz;                         // gradient into (ssm + D u)
+      const float h_t = hist[i + 1], h_prev = hist[i];
+      const float ssm = half_warp_sum(Cn * h_t);
+      g += Cn * dyy;                                      // dL/dh_t (total)
+      const float dec = __expf(dt * An);
+      // contributions of this step
+      const float ddt_n = g * (An * dec * h_prev + Bn * uu);
+      const float du_n = g * dt * Bn;
+      const float ddt = half_warp_sum(ddt_n);
+      const float duu = half_warp_sum(du_n);
+      dA_acc += g * dt * dec * h_prev;
+      atomicAdd(dBf + row * kSN + n, g * dt * uu);        // summed over channels d
+      atomicAdd(dCf + row * kSN + n, dyy * h_t);
+      if (n == 0) {
+        const float draw = a.softplus ? ddt * sigmoid_f(raw) : ddt;
+        ddelta[row * lddd + d] = __float2bfloat16(draw);
+        db_acc += draw;
+        du[row * lddu + d] = __float2bfloat16(duu + Dd * dyy);
+        dD_acc += dyy * uu;
+        if (a.z) dz[row * lddz + d] = __float2bfloat16(dyv * (ssm + Dd * uu) * dsz);
+      }
+      g *= dec;                                           // becomes dL/dh_{t-1} through h_t
+    }
+  }
+  atomicAdd(dA + d * kSN + n, dA_acc);
+  if (n == 0) {
+    if (dD) atomicAdd(dD + d, dD_acc);
+    if (dbias) atomicAdd(dbias + d, db_acc);
+  }
+}
+
+// K23: single-token update.  state [B, Dn, N] fp32 in place; one half-warp per (b, d).
+__global__ void sscan_update_kernel(float* __restrict__ state, const bf16* __restrict__ x, long long ldx,
+                                    const bf16* __restrict__ delta, long long ldd, const float* __restrict__ A,
+                                    const bf16* __restrict__ Bm, long long ldb, const bf16* __restrict__ Cm, long long ldc,
+                                    const float* __restrict__ D, const bf16* __restrict__ z, long long ldz,
+                                    const float* __restrict__ bias, bf16* __restrict__ y, long long ldy, int Bsz, int Dn,
+                                    int softplus) {
+  const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int n = gid & (kSN - 1), bd = gid >> 4;
+  if (bd >= Bsz * Dn) return;
+  const int b = bd / Dn, d = bd % Dn;
+  float dt = __bfloat162float(delta[(size_t)b * ldd + d]) + (bias ? bias[d] : 0.f);
+  if (softplus) dt = softplus_f(dt);
+  const float uu = __bfloat162float(x[(size_t)b * ldx + d]);
+  float h = state[(size_t)bd * kSN + n];
+  h = __expf(dt * A[d * kSN + n]) * h + dt * __bfloat162float(Bm[(size_t)b * ldb + n]) * uu;
+  state[(size_t)bd * kSN + n] = h;
+  float yy = half_warp_sum(__bfloat162float(Cm[(size_t)b * ldc + n]) * h);
+  if (n == 0) {
+    if (D) yy += D[d] * uu;
+    if (z) yy *= silu_f(__bfloat162float(z[(size_t)b * ldz + d]));
+    y[(size_t)b * ldy + d] = __float2bfloat16(yy);
+  }
+}
+
+static SScanArgs make_args(const void* u, long long ldu, const void* delta, long long ldd, const float* A,
+                           const void* Bm, long long ldb, const void* Cm, long long ldc, const float* D, const void* z,
+                           long long ldz, const float* bias, int Bsz, int T, int Dn, int softplus) {
+  SScanArgs a;
+  a.u = (const bf16*)u; a.ldu = ldu; a.delta = (const bf16*)delta; a.ldd = ldd; a.A = A;
+  a.Bm = (const bf16*)Bm; a.ldb = ldb; a.Cm = (const bf16*)Cm; a.ldc = ldc; a.D = D;
+  a.z = (const bf16*)z; a.ldz = ldz; a.delta_bias = bias;
+  a.Bsz = Bsz; a.T = T; a.Dn = Dn; a.ntiles = cdiv(T, kSTile); a.softplus = softplus;
+  return a;
+}
+
+}  // namespace mb
+using namespace mb;
+
+// scratch layout (fp32): P | S | hin, each [B, ntiles, Dn, N]
+extern "C" long long mb_sscan_scratch_floats(int B, int T, int Dn, int N) {
+  return 3ll * B * cdiv(T, kSTile) * Dn * N;
+}
+
+extern "C" int mb_sscan_fwd(const void* u, long long ldu, const void* delta, long long ldd, const float* A,
+                            const void* Bm, long long ldb, const void* Cm, long long ldc, const float* D,
+                            const void* z, long long ldz, const float* delta_bias, void* y, long long ldy,
+                            float* scratch, int B, int T, int Dn, int N, int softplus, cudaStream_t stream) {
+  MB_REQUIRE(N == kSN, "sscan: d_state must be %d (got %d)", kSN, N);
+  if (B * T * Dn == 0) return 0;
+  SScanArgs a = make_args(u, ldu, delta, ldd, A, Bm, ldb, Cm, ldc, D, z, ldz, delta_bias, B, T, Dn, softplus);
+  const size_t one = (size_t)B * a.ntiles * Dn * N;
+  float *P = scratch, *S = scratch + one, *hin = scratch + 2 * one;
+  dim3 grid(cdiv(Dn, kSChan), a.ntiles, B);
+  sscan_local_kernel<<<grid, kSChan * kSN, 0, stream>>>(a, P, S);
+  if (check_launch("sscan_fwd/local")) return 1;
+  sscan_carry_fwd_kernel<<<cdiv((long long)B * Dn * N, 256), 256, 0, stream>>>(P, S, hin, B, a.ntiles, Dn * N);
+  if (check_launch("sscan_fwd/carry")) return 1;
+  sscan_fwd_kernel<<<grid, kSChan * kSN, 0, stream>>>(a, hin, (bf16*)y, ldy);
+  return check_launch("sscan_fwd");
+}
+
+// scratch: the forward's P | S | hin must be passed back unchanged; `scratch2` (2 x [B,ntiles,Dn,N]) is
+// workspace.  dA [Dn,N], dB/dC fp32 [B*T, N], dD [Dn], dbias [Dn] are ACCUMULATED into (pre-zero them).
+extern "C" int mb_sscan_bwd(const void* u, long long ldu, const void* delta, long long ldd, const float* A,
+                            const void* Bm, long long ldb, const void* Cm, long long ldc, const float* D,
+                            const void* z, long long ldz, const float* delta_bias, const void* dy, long long lddy,
+                            const float* scratch, float* scratch2, void* du, long long lddu, void* ddelta,
+                            long long lddd, float* dA, float* dB, float* dC, float* dD, void* dz, long long lddz,
+                            float* dbias, int B, int T, int Dn, int N, int softplus, cudaStream_t stream) {
+  MB_REQUIRE(N == kSN, "sscan: d_state must be %d (got %d)", kSN, N);
+  if (B * T * Dn == 0) return 0;
+  SScanArgs a = make_args(u, ldu, delta, ldd, A, Bm, ldb, Cm, ldc, D, z, ldz, delta_bias, B, T, Dn, softplus);
+  const size_t one = (size_t)B * a.ntiles * Dn * N;
+  const float *P = scratch, *hin = scratch + 2 * one;
+  float *Gl = scratch2, *gin = scratch2 + one;
+  dim3 grid(cdiv(Dn, kSChan), a.ntiles, B);
+  sscan_bwd_local_kernel<<<grid, kSChan * kSN, 0, stream>>>(a, (const bf16*)dy, lddy, hin, Gl);
+  if (check_launch("sscan_bwd/local")) return 1;
+  sscan_carry_bwd_kernel<<<cdiv((long long)B * Dn * N, 256), 256, 0, stream>>>(P, Gl, gin, B, a.ntiles, Dn * N);
+  if (check_launch("sscan_bwd/carry")) return 1;
+  sscan_bwd_kernel<<<grid, kSChan * kSN, 0, stream>>>(a, (const bf16*)dy, lddy, hin, gin, (bf16*)du, lddu, (bf16*)ddelta,
+                                                      lddd, dA, dB, dC, dD, (bf16*)dz, lddz, dbias);
+  return check_launch("sscan_bwd");
+}
+
+extern "C" int mb_sscan_update(float* state, const void* x, long long ldx, const void* delta, long long ldd,
+                               const float* A, const void* Bm, long long ldb, const void* Cm, long long ldc,
+                               const float* D, const void* z, long long ldz, const float* delta_bias, void* y,
+                               long long ldy, int B, int Dn, int N, int softplus, cudaStream_t stream) {
+  MB_REQUIRE(N == kSN, "sscan_update: d_state must be %d (got %d)", kSN, N);
+  if (B * Dn == 0) return 0;
+  const long long threads = (long long)B * Dn * kSN;
+  sscan_update_kernel<<<cdiv(threads, 256), 256, 0, stream>>>(state, (const bf16*)x, ldx, (const bf16*)delta, ldd, A,
+                                                             (const bf16*)Bm, ldb, (const bf16*)Cm, ldc, D, (const bf16*)z,
+                                                             ldz, delta_bias, (bf16*)y, ldy, B, Dn, softplus);
+  return check_launch("sscan_update");
+}

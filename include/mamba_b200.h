@@ -116,6 +116,26 @@ int mb_ssd_bwd_finalize(const void* dy, long long lddy, const void* y_ssm, long 
                         void* draw_out, long long ld_draw, float* dA_log, float* ddt_bias, int B, int T, int H,
                         int P, int L, cudaStream_t stream);
 
+/* ---- K4 / K5 / K23: Mamba-1 selective scan fwd / bwd / single-token update (mamba_ssm
+ * csrc/selective_scan + Triton selective_state_update), channel-last, d_state = 16.
+ * fwd scratch: mb_sscan_scratch_floats() floats, must be handed back unchanged to bwd; bwd scratch2:
+ * two thirds of that.  dA, dB, dC (fp32 [B*T, N]), dD, dbias are accumulated into: pre-zero them. */
+long long mb_sscan_scratch_floats(int B, int T, int Dn, int N);
+int mb_sscan_fwd(const void* u, long long ldu, const void* delta, long long ldd, const float* A,
+                 const void* Bm, long long ldb, const void* Cm, long long ldc, const float* D,
+                 const void* z, long long ldz, const float* delta_bias, void* y, long long ldy,
+                 float* scratch, int B, int T, int Dn, int N, int softplus, cudaStream_t stream);
+int mb_sscan_bwd(const void* u, long long ldu, const void* delta, long long ldd, const float* A,
+                 const void* Bm, long long ldb, const void* Cm, long long ldc, const float* D,
+                 const void* z, long long ldz, const float* delta_bias, const void* dy, long long lddy,
+                 const float* scratch, float* scratch2, void* du, long long lddu, void* ddelta,
+                 long long lddd, float* dA, float* dB, float* dC, float* dD, void* dz, long long lddz,
+                 float* dbias, int B, int T, int Dn, int N, int softplus, cudaStream_t stream);
+int mb_sscan_update(float* state, const void* x, long long ldx, const void* delta, long long ldd,
+                    const float* A, const void* Bm, long long ldb, const void* Cm, long long ldc,
+                    const float* D, const void* z, long long ldz, const float* delta_bias, void* y,
+                    long long ldy, int B, int Dn, int N, int softplus, cudaStream_t stream);
+
 /* ---- K19-K21: gradient reduce-scatter + global-norm clip + sharded AdamW + bf16 parameter
  * all-gather over NVLink peer memory (replaces DDP's NCCL all-reduce, clip_grad_norm_ and
  * torch.optim.AdamW of /root/reference/train.py:86,219-227).  *_ptrs are HOST arrays of `world`
