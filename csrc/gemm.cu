@@ -17,6 +17,7 @@
 // tile i+1.  Out-of-bounds rows / columns / K are zero-filled by TMA and predicated on store,
 // so ragged shapes (N = 3352, K = 48, ...) need no padding copies.
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "ptx.cuh"
@@ -29,6 +30,18 @@ constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int kGemmThreads = 192;
 
+// Tile rasterisation.  With few N tiles (dgrad: N = d_model) consecutive CTAs take all N tiles of
+// one M block, so the large A operand (activations / gradients, > L2) is streamed from HBM once;
+// with many N tiles consecutive CTAs share one N tile (the weight tile) and A (which then fits in
+// L2) is re-read from L2.
+__device__ __forceinline__ void decode_tile(int tile, int tiles_m, int tiles_n, int& m_blk, int& n_blk, int& split) {
+  const int per_split = tiles_m * tiles_n;
+  split = tile / per_split;
+  const int t = tile - split * per_split;
+  if (tiles_n <= 8) { m_blk = t / tiles_n; n_blk = t - m_blk * tiles_n; }
+  else { n_blk = t / tiles_m; m_blk = t - n_blk * tiles_m; }
+}
+
 enum { EPI_BF16 = 0, EPI_F32 = 1, EPI_F32_ATOMIC = 2 };
 
 template <int BN>
@@ -40,7 +53,12 @@ struct GemmCfg {
   static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + STAGING + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
-template <int BN, uint32_t A_MAJOR, uint32_t B_MAJOR, int EPI, bool TMA_STORE>
+// MC = true: launched as clusters of 2 CTAs that work on two vertically adjacent output tiles
+// (same N block).  Each CTA TMA-loads its own A tile and HALF of the shared B tile, multicast to
+// both CTAs, which cuts L2->SM operand traffic per tile from 48 KB to 32 KB per k-block (the
+// mainloop is L2-bandwidth bound otherwise: ncu showed 64 % tensor-pipe activity at 148 x 48 KB
+// per 512 clk).  Stage release needs both CTAs' MMA commits (multicast commit, count 2).
+template <int BN, uint32_t A_MAJOR, uint32_t B_MAJOR, int EPI, bool TMA_STORE, bool MC>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmD, void* __restrict__ Dout, const float* __restrict__ bias, int Mg, int Ng, int Kg,
@@ -60,15 +78,20 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int tiles_m = (Mg + BM - 1) / BM, tiles_n = (Ng + BN - 1) / BN;
+  const int tiles_m_real = (Mg + BM - 1) / BM, tiles_n = (Ng + BN - 1) / BN;
+  // with MC the scheduler hands out PAIRS of M blocks to a cluster; CTA `crank` takes block 2*pm + crank
+  const int tiles_m = MC ? (tiles_m_real + 1) / 2 : tiles_m_real;
   const int num_tiles = tiles_m * tiles_n * splitk;
   const int kblocks = (Kg + BK - 1) / BK;
+  const int crank = MC ? (int)cluster_ctarank() : 0;
+  const int worker = MC ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int nworkers = MC ? (int)(gridDim.x >> 1) : (int)gridDim.x;
 
   if (warp == 0 && lane == 0) {
     prefetch_tensormap(&tmA);
     prefetch_tensormap(&tmB);
     if (TMA_STORE) prefetch_tensormap(&tmD);
-    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], MC ? 2 : 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 4); }
     fence_mbar_init();
   }
@@ -78,6 +101,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
   tc_fence_before();
   __syncthreads();
+  if (MC) cluster_sync_all();  // the peer's barriers exist before anything is multicast into them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -86,11 +110,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        int t = tile;
-        const int m_blk = t % tiles_m; t /= tiles_m;
-        const int n_blk = t % tiles_n;
-        const int split = t / tiles_n;
+      for (int tile = worker; tile < num_tiles; tile += nworkers) {
+        int m_blk, n_blk, split;
+        decode_tile(tile, tiles_m, tiles_n, m_blk, n_blk, split);
+        if (MC) m_blk = 2 * m_blk + crank;
         const int kb0 = split * kb_per_split;
         const int kb1 = min(kb0 + kb_per_split, kblocks);
         for (int kb = kb0; kb < kb1; ++kb) {
@@ -105,12 +128,26 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             for (int j = 0; j < BM / 64; ++j)
               tma_load_2d(a_dst + j * (BK * 128), &tmA, &full_bar[stage], m_blk * BM + j * 64, kb * BK);
           }
-          if (B_MAJOR == MAJOR_K) {
-            tma_load_2d(b_dst, &tmB, &full_bar[stage], kb * BK, n_blk * BN);
-          } else {
+          if (!MC) {
+            if (B_MAJOR == MAJOR_K) {
+              tma_load_2d(b_dst, &tmB, &full_bar[stage], kb * BK, n_blk * BN);
+            } else {
 #pragma unroll
-            for (int j = 0; j < BN / 64; ++j)
-              tma_load_2d(b_dst + j * (BK * 128), &tmB, &full_bar[stage], n_blk * BN + j * 64, kb * BK);
+              for (int j = 0; j < BN / 64; ++j)
+                tma_load_2d(b_dst + j * (BK * 128), &tmB, &full_bar[stage], n_blk * BN + j * 64, kb * BK);
+            }
+          } else {
+            // this CTA fetches half of the B tile and multicasts it into both CTAs' stage
+            if (B_MAJOR == MAJOR_K) {
+              tma_load_2d_mc(b_dst + crank * (BN / 2) * 128, &tmB, &full_bar[stage], kb * BK,
+                             n_blk * BN + crank * (BN / 2), 0b11);
+            } else {
+#pragma unroll
+              for (int j = 0; j < BN / 128; ++j) {
+                const int atom = crank * (BN / 128) + j;
+                tma_load_2d_mc(b_dst + atom * (BK * 128), &tmB, &full_bar[stage], n_blk * BN + atom * 64, kb * BK, 0b11);
+              }
+            }
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -128,7 +165,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       int stage = 0;
       uint32_t phase = 0;
       int local = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
+      for (int tile = worker; tile < num_tiles; tile += nworkers, ++local) {
         const int split = tile / (tiles_m * tiles_n);
         const int kb0 = split * kb_per_split;
         const int kb1 = min(kb0 + kb_per_split, kblocks);
@@ -148,7 +185,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const uint64_t db = make_smem_desc(b_addr + k * b_kstep, b_lbo, 1024);
             mma_bf16_ss(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
-          mma_commit(&empty_bar[stage]);  // frees this smem stage when the MMAs above retire
+          // frees this smem stage when the MMAs above retire (in BOTH CTAs with MC: the peer's
+          // producer multicasts into our stage too)
+          if (MC) mma_commit_mc(&empty_bar[stage], 0b11); else mma_commit(&empty_bar[stage]);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
         mma_commit(&tfull_bar[acc]);  // accumulator complete -> epilogue
@@ -159,10 +198,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int lane_grp = warp & 3;  // TMEM lanes [32*lane_grp, +32) are the ones this warp may read
     int local = 0;
     int st_iter = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
-      int t = tile;
-      const int m_blk = t % tiles_m; t /= tiles_m;
-      const int n_blk = t % tiles_n;
+    for (int tile = worker; tile < num_tiles; tile += nworkers, ++local) {
+      int m_blk, n_blk, split_unused;
+      decode_tile(tile, tiles_m, tiles_n, m_blk, n_blk, split_unused);
+      if (MC) m_blk = 2 * m_blk + crank;
       const int acc = local & 1;
       const uint32_t acc_phase = (local >> 1) & 1;
       mbar_wait(&tfull_bar[acc], acc_phase);
@@ -273,6 +312,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
   tc_fence_before();
   __syncthreads();
+  if (MC) cluster_sync_all();  // no CTA leaves while its peer may still signal / write into it
   if (warp == 1) tmem_dealloc(tmem_base, 2 * BN);
 }
 
@@ -326,25 +366,54 @@ int make_tmap_bf16_2d(CUtensorMap* map, const void* ptr, long long rows, long lo
   return 0;
 }
 
-template <int BN, uint32_t AM, uint32_t BMJ, int EPI, bool TS>
-static int launch_gemm_ts(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, void* D,
+template <int BN, uint32_t AM, uint32_t BMJ, int EPI, bool TS, bool MC>
+static int launch_gemm_mc(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, void* D,
                           const float* bias, int M, int N, int K, long long ldd, int splitk, int kb_per_split,
                           float alpha, cudaStream_t stream) {
-  auto kern = gemm_bf16_kernel<BN, AM, BMJ, EPI, TS>;
+  auto kern = gemm_bf16_kernel<BN, AM, BMJ, EPI, TS, MC>;
   static bool attr_set = false;
   if (!attr_set) {
     MB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<BN>::SMEM));
     attr_set = true;
   }
-  const int tiles = cdiv(M, BM) * cdiv(N, BN) * splitk;
-  const int grid = tiles < num_sms() ? tiles : num_sms();
-  kern<<<grid, kGemmThreads, GemmCfg<BN>::SMEM, stream>>>(ta, tb, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha);
+  const int tiles_m = MC ? (cdiv(M, BM) + 1) / 2 : cdiv(M, BM);
+  const int tiles = tiles_m * cdiv(N, BN) * splitk;       // pairs of tiles when MC
+  int grid = MC ? 2 * (tiles < num_sms() / 2 ? tiles : num_sms() / 2) : (tiles < num_sms() ? tiles : num_sms());
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = GemmCfg<BN>::SMEM;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = MC ? 2 : 1;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  MB_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha));
   return check_launch("gemm_bf16");
 }
 
+static bool use_multicast() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("MAMBA_B200_GEMM_MULTICAST"); v = (e == nullptr || e[0] != '0') ? 1 : 0; }
+  return v == 1;
+}
+
+template <int BN, uint32_t AM, uint32_t BMJ, int EPI, bool TS>
+static int launch_gemm_ts(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tb_half, const CUtensorMap& td,
+                          void* D, const float* bias, int M, int N, int K, long long ldd, int splitk, int kb_per_split,
+                          float alpha, cudaStream_t stream) {
+  if (use_multicast() && cdiv(M, BM) >= 2)
+    return launch_gemm_mc<BN, AM, BMJ, EPI, TS, true>(ta, tb_half, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha, stream);
+  return launch_gemm_mc<BN, AM, BMJ, EPI, TS, false>(ta, tb, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha, stream);
+}
+
 template <int BN, uint32_t AM, uint32_t BMJ, int EPI>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, void* D, const float* bias, int M, int N,
-                       int K, long long ldd, int splitk, int kb_per_split, float alpha, cudaStream_t stream) {
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tb_half, void* D,
+                       const float* bias, int M, int N, int K, long long ldd, int splitk, int kb_per_split,
+                       float alpha, cudaStream_t stream) {
   // stores go through TMA whenever the output satisfies its alignment rules; the additive
   // (wgrad) epilogue uses vector reductions straight from registers
   const bool ts = EPI != EPI_F32_ATOMIC && (EPI == EPI_BF16 ? (ldd % 8 == 0) : (ldd % 4 == 0));
@@ -352,20 +421,20 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, void* D, co
   if (ts) {
     if (EPI == EPI_BF16) { if (make_tmap_bf16_2d(&td, D, M, N, ldd, 32)) return 1; }
     else { if (make_tmap_f32_2d(&td, D, M, N, ldd)) return 1; }
-    return launch_gemm_ts<BN, AM, BMJ, EPI, (EPI != EPI_F32_ATOMIC)>(ta, tb, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha, stream);
+    return launch_gemm_ts<BN, AM, BMJ, EPI, (EPI != EPI_F32_ATOMIC)>(ta, tb, tb_half, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha, stream);
   }
   td = ta;
-  return launch_gemm_ts<BN, AM, BMJ, EPI, false>(ta, tb, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha, stream);
+  return launch_gemm_ts<BN, AM, BMJ, EPI, false>(ta, tb, tb_half, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha, stream);
 }
 
 template <int BN, int EPI>
-static int dispatch_major(int a_major, int b_major, const CUtensorMap& ta, const CUtensorMap& tb, void* D,
-                          const float* bias, int M, int N, int K, long long ldd, int splitk, int kbps, float alpha,
-                          cudaStream_t s) {
-  if (a_major == 0 && b_major == 0) return launch_gemm<BN, MAJOR_K, MAJOR_K, EPI>(ta, tb, D, bias, M, N, K, ldd, splitk, kbps, alpha, s);
-  if (a_major == 0 && b_major == 1) return launch_gemm<BN, MAJOR_K, MAJOR_MN, EPI>(ta, tb, D, bias, M, N, K, ldd, splitk, kbps, alpha, s);
-  if (a_major == 1 && b_major == 1) return launch_gemm<BN, MAJOR_MN, MAJOR_MN, EPI>(ta, tb, D, bias, M, N, K, ldd, splitk, kbps, alpha, s);
-  return launch_gemm<BN, MAJOR_MN, MAJOR_K, EPI>(ta, tb, D, bias, M, N, K, ldd, splitk, kbps, alpha, s);
+static int dispatch_major(int a_major, int b_major, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tbh,
+                          void* D, const float* bias, int M, int N, int K, long long ldd, int splitk, int kbps,
+                          float alpha, cudaStream_t s) {
+  if (a_major == 0 && b_major == 0) return launch_gemm<BN, MAJOR_K, MAJOR_K, EPI>(ta, tb, tbh, D, bias, M, N, K, ldd, splitk, kbps, alpha, s);
+  if (a_major == 0 && b_major == 1) return launch_gemm<BN, MAJOR_K, MAJOR_MN, EPI>(ta, tb, tbh, D, bias, M, N, K, ldd, splitk, kbps, alpha, s);
+  if (a_major == 1 && b_major == 1) return launch_gemm<BN, MAJOR_MN, MAJOR_MN, EPI>(ta, tb, tbh, D, bias, M, N, K, ldd, splitk, kbps, alpha, s);
+  return launch_gemm<BN, MAJOR_MN, MAJOR_K, EPI>(ta, tb, tbh, D, bias, M, N, K, ldd, splitk, kbps, alpha, s);
 }
 
 }  // namespace mb
@@ -384,11 +453,14 @@ extern "C" int mb_gemm_bf16(const void* A, long long lda, int a_major, const voi
   MB_REQUIRE(K > 0, "gemm: K must be positive");
   MB_REQUIRE(((uintptr_t)D & 15) == 0, "gemm: output must be 16-byte aligned");
   const int BN = N > 128 ? 256 : 128;
-  CUtensorMap ta, tb;
+  CUtensorMap ta, tb, tbh;
   if (a_major == 0) { if (make_tmap_bf16_2d(&ta, A, M, K, lda, BM)) return 1; }
   else { if (make_tmap_bf16_2d(&ta, A, K, M, lda, BK)) return 1; }
   if (b_major == 0) { if (make_tmap_bf16_2d(&tb, B, N, K, ldb, BN)) return 1; }
   else { if (make_tmap_bf16_2d(&tb, B, K, N, ldb, BK)) return 1; }
+  // half-height box of the K-major B tile for the multicast path (MN-major boxes are per 64-wide atom already)
+  if (b_major == 0) { if (make_tmap_bf16_2d(&tbh, B, N, K, ldb, BN / 2)) return 1; }
+  else tbh = tb;
   // split-K only where the epilogue is additive
   const int kblocks = cdiv(K, BK);
   int splitk = 1;
@@ -401,7 +473,7 @@ extern "C" int mb_gemm_bf16(const void* A, long long lda, int a_major, const voi
   }
   int kbps = cdiv(kblocks, splitk);
   splitk = cdiv(kblocks, kbps);
-#define GO(BN_, EPI_) return dispatch_major<BN_, EPI_>(a_major, b_major, ta, tb, D, bias, M, N, K, ldd, splitk, kbps, alpha, stream)
+#define GO(BN_, EPI_) return dispatch_major<BN_, EPI_>(a_major, b_major, ta, tb, tbh, D, bias, M, N, K, ldd, splitk, kbps, alpha, stream)
   if (BN == 256) {
     if (d_mode == 0) GO(256, EPI_BF16);
     if (d_mode == 1) GO(256, EPI_F32);
