@@ -222,6 +222,15 @@ def main():
     e1.record()
     barrier()
     launches = _lib.kernel_launches() - launches0
+    comm_t = None
+    if fused and getattr(wrapped, "symm", None) is not None:
+        t_ = wrapped.symm.last_timings()  # last timed step: device ms, this rank
+        if t_ is not None:
+            ct = torch.tensor([t_[0], t_[1]], device=device)
+            if ddp:
+                dist.all_reduce(ct, op=dist.ReduceOp.MAX)
+            comm_t = {"exposed_grad_reduce_scatter_ms": float(ct[0]), "clip_adamw_allgather_ms": float(ct[1]),
+                      "note": "device time on the comm stream after the end of backward; max over ranks"}
     ms = torch.tensor([e0.elapsed_time(e1)], device=device)
     if ddp:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
@@ -260,7 +269,7 @@ def main():
                        "optimizer": "AdamW(0.9,0.95) wd0.1 clip1.0, fp32 master + bf16 compute",
                        "l2": "per-step working set (activations, 1.1 GB grads, weights) >> 126 MB L2; no flush needed",
                        "comm": getattr(wrapped, "comm", "nccl-ddp")},
-            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
+            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "comm": comm_t,
             "loss_first": loss0, "loss_last": float(loss),
         }
         print(json.dumps(out))

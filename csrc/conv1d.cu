@@ -37,18 +37,16 @@ conv1d_fwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __rest
 #pragma unroll
   for (int k = 0; k < W - 1; ++k) {
     const int t = t0 - (W - 1) + k;
-    if (t >= 0) halo[k] = ld8(xb + (size_t)t * ldx);
-    else halo[k].v[0] = halo[k].v[1] = halo[k].v[2] = halo[k].v[3] = __floats2bfloat162_rn(0.f, 0.f);
+    halo[k] = ld8(xb + (size_t)max(t, 0) * ldx);
+    if (t < 0) halo[k].v[0] = halo[k].v[1] = halo[k].v[2] = halo[k].v[3] = __floats2bfloat162_rn(0.f, 0.f);
   }
   for (int tb = t0; tb < t1; tb += U) {
     bf16x8 raw[U + W - 1];
 #pragma unroll
     for (int k = 0; k < W - 1; ++k) raw[k] = halo[k];
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      if (tb + u < t1) raw[W - 1 + u] = ld8(xb + (size_t)(tb + u) * ldx);
-      else raw[W - 1 + u] = raw[W - 2 + u];
-    }
+    for (int u = 0; u < U; ++u)  // unconditional (clamped) loads: all U issue back to back
+      raw[W - 1 + u] = ld8(xb + (size_t)min(tb + u, T - 1) * ldx);
 #pragma unroll
     for (int k = 0; k < W - 1; ++k) halo[k] = raw[U + k];
     float acc[U][8];
@@ -82,21 +80,46 @@ conv1d_fwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __rest
   }
 }
 
-// Backward.  dw / dbias are accumulated with one fp32 atomic per (block, channel, tap).
+// Backward.  Each thread owns 4 channels (one 8-byte vector) and walks its token tile in register
+// batches of U tokens with everything statically indexed: the g = dy * silu'(pre) values and the x
+// rows a batch shares with the next one are carried in registers, so every x / dy row is loaded
+// once and no window is ever shifted.  dw / dbias: one fp32 atomic per (block, channel, tap).
+struct __align__(8) bf16x4 { bf162 v[2]; };
+__device__ __forceinline__ bf16x4 ld4(const bf16* p) {
+  const uint2 t = *reinterpret_cast<const uint2*>(p);
+  bf16x4 r;
+  memcpy(&r, &t, 8);
+  return r;
+}
+__device__ __forceinline__ void st4(bf16* p, const float* f) {
+  bf16x4 r;
+  r.v[0] = __floats2bfloat162_rn(f[0], f[1]);
+  r.v[1] = __floats2bfloat162_rn(f[2], f[3]);
+  uint2 t;
+  memcpy(&t, &r, 8);
+  *reinterpret_cast<uint2*>(p) = t;
+}
+__device__ __forceinline__ void unpack4(const bf16x4& p, float* f) {
+  const float2 a = __bfloat1622float2(p.v[0]), b = __bfloat1622float2(p.v[1]);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y;
+}
+
 template <int W, bool SILU>
 __global__ void __launch_bounds__(kConvThreads)
 conv1d_bwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __restrict__ w,
                   const float* __restrict__ bias, const bf16* __restrict__ dy, long long lddy,
                   bf16* __restrict__ dx, long long lddx, float* __restrict__ dw,
                   float* __restrict__ dbias, int T, int C) {
-  const int c0 = (blockIdx.x * kConvThreads + threadIdx.x) * 8;
+  constexpr int H = W - 1;  // halo
+  constexpr int U = 4;      // tokens per register batch
+  const int c0 = (blockIdx.x * kConvThreads + threadIdx.x) * 4;
   if (c0 >= C) return;
   const int b = blockIdx.z;
   const int t0 = blockIdx.y * kConvTile;
   const int t1 = min(t0 + kConvTile, T);
-  float wt[8][W], bs[8], dwa[8][W], dba[8];
+  float wt[4][W], bs[4], dwa[4][W], dba[4];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
+  for (int j = 0; j < 4; ++j) {
 #pragma unroll
     for (int k = 0; k < W; ++k) { wt[j][k] = w[(c0 + j) * W + k]; dwa[j][k] = 0.f; }
     bs[j] = bias != nullptr ? bias[c0 + j] : 0.f;
@@ -105,74 +128,92 @@ conv1d_bwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __rest
   const bf16* xb = x + ((size_t)b * T) * ldx + c0;
   const bf16* gb = dy + ((size_t)b * T) * lddy + c0;
   bf16* dxb = dx + ((size_t)b * T) * lddx + c0;
-  float win[W][8];  // x window ending at t
-  float gw[W][8];   // gw[k] = g[t - (W-1) + k]
+  // Branch-free: out-of-range rows read a clamped (valid) row and are zeroed by a select, so the
+  // compiler can issue a batch's loads back to back (a conditional load ends the basic block and
+  // each load would then pay its full latency in turn — ncu: 67 % long-scoreboard stalls).
+  auto load_x = [&](int t, float* f) {
+    const int tc = min(max(t, 0), T - 1);
+    unpack4(ld4(xb + (size_t)tc * ldx), f);
+    const float m = (t >= 0 && t < T) ? 1.f : 0.f;
+    f[0] *= m; f[1] *= m; f[2] *= m; f[3] *= m;
+  };
+  // g[t] = dy[t] * silu'(pre[t]) from the W x-rows ending at t; also this token's dw / db terms
+  auto make_g = [&](int t, const float (*xw)[4], const float* d4, float* g) {  // xw[k] = x[t - H + k]
+    const float live = t < T ? 1.f : 0.f, own = t < t1 ? 1.f : 0.f;
 #pragma unroll
-  for (int k = 0; k < W; ++k)
+    for (int j = 0; j < 4; ++j) {
+      float gg = d4[j] * live;
+      if (SILU) {
+        float a = bs[j];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { win[k][j] = 0.f; gw[k][j] = 0.f; }
-#pragma unroll
-  for (int k = 0; k < W - 1; ++k) {
-    const int t = t0 - (W - 1) + k;
-    if (t >= 0) unpack8(ld8(xb + (size_t)t * ldx), win[k + 1]);
-  }
-  const int tend = t1 + (W - 1);  // g of the W-1 tokens after the tile feeds dx of the tile's tail
-  constexpr int U = 8;
-  for (int tb = t0; tb < tend; tb += U) {
-    bf16x8 rx[U], rg[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u)
-      if (tb + u < tend && tb + u < T) {
-        rx[u] = ld8(xb + (size_t)(tb + u) * ldx);
-        rg[u] = ld8(gb + (size_t)(tb + u) * lddy);
+        for (int k = 0; k < W; ++k) a += wt[j][k] * xw[k][j];
+        gg *= dsilu_f(a);
       }
+      g[j] = gg;
+      const float go = gg * own;  // only the tile that owns token t accumulates its dw / db terms
+      dba[j] += go;
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int t = tb + u;
-      if (t >= tend) break;
+      for (int k = 0; k < W; ++k) dwa[j][k] += go * xw[k][j];
+    }
+  };
+  auto load_dy = [&](int t, float* f) { unpack4(ld4(gb + (size_t)min(t, T - 1) * lddy), f); };
+
+  // rows carried between batches: xr[0..H) = x[tb .. tb+H), gr[0..H) = g[tb .. tb+H)
+  float xr[H + U][4], gr[H + U][4];
+  {
+    float xp[2 * H][4];  // x[t0-H .. t0+H)
 #pragma unroll
-      for (int k = 0; k < W - 1; ++k)
+    for (int i = 0; i < 2 * H; ++i) load_x(t0 - H + i, xp[i]);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) { win[k][j] = win[k + 1][j]; gw[k][j] = gw[k + 1][j]; }
-      if (t < T) {
-        float g[8];
-        unpack8(rx[u], win[W - 1]);
-        unpack8(rg[u], g);
+    for (int i = 0; i < H; ++i) {
+      float xw[W][4];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          if (SILU) {
-            float a = bs[j];
+      for (int k = 0; k < W; ++k)
 #pragma unroll
-            for (int k = 0; k < W; ++k) a += wt[j][k] * win[k][j];
-            g[j] *= dsilu_f(a);
-          }
-          gw[W - 1][j] = g[j];
-          if (t < t1) {  // this tile owns the weight-gradient contribution of token t
-            dba[j] += g[j];
+        for (int j = 0; j < 4; ++j) xw[k][j] = xp[i + k][j];
+      float d4[4];
+      load_dy(t0 + i, d4);
+      make_g(t0 + i, xw, d4, gr[i]);
 #pragma unroll
-            for (int k = 0; k < W; ++k) dwa[j][k] += g[j] * win[k][j];
-          }
-        }
-      } else {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) { gw[W - 1][j] = 0.f; win[W - 1][j] = 0.f; }
-      }
-      const int s_ = t - (W - 1);  // dx[s] = sum_k w[k] * g[s + (W-1) - k] = sum_k w[k] * gw[W-1-k]
-      if (s_ >= t0 && s_ < t1) {
-        float o[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          float a = 0.f;
-#pragma unroll
-          for (int k = 0; k < W; ++k) a += wt[j][k] * gw[W - 1 - k][j];
-          o[j] = a;
-        }
-        st8(dxb + (size_t)s_ * lddx, pack8(o));
-      }
+      for (int j = 0; j < 4; ++j) xr[i][j] = xp[H + i][j];
     }
   }
+  for (int tb = t0; tb < t1; tb += U) {
+    // new rows: tokens tb+H .. tb+H+U-1
+    float dyb[U][4];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
+    for (int u = 0; u < U; ++u) { load_x(tb + H + u, xr[H + u]); load_dy(tb + H + u, dyb[u]); }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      float xw[W][4];
+#pragma unroll
+      for (int k = 0; k < W; ++k)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) xw[k][j] = xr[u + k][j];  // x[(tb+H+u) - H + k] = x[tb + u + k]
+      make_g(tb + H + u, xw, dyb[u], gr[H + u]);
+    }
+    // dx[tb+u] = sum_k w[k] * g[tb+u + H - k]
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (tb + u < t1) {
+        float o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          float a = 0.f;
+#pragma unroll
+          for (int k = 0; k < W; ++k) a += wt[j][k] * gr[u + H - k][j];
+          o[j] = a;
+        }
+        st4(dxb + (size_t)(tb + u) * lddx, o);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < H; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { xr[i][j] = xr[U + i][j]; gr[i][j] = gr[U + i][j]; }
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
 #pragma unroll
     for (int k = 0; k < W; ++k) atomicAdd(dw + (c0 + j) * W + k, dwa[j][k]);
     if (dbias != nullptr) atomicAdd(dbias + c0 + j, dba[j]);
@@ -229,7 +270,7 @@ extern "C" int mb_conv1d_bwd(const void* x, long long ldx, const float* w, const
   MB_REQUIRE(C % 8 == 0 && ldx % 8 == 0 && lddy % 8 == 0 && lddx % 8 == 0,
              "conv1d_bwd: C and row strides must be multiples of 8");
   if (B * T == 0) return 0;
-  dim3 grid(cdiv(C / 8, kConvThreads), cdiv(T, kConvTile), B);
+  dim3 grid(cdiv(C / 4, kConvThreads), cdiv(T, kConvTile), B);
   DISPATCH_W(width, silu, {
     conv1d_bwd_kernel<W, S><<<grid, kConvThreads, 0, stream>>>((const bf16*)x, ldx, w, bias, (const bf16*)dy, lddy,
                                                                (bf16*)dx, lddx, dw, dbias, T, C);

@@ -359,7 +359,7 @@ gated_rmsnorm_bwd_rows_kernel(const bf16* __restrict__ x, int ldx, const bf16* _
   }
 }
 
-constexpr int kDwRows = 32;  // rows per strip (more strips -> more loads in flight; 8 atomics per strip-thread)
+constexpr int kDwRows = 64;  // rows per strip: 8 atomics per strip-thread
 __global__ void __launch_bounds__(128)
 gated_rmsnorm_bwd_dw_kernel(const bf16* __restrict__ x, int ldx, const bf16* __restrict__ z, int ldz,
                             const float* __restrict__ rstd_in, const bf16* __restrict__ dout, int ldo,
@@ -376,21 +376,20 @@ gated_rmsnorm_bwd_dw_kernel(const bf16* __restrict__ x, int ldx, const bf16* __r
     bf16x8 px[U], pz[U], pg[U];
     float rs[U];
 #pragma unroll
-    for (int u = 0; u < U; ++u)
-      if (rb + u < r1) {
-        px[u] = ld8(x + (size_t)(rb + u) * ldx + col);
-        pz[u] = ld8(z + (size_t)(rb + u) * ldz + col);
-        pg[u] = ld8(dout + (size_t)(rb + u) * ldo + col);
-        rs[u] = rstd_in[rb + u];
-      }
+    for (int u = 0; u < U; ++u) {  // clamped, unconditional loads (issued back to back); tail rows get weight 0
+      const int rr = min(rb + u, r1 - 1);
+      px[u] = ld8(x + (size_t)rr * ldx + col);
+      pz[u] = ld8(z + (size_t)rr * ldz + col);
+      pg[u] = ld8(dout + (size_t)rr * ldo + col);
+      rs[u] = rb + u < r1 ? rstd_in[rr] : 0.f;
+    }
 #pragma unroll
-    for (int u = 0; u < U; ++u)
-      if (rb + u < r1) {
-        float xv[8], zz[8], go[8];
-        unpack8(px[u], xv); unpack8(pz[u], zz); unpack8(pg[u], go);
+    for (int u = 0; u < U; ++u) {
+      float xv[8], zz[8], go[8];
+      unpack8(px[u], xv); unpack8(pz[u], zz); unpack8(pg[u], go);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] += go[j] * xv[j] * silu_f(zz[j]) * rs[u];
-      }
+      for (int j = 0; j < 8; ++j) acc[j] += go[j] * xv[j] * silu_f(zz[j]) * rs[u];
+    }
   }
 #pragma unroll
   for (int j = 0; j < 8; ++j) atomicAdd(dw + col + j, acc[j]);

@@ -381,7 +381,12 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
       tc_fence_before();
       mbar_arrive(&acc_empty[acc]);
       TMARK("epi", hh, "epi_done");
-      if (hh + 2 < hgs) prefetch_head(hh + 2, et, 128);  // slot hh&1 is free: everything of head hh retired
+      if (hh + 2 < hgs) {
+        // all four epilogue warps must be done reading sV / a / dt of head hh before any of them
+        // overwrites that slot (named barrier over the 128 epilogue threads only)
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        prefetch_head(hh + 2, et, 128);
+      }
     }
     cp_async_wait<0>();
   } else if (lane == 0) {
