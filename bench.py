@@ -257,7 +257,7 @@ def main():
 
     if rank == 0:
         out = {
-            "metric": "train tokens/sec Mamba-2 280M DDP",
+            "metric": f"train tokens/sec Mamba-2 {args.preset.upper()} DDP",
             "impl": args.impl,
             "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,

@@ -415,13 +415,16 @@ using namespace mb;
     case 7: case 8: { constexpr int NV = 8; __VA_ARGS__; } break;   \
     case 9: case 10: { constexpr int NV = 10; __VA_ARGS__; } break; \
     case 11: case 12: { constexpr int NV = 12; __VA_ARGS__; } break; \
-    default: { constexpr int NV = 16; __VA_ARGS__; } break;    \
+    case 13: case 14: case 15: case 16: { constexpr int NV = 16; __VA_ARGS__; } break; \
+    case 17: case 18: case 19: case 20: { constexpr int NV = 20; __VA_ARGS__; } break; \
+    case 21: case 22: case 23: case 24: { constexpr int NV = 24; __VA_ARGS__; } break; \
+    default: { constexpr int NV = 32; __VA_ARGS__; } break;    \
   }
 
 extern "C" int mb_add_rmsnorm_fwd(const void* x, int x_is_fp32, const float* residual,
                                   const float* weight, void* y, float* res_out, float* rstd, int M,
                                   int D, float eps, cudaStream_t stream) {
-  MB_REQUIRE(D % 8 == 0 && D <= 4096, "add_rmsnorm_fwd: D=%d must be a multiple of 8 and <= 4096", D);
+  MB_REQUIRE(D % 8 == 0 && D <= 8192, "add_rmsnorm_fwd: D=%d must be a multiple of 8 and <= 8192", D);
   if (M == 0) return 0;
   const int nv = cdiv(D, 256);
   dim3 grid(cdiv(M, kWarpsPerBlock)), block(kWarpsPerBlock * 32);
@@ -442,7 +445,7 @@ extern "C" int mb_add_rmsnorm_bwd(const float* r, const void* dy, const float* r
                                   const float* weight, const float* dres_in, float* dres_out,
                                   void* dx_bf16, float* dw, int dw_accumulate, float* scratch, int M,
                                   int D, cudaStream_t stream) {
-  MB_REQUIRE(D % 8 == 0 && D <= 4096, "add_rmsnorm_bwd: D=%d must be a multiple of 8 and <= 4096", D);
+  MB_REQUIRE(D % 8 == 0 && D <= 8192, "add_rmsnorm_bwd: D=%d must be a multiple of 8 and <= 8192", D);
   if (M == 0) return 0;
   const int nv = cdiv(D, 256);
   const int grid = bwd_grid(M);
@@ -458,7 +461,7 @@ extern "C" int mb_add_rmsnorm_bwd(const float* r, const void* dy, const float* r
 extern "C" int mb_gated_rmsnorm_fwd(const void* x, int ldx, const void* z, int ldz,
                                     const float* weight, void* out, int ldo, float* rstd, int M,
                                     int D, int group_size, float eps, cudaStream_t stream) {
-  MB_REQUIRE(D % group_size == 0 && group_size % 8 == 0 && group_size <= 4096,
+  MB_REQUIRE(D % group_size == 0 && group_size % 8 == 0 && group_size <= 8192,
              "gated_rmsnorm_fwd: bad D=%d group_size=%d", D, group_size);
   MB_REQUIRE(ldx % 8 == 0 && ldz % 8 == 0 && ldo % 8 == 0, "gated_rmsnorm_fwd: row strides must be multiples of 8");
   if (M == 0) return 0;
@@ -476,7 +479,7 @@ extern "C" int mb_gated_rmsnorm_bwd(const void* x, int ldx, const void* z, int l
                                     void* dx, int lddx, void* dz, int lddz, float* dw,
                                     int dw_accumulate, float* scratch, int M, int D, int group_size,
                                     cudaStream_t stream) {
-  MB_REQUIRE(D % group_size == 0 && group_size % 8 == 0 && group_size <= 4096,
+  MB_REQUIRE(D % group_size == 0 && group_size % 8 == 0 && group_size <= 8192,
              "gated_rmsnorm_bwd: bad D=%d group_size=%d", D, group_size);
   if (M == 0) return 0;
   const int G = D / group_size, nv = cdiv(group_size, 256);

@@ -142,6 +142,8 @@ def evaluate(model_type="custom", hf_model_name: str = "state-spaces/mamba2-370m
 
     num_correct_norm = num_correct = num_total = 0
     pending = []
+    import time
+    t_start = time.time()
 
     def flush():
         nonlocal num_correct_norm, num_correct, num_total
@@ -187,14 +189,19 @@ def evaluate(model_type="custom", hf_model_name: str = "state-spaces/mamba2-370m
         dist.all_reduce(c)
         num_total, num_correct, num_correct_norm = c.tolist()
     acc_norm = num_correct_norm / max(num_total, 1)
+    if dev_type == "cuda":
+        torch.cuda.synchronize()
+    elapsed = time.time() - t_start
     if rank == 0:
+        print(f"scored {num_total} examples in {elapsed:.2f} s = {num_total / max(elapsed, 1e-9):.1f} examples/s "
+              f"({world} rank(s), {batch_examples} examples per forward)")
         os.makedirs("log", exist_ok=True)
         with open("log/hellaswag_eval.txt", "a") as file:
             file.write(f"{num_total} {num_correct_norm}/{num_total} {acc_norm:.4f}\n")
         print(f"final: acc {num_correct}/{num_total}={num_correct/max(num_total,1):.4f} "
               f"acc_norm {num_correct_norm}/{num_total}={acc_norm:.4f}")
     return {"num_total": num_total, "num_correct": num_correct, "num_correct_norm": num_correct_norm,
-            "acc_norm": acc_norm}
+            "acc_norm": acc_norm}  # (timing is printed, not returned: results must compare equal across runs)
 
 
 if __name__ == "__main__":
