@@ -20,8 +20,9 @@ constexpr int kDcbSmem = 2 * 2 * (128 * 128) + 2 * 2 * kL * 4 + 64 + 1024;  // d
 
 __global__ void __launch_bounds__(kThreadsB, 2)
 ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restrict__ x, long long ldx,
-               const float* __restrict__ dtv, const float* __restrict__ av, bf16* __restrict__ dcb, int T, int H,
-               int G, int nc) {
+               const bf16* __restrict__ Cm, const bf16* __restrict__ Bm, long long ldbc,
+               const float* __restrict__ dtv, const float* __restrict__ av, bf16* __restrict__ dcb,
+               float* __restrict__ rowsum_m, int T, int H, int G, int nc) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align1024(smem_raw);
   float* s_ad = reinterpret_cast<float*>(smem + 2 * 2 * 128 * 128);  // [2][a(256) | dt(256)]
@@ -40,12 +41,42 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
   const size_t row_base = (size_t)b * T + (size_t)c * kL;
 
   if (tid == 0) { mbar_init(bar, 1); fence_mbar_init(); }
-  if (warp == 0) { tmem_alloc(tmem_slot, 128); tmem_relinquish(); }
+  if (warp == 0) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  const uint32_t tCB = tmem + 128;
   uint32_t phase = 0;
+
+  // CB block (rows ri0.., columns cj0..) once per CTA: needed for the row sums of dM o M below.
+  // The C / B tiles borrow the per-head double buffer (2 x 32 KB) before the head loop starts.
+  {
+    uint8_t* sCt = smem;
+    uint8_t* sBt = smem + 2 * 128 * 128;
+    load_tile<2, false>(sCt, Cm + (row_base + ri0) * ldbc + g * kN, ldbc, 128, max(0, min(128, valid - ri0)), NoScale(),
+                        tid, kThreadsB);
+    load_tile<2, false>(sBt, Bm + (row_base + cj0) * ldbc + g * kN, ldbc, 128, max(0, min(128, valid - cj0)), NoScale(),
+                        tid, kThreadsB);
+    cp_async_commit();
+    cp_async_wait<0>();
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (tid == 0) {
+      tc_fence_after();
+      constexpr uint32_t idesc = make_idesc_bf16(128, 128, MAJOR_K, MAJOR_K);
+      const uint32_t a_addr = smem_u32(sCt), b_addr = smem_u32(sBt);
+#pragma unroll
+      for (int k = 0; k < kN / 16; ++k)
+        mma_bf16_ss(tCB, desc_kmajor(a_addr, 128, k >> 2, k & 3), desc_kmajor(b_addr, 128, k >> 2, k & 3), idesc,
+                    k > 0 ? 1u : 0u);
+      mma_commit(bar);
+    }
+    mbar_wait(bar, phase);
+    phase ^= 1;
+    tc_fence_after();
+    __syncthreads();  // everyone is past the wait before the tiles are overwritten by the head prefetch
+  }
 
   const int lg = warp & 3, half = warp >> 2;
   const int r = lg * 32 + lane;
@@ -72,6 +103,7 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
   };
   prefetch_head(0);
   for (int hh = 0; hh < hpg; ++hh) {
+    const int h = g * hpg + hh;
     uint8_t* sDY = smem + (hh & 1) * 2 * 128 * 128;
     uint8_t* sX = sDY + 128 * 128;
     const float* s_a = s_ad + (hh & 1) * 2 * kL;
@@ -93,34 +125,42 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
     phase ^= 1;
     tc_fence_after();
     const float a_i = s_a[ri];
+    float rsum = 0.f;  // sum_j (dM o M)[ri, j] over this thread's columns, with M rounded exactly as
+                       // the dx kernel rounds it (see ssd_bwd_finalize: makes row - column sums cancel)
 #pragma unroll
-    for (int ch = 0; ch < 2; ++ch) {
-      const int k0 = half * 64 + ch * 32;
+    for (int ch = 0; ch < 4; ++ch) {  // 16 columns at a time: keeps (P, CB) staging at 32 registers
+      const int k0 = half * 64 + ch * 16;
       if (cj0 + k0 > warp_row_max) continue;  // warp-uniform: block entirely above the diagonal
-      uint32_t v[32];
-      tmem_ld32(tmem + lane_sel + k0, v);
+      uint32_t v[16], cbv[16];
+      tmem_ld16(tmem + lane_sel + k0, v);
+      tmem_ld16(tCB + lane_sel + k0, cbv);
       tmem_ld_wait();
 #pragma unroll
-      for (int q = 0; q < 8; ++q) {  // branch-free, 128-bit broadcast loads of a_j / dt_j
+      for (int q = 0; q < 4; ++q) {  // branch-free, 128-bit broadcast loads of a_j / dt_j
         const float4 a4 = *reinterpret_cast<const float4*>(s_a + cj0 + k0 + 4 * q);
         const float4 d4 = *reinterpret_cast<const float4*>(s_dt + cj0 + k0 + 4 * q);
         const float aj[4] = {a4.x, a4.y, a4.z, a4.w}, dj[4] = {d4.x, d4.y, d4.z, d4.w};
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
           const int cj = cj0 + k0 + 4 * q + t;
-          const float val = __uint_as_float(v[4 * q + t]) * __expf(fminf(a_i - aj[t], 0.f)) * dj[t];
+          const float e = __expf(fminf(a_i - aj[t], 0.f));
+          const float pd = __uint_as_float(v[4 * q + t]) * dj[t];   // P * dt_j
           const unsigned keep = (cj <= ri) ? 0xffffffffu : 0u;
-          acc[ch * 32 + 4 * q + t] += __uint_as_float(__float_as_uint(val) & keep);
+          acc[ch * 16 + 4 * q + t] += __uint_as_float(__float_as_uint(pd * e) & keep);
+          // M'[ri,cj] = bf16(CB * e), the operand value the dx kernel multiplies with
+          const float mr = __bfloat162float(__float2bfloat16(__uint_as_float(cbv[4 * q + t]) * e));
+          rsum += __uint_as_float(__float_as_uint(pd * mr) & keep);
         }
       }
     }
+    if (ri < valid) atomicAdd(rowsum_m + ((size_t)bc * H + h) * kL + ri, rsum);
     tc_fence_before();
     __syncthreads();
   }
   bf16* dst = dcb + (((size_t)bc * G + g) * kL + ri) * kL + cj0 + half * 64;
 #pragma unroll
   for (int q = 0; q < 8; ++q) st8(dst + 8 * q, pack8(acc + 8 * q));
-  if (warp == 0) tmem_dealloc(tmem, 128);
+  if (warp == 0) tmem_dealloc(tmem, 256);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -247,15 +287,18 @@ ssd_dbdc_kernel(const bf16* __restrict__ dcb,                       // [B,nc,G,2
 using namespace mb;
 using namespace mb::ssd;
 
-extern "C" int mb_ssd_bwd_dcb(const void* dy, long long lddy, const void* x, long long ldx, const float* dt,
-                              const float* a, void* dcb, int B, int T, int H, int G, int P, int N, int L,
+// rowsum_m[b,c,h,i] += sum_j (dM o M)[i,j]  (pre-zeroed by the caller), the intra-chunk part of d a_i
+extern "C" int mb_ssd_bwd_dcb(const void* dy, long long lddy, const void* x, long long ldx, const void* Cm,
+                              const void* Bm, long long ldbc, const float* dt, const float* a, void* dcb,
+                              float* rowsum_m, int B, int T, int H, int G, int P, int N, int L,
                               cudaStream_t stream) {
   MB_REQUIRE(L == kL && P == kP && N == kN, "ssd_bwd_dcb: needs chunk=256, headdim=64, d_state=128");
   const int nc = cdiv(T, L);
   static bool once = false;
   if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_dcb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDcbSmem)); once = true; }
   dim3 grid(B * nc * 3, G);
-  ssd_dcb_kernel<<<grid, kThreadsB, kDcbSmem, stream>>>((const bf16*)dy, lddy, (const bf16*)x, ldx, dt, a, (bf16*)dcb, T, H, G, nc);
+  ssd_dcb_kernel<<<grid, kThreadsB, kDcbSmem, stream>>>((const bf16*)dy, lddy, (const bf16*)x, ldx, (const bf16*)Cm,
+                                                        (const bf16*)Bm, ldbc, dt, a, (bf16*)dcb, rowsum_m, T, H, G, nc);
   return check_launch("ssd_bwd_dcb");
 }
 

@@ -334,14 +334,14 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
         float o[32];
         if (!BWD) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) o[j] = ea * __uint_as_float(vo[j]) + __uint_as_float(vd[j]);
-          if (ri < valid) {  // y_ssm = y - D x is kept for backward (see ssd_bwd_finalize)
+          for (int j = 0; j < 32; ++j) o[j] = ea * __uint_as_float(vo[j]);
+          if (ri < valid) {  // y_off = exp(a_t) C_t S_prev^T alone is kept for backward (see ssd_bwd_finalize)
             bf16* dst2 = out2 + (row_base + ri) * ldo + h * kP + p0;
 #pragma unroll
             for (int q = 0; q < 4; ++q) st8(dst2 + 8 * q, pack8(o + 8 * q));
           }
 #pragma unroll
-          for (int j = 0; j < 32; ++j) o[j] += Dh * xv[j];
+          for (int j = 0; j < 32; ++j) o[j] += __uint_as_float(vd[j]) + Dh * xv[j];
         } else {
           if (ri < valid) {
             const bf16* xr = xsrc + (row_base + ri) * ldx + h * kP + p0;
@@ -472,10 +472,10 @@ extern "C" int mb_ssd_chunk_state(const void* arow, long long lda, const void* b
   return check_launch("ssd_chunk_state");
 }
 
-// y[t,h,:] = exp(a_t) C_t S_prev^T + sum_{s<=t} (C_t.B_s) exp(a_t - a_s) dt_s x_s + D_h x_t ;  y_ssm = y - D_h x_t
+// y[t,h,:] = exp(a_t) C_t S_prev^T + sum_{s<=t} (C_t.B_s) exp(a_t - a_s) dt_s x_s + D_h x_t ;  y_off = first term only
 extern "C" int mb_ssd_chunk_scan_fwd(const void* Cm, const void* Bm, long long ldbc, const void* x, long long ldx,
                                      const void* sprev_bf16, const float* dt, const float* a, const float* D,
-                                     void* y, void* y_ssm, long long ldy, int B, int T, int H, int G, int P, int N, int L,
+                                     void* y, void* y_off, long long ldy, int B, int T, int H, int G, int P, int N, int L,
                                      cudaStream_t stream) {
   SSD_SHAPE_CHECK("ssd_chunk_scan_fwd");
   const int nc = cdiv(T, L);
@@ -484,7 +484,7 @@ extern "C" int mb_ssd_chunk_scan_fwd(const void* Cm, const void* Bm, long long l
   if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_scan_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kScanSmem)); once = true; }
   dim3 grid(B * nc * 2, H / hgs);
   ssd_scan_kernel<false><<<grid, kScanThreads, kScanSmem, stream>>>((const bf16*)Cm, (const bf16*)Bm, ldbc, (const bf16*)x, ldx,
-                                                                (const bf16*)sprev_bf16, dt, a, D, (bf16*)y, ldy, (bf16*)y_ssm,
+                                                                (const bf16*)sprev_bf16, dt, a, D, (bf16*)y, ldy, (bf16*)y_off,
                                                                 nullptr, 0, nullptr, nullptr, nullptr, T, H, G, nc, hgs);
   return check_launch("ssd_chunk_scan_fwd");
 }

@@ -112,7 +112,11 @@ __global__ void ssd_state_passing_bwd_kernel(const float* __restrict__ dstates_d
 }
 
 // Backward finalize.  One block = one (b, c, head), thread t = token:
-//   rowpart_t = sum_p dY[t,p] * y_ssm[t,p]   (y_ssm = y - D x, stored by forward; d a_t from Y_off and M)
+//   rowpart_t = rowsum_m[t] + sum_p dY[t,p] * y_off[t,p]
+//     rowsum_m = row sums of dM o M from the dCB kernel, built from the SAME bf16-rounded M the dx kernel
+//     uses for the column sums (dt_t * ddt1_t), so the suffix sum of (row - column) sums — which equals the
+//     rectangle sum_{i >= t > j} (dM o M)[i,j] — cancels exactly instead of amplifying operand rounding;
+//     y_off = exp(a_t) C_t S_prev^T is the inter-chunk part, stored by forward.
 //   da_t      = rowpart_t - dt_t * (ddt1_t + ddt2_t)  (+ da_last at t = L-1, + sum_s dt_s ddt2_s at L-1)
 //   ddA_t     = suffix-sum_{s >= t} da_s ;  ddt_t = ddt1_t + ddt2_t + A_h * ddA_t
 //   draw_t    = ddt_t * sigmoid(raw_t + bias_h) -> bf16 into the dt columns of d(zxbcdt)
@@ -120,7 +124,8 @@ __global__ void ssd_state_passing_bwd_kernel(const float* __restrict__ dstates_d
 __global__ void ssd_bwd_finalize_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restrict__ y,
                                         long long ldy, const bf16* __restrict__ dt_raw, long long ld_dt,
                                         const float* __restrict__ dt, const float* __restrict__ ddt1,
-                                        const float* __restrict__ ddt2, const float* __restrict__ da_last,
+                                        const float* __restrict__ ddt2, const float* __restrict__ rowsum_m,
+                                        const float* __restrict__ da_last,
                                         const float* __restrict__ dt_bias, const float* __restrict__ A_log,
                                         bf16* __restrict__ draw_out,
                                         long long ld_draw, float* __restrict__ dA_log, float* __restrict__ ddt_bias,
@@ -149,6 +154,7 @@ __global__ void ssd_bwd_finalize_kernel(const bf16* __restrict__ dy, long long l
       }
     }
     const float d1 = ddt1[sidx], d2 = ddt2[sidx];
+    rowpart += rowsum_m[sidx];
     float da = rowpart - dtv * (d1 + d2);
     // a_last receives: state-passing term and sum_s dt_s * ddt2_s  (w_s = exp(a_last - a_s) dt_s)
     float q = dtv * d2;
@@ -228,16 +234,17 @@ extern "C" int mb_ssd_state_passing_bwd(const float* dstates_direct, const void*
   return check_launch("ssd_state_passing_bwd");
 }
 
-extern "C" int mb_ssd_bwd_finalize(const void* dy, long long lddy, const void* y_ssm, long long ldy,
+extern "C" int mb_ssd_bwd_finalize(const void* dy, long long lddy, const void* y_off, long long ldy,
                                    const void* dt_raw, long long ld_dt, const float* dt, const float* ddt1,
-                                   const float* ddt2, const float* da_last, const float* dt_bias,
+                                   const float* ddt2, const float* rowsum_m, const float* da_last,
+                                   const float* dt_bias,
                                    const float* A_log, void* draw_out, long long ld_draw, float* dA_log,
                                    float* ddt_bias, int B, int T, int H, int P, int L, cudaStream_t stream) {
   MB_REQUIRE(L == 64 || L == 128 || L == 256, "ssd_bwd_finalize: chunk size %d not in {64,128,256}", L);
   MB_REQUIRE(P % 8 == 0, "ssd_bwd_finalize: headdim must be a multiple of 8");
   const int nc = cdiv(T, L);
-  ssd_bwd_finalize_kernel<<<dim3(B * nc, H), L, 0, stream>>>((const bf16*)dy, lddy, (const bf16*)y_ssm, ldy,
-                                                    (const bf16*)dt_raw, ld_dt, dt, ddt1, ddt2, da_last, dt_bias,
+  ssd_bwd_finalize_kernel<<<dim3(B * nc, H), L, 0, stream>>>((const bf16*)dy, lddy, (const bf16*)y_off, ldy,
+                                                    (const bf16*)dt_raw, ld_dt, dt, ddt1, ddt2, rowsum_m, da_last, dt_bias,
                                                     A_log, (bf16*)draw_out, ld_draw, dA_log, ddt_bias, T, H, P, L, nc);
   return check_launch("ssd_bwd_finalize");
 }

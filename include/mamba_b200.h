@@ -97,22 +97,23 @@ int mb_ssd_state_passing_bwd(const float* dstates_direct, const void* sprev_bf16
                              cudaStream_t stream);
 int mb_ssd_chunk_scan_fwd(const void* Cm, const void* Bm, long long ldbc, const void* x, long long ldx,
                           const void* sprev_bf16, const float* dt, const float* a, const float* D, void* y,
-                          void* y_ssm, long long ldy, int B, int T, int H, int G, int P, int N, int L,
+                          void* y_off, long long ldy, int B, int T, int H, int G, int P, int N, int L,
                           cudaStream_t stream);
 int mb_ssd_chunk_scan_bwd_dx(const void* Bm, const void* Cm, long long ldbc, const void* dy, long long lddy,
                              const void* ds_bf16, const float* dt, const float* a, const float* D, void* dx,
                              long long lddx, const void* x, long long ldx, float* ddt1, float* ddt2,
                              float* dD, int B, int T, int H, int G, int P, int N, int L, cudaStream_t stream);
-int mb_ssd_bwd_dcb(const void* dy, long long lddy, const void* x, long long ldx, const float* dt,
-                   const float* a, void* dcb, int B, int T, int H, int G, int P, int N, int L,
-                   cudaStream_t stream);
+int mb_ssd_bwd_dcb(const void* dy, long long lddy, const void* x, long long ldx, const void* Cm,
+                   const void* Bm, long long ldbc, const float* dt, const float* a, void* dcb,
+                   float* rowsum_m, int B, int T, int H, int G, int P, int N, int L, cudaStream_t stream);
 int mb_ssd_bwd_dbdc(const void* dcb, const void* Bm, const void* Cm, long long ldbc, const void* dy,
                     long long lddy, const void* x, long long ldx, const void* sprev_bf16,
                     const void* ds_bf16, const float* dt, const float* a, void* dB, void* dC, long long ldo,
                     int B, int T, int H, int G, int P, int N, int L, cudaStream_t stream);
-int mb_ssd_bwd_finalize(const void* dy, long long lddy, const void* y_ssm, long long ldy,
+int mb_ssd_bwd_finalize(const void* dy, long long lddy, const void* y_off, long long ldy,
                         const void* dt_raw, long long ld_dt, const float* dt, const float* ddt1,
-                        const float* ddt2, const float* da_last, const float* dt_bias, const float* A_log,
+                        const float* ddt2, const float* rowsum_m, const float* da_last,
+                        const float* dt_bias, const float* A_log,
                         void* draw_out, long long ld_draw, float* dA_log, float* ddt_bias, int B, int T, int H,
                         int P, int L, cudaStream_t stream);
 

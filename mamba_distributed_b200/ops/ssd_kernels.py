@@ -46,7 +46,7 @@ def ssd_fwd(xBC, zxbcdt, Bsz, T, cfg, dt_bias, A_log, D):
     sprev = torch.empty(Bsz, nc, H, P, N, dtype=torch.bfloat16, device=dev)
     call("mb_ssd_state_passing_fwd", states, a, sprev, None, Bsz, nc, H, P * N, L)
     y = torch.empty(M, d_in, dtype=torch.bfloat16, device=dev)
-    y_ssm = torch.empty(M, d_in, dtype=torch.bfloat16, device=dev)  # y - D*x, needed by backward (d a_t)
+    y_ssm = torch.empty(M, d_in, dtype=torch.bfloat16, device=dev)  # inter-chunk part exp(a) C S_prev^T, needed by backward (d a_t)
     call("mb_ssd_chunk_scan_fwd", Cm, Bm, ld, x, ld, sprev, dt, a, D, y, y_ssm, y.stride(0), Bsz, T, H, G, P, N, L)
     return y, (dt, a, sprev, y_ssm)
 
@@ -66,17 +66,17 @@ def ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, s
     ds = torch.empty(Bsz, nc, H, P, N, dtype=torch.bfloat16, device=dev)
     da_last = torch.empty(Bsz, nc, H, dtype=torch.float32, device=dev)
     call("mb_ssd_state_passing_bwd", dstates, sprev, a, ds, da_last, Bsz, nc, H, P * N, L)
-    ddt12 = torch.zeros(2, Bsz, nc, H, L, dtype=torch.float32, device=dev)
+    ddt12 = torch.zeros(3, Bsz, nc, H, L, dtype=torch.float32, device=dev)  # ddt1 | ddt2 | row sums of dM o M
     lddx = dxBC.stride(0)
     red = torch.zeros(3, H, dtype=torch.float32, device=dev)  # dA_log | ddt_bias | dD
     call("mb_ssd_chunk_scan_bwd_dx", Bm, Cm, ld, dy, lddy, ds, dt, a, D, dxBC, lddx, x, ld, ddt12[0], ddt12[1],
          red[2], Bsz, T, H, G, P, N, L)
     dcb = torch.empty(Bsz, nc, G, L, L, dtype=torch.bfloat16, device=dev)
-    call("mb_ssd_bwd_dcb", dy, lddy, x, ld, dt, a, dcb, Bsz, T, H, G, P, N, L)
+    call("mb_ssd_bwd_dcb", dy, lddy, x, ld, Cm, Bm, ld, dt, a, dcb, ddt12[2], Bsz, T, H, G, P, N, L)
     dB = dxBC[:, d_in:]
     dC = dxBC[:, d_in + G * N:]
     call("mb_ssd_bwd_dbdc", dcb, Bm, Cm, ld, dy, lddy, x, ld, sprev, ds, dt, a, dB, dC, lddx, Bsz, T, H, G, P, N, L)
     draw = dzxbcdt[:, dzxbcdt.shape[1] - H:]
     call("mb_ssd_bwd_finalize", dy, lddy, y_ssm, y_ssm.stride(0), dt_raw, zxbcdt.stride(0), dt, ddt12[0], ddt12[1],
-         da_last, dt_bias, A_log, draw, dzxbcdt.stride(0), red[0], red[1], Bsz, T, H, P, L)
+         ddt12[2], da_last, dt_bias, A_log, draw, dzxbcdt.stride(0), red[0], red[1], Bsz, T, H, P, L)
     return red[1], red[0], red[2]  # ddt_bias, dA_log, dD

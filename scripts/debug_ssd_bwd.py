@@ -77,7 +77,7 @@ ddA_k = torch.flip(torch.cumsum(torch.flip(da_k, [2]), 2), [2])
 print("da (kernel inputs, torch formula)", rel(da_k, da), "ddA", rel(ddA_k, ddA))
 print("|rowpart| %.3g |dt*d| %.3g |da| %.3g |ddA| %.3g" % (rowpart.abs().mean(), (dt * (d1 + d2)).abs().mean(), da.abs().mean(), ddA.abs().mean()))
 red = torch.zeros(2, H, device=dev); ddtbuf = torch.zeros_like(dtbuf)
-call("mb_ssd_bwd_finalize", dy, d_in, yssm_k, d_in, dtbuf[:, Hp - H:], Hp, dt_k, ddt12[0], ddt12[1], dal_k, dt_bias, A_log, ddtbuf[:, Hp - H:], Hp, red[0], red[1], B, T, H, P, L)
+call("mb_ssd_bwd_finalize", dy, d_in, yssm_k, d_in, dtbuf[:, Hp - H:], Hp, dt_k, ddt12[0], ddt12[1], torch.zeros_like(ddt12[0]), dal_k, dt_bias, A_log, ddtbuf[:, Hp - H:], Hp, red[0], red[1], B, T, H, P, L)
 ddt_ref = d1 + d2 + A * ddA
 draw_ref = ddt_ref * torch.sigmoid(dtbuf[:, Hp - H:].float() + dt_bias).view(B, nc, L, H)
 print("draw", rel(ddtbuf[:, Hp - H:].float().view(B, nc, L, H), draw_ref))

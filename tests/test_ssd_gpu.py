@@ -61,8 +61,8 @@ def test_ssd_backward_head_reductions(B, T, H, G):
     column-sums of dM o M).  With a random upstream gradient the result is a heavily cancelled sum
     and the 0.2 % bf16 rounding of the MMA operands dominates it; a gradient correlated with y
     (as a real loss gradient is) gives a well-conditioned sum that pins the kernels' arithmetic.
-    Known limitation: d(dt*A) is still formed as a suffix sum of (row - column) sums,
-    so fast-decaying heads keep a few-percent error; the rectangle-sum form is future work."""
+    The row sums and the column sums are built from bit-identical bf16-rounded M operands in the
+    two kernels that produce them, so their difference does not amplify the operand rounding."""
     from mamba_distributed_b200.ops import ssd_native
     x, dt, A, Bm, Cm, D, dt_bias = _mk(B, T, H, G, seed=2)
     rl = [t.detach().float().requires_grad_(True) for t in (x, dt, A, Bm, Cm, D, dt_bias)]
@@ -73,7 +73,7 @@ def test_ssd_backward_head_reductions(B, T, H, G):
     y = ssd_native.ssd_combined(*leaves[:5], 256, leaves[5], None, leaves[6], True)
     grads = torch.autograd.grad(y, leaves, dy)
     for i, n in ((2, "dA"), (6, "ddt_bias"), (1, "ddt")):
-        assert _rel(grads[i], grads_ref[i]) < 8e-2, (n, _rel(grads[i], grads_ref[i]), grads[i].flatten()[:6], grads_ref[i].flatten()[:6])
+        assert _rel(grads[i], grads_ref[i]) < 2e-2, (n, _rel(grads[i], grads_ref[i]), grads[i].flatten()[:6], grads_ref[i].flatten()[:6])
 
 
 def test_mamba2_mixer_and_model_match_torch_path():
