@@ -27,7 +27,7 @@ def test_train_loss_decreases_checkpoint_roundtrip_and_eval(tmp_path):
     r = _run([os.path.join(ROOT, "train.py")] + common + ["--max_steps", "41", "--val_every", "20",
                                                           "--sample_every", "1000", "--ckpt_every", "20"], cwd)
     assert r.returncode == 0, r.stderr[-3000:]
-    losses = [float(m) for m in re.findall(r"loss: ([0-9.]+)", r.stdout)]
+    losses = [float(m) for m in re.findall(r"\| loss: ([0-9.]+)", r.stdout)]
     assert len(losses) == 41
     assert losses[0] > 10.0 and min(losses[-5:]) < losses[0] - 1.0, losses[::5]
     assert "using fused grad-sync + AdamW: True" in r.stdout
