@@ -107,11 +107,11 @@ ssd_outer_kernel(const bf16* __restrict__ arow, long long lda, const bf16* __res
 // ------------------------------------------------------------------------------------------
 // scan kernel (FWD: y ; BWD: dx, ddt partials) — warp-specialised, software-pipelined over heads
 //
-//   warps 0-7   "scale"     read the CB tile from TMEM, apply decay / mask / dt, write the bf16
+//   warps 0-15  "scale"     read the CB tile from TMEM, apply decay / mask / dt, write the bf16
 //                           operand G one 128-column half-tile at a time into a 2-slot smem ring
-//   warps 8-11  "epilogue"  read the finished accumulators of the previous head from TMEM, add the
+//   warps 16-19 "epilogue"  read the finished accumulators of the previous head from TMEM, add the
 //                           skip terms, store y / dx; then prefetch (cp.async) the tiles of head+2
-//   warp 12     "mma"       one lane issues tcgen05.mma: C.S^T (per head) and G.X (per half-tile);
+//   warp 20     "mma"       one lane issues tcgen05.mma: C.S^T (per head) and G.X (per half-tile);
 //                           tcgen05.commit frees G slots and publishes accumulators
 // Accumulators are double-buffered in TMEM (CB 256 cols + 2 x (64 + 64)), per-head tiles in smem, so
 // head h+1 is being scaled while head h is multiplied and head h-1 is written out.
@@ -121,7 +121,8 @@ __device__ long long g_tlog[2048];
 __device__ int g_tmeta[2048];
 __device__ int g_tcount = 0;
 #endif
-constexpr int kScanThreads = 13 * 32;
+constexpr int kScanWarpsScale = 8;   // measured: 16 scale warps (one 32-column chunk each) is not faster
+constexpr int kScanThreads = (kScanWarpsScale + 4 + 1) * 32;
 constexpr int kScanSmem = 128 * 2 * 128     /* sR  row operand  [128][2 kblk]               32 KB */
                         + 2 * (128 * 128 * 2) /* sG ring: 2 x [128][128] bf16 (aliases sC)     64 KB */
                         + 2 * kL * 128      /* sV  X_h / dY_h   [256][1 atom]   x2 buffers   64 KB */
@@ -146,11 +147,11 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
   float* s_ad = reinterpret_cast<float*>(sS0 + 2 * kP * 2 * 128);  // [2][a(256) | dt(256)]
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_ad + 2 * 2 * kL);
   uint64_t* cb_bar = bars;            // 1
-  uint64_t* g_full = bars + 1;        // [2]  256 scale threads arrive
+  uint64_t* g_full = bars + 1;        // [2]  one arrival per scale warp
   uint64_t* g_empty = bars + 3;       // [2]  tcgen05.commit
   uint64_t* acc_full = bars + 5;      // [2]  tcgen05.commit
-  uint64_t* acc_empty = bars + 7;     // [2]  128 epilogue threads arrive
-  uint64_t* tiles_full = bars + 9;    // [2]  128 epilogue threads arrive after their cp.async landed
+  uint64_t* acc_empty = bars + 7;     // [2]  one arrival per epilogue warp
+  uint64_t* tiles_full = bars + 9;    // [2]  one arrival per epilogue warp after its cp.async landed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -169,12 +170,13 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
   if (tid == 0) {
     mbar_init(cb_bar, 1);
     for (int i = 0; i < 2; ++i) {
-      mbar_init(&g_full[i], 256); mbar_init(&g_empty[i], 1); mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], 128); mbar_init(&tiles_full[i], 128);
+      // one arrival per WARP (after __syncwarp): hundreds of per-thread arrivals on one mbarrier word serialise
+      mbar_init(&g_full[i], kScanWarpsScale); mbar_init(&g_empty[i], 1); mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_empty[i], 4); mbar_init(&tiles_full[i], 4);
     }
     fence_mbar_init();
   }
-  if (warp == 12) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
+  if (warp == kScanWarpsScale + 4) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
 
   // per-head tiles: a | dt (2 KB), V tile [ncols][64], state tile [64][128]; issued by `nthr` threads
   auto prefetch_head = [&](int hh, int t, int nthr) {
@@ -207,7 +209,7 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   const uint32_t tCB = tmem;
-  if (warp == 12 && lane == 0) {
+  if (warp == kScanWarpsScale + 4 && lane == 0) {
     const uint32_t idesc = make_idesc_bf16(128, ncols, MAJOR_K, MAJOR_K);
     const uint32_t a_addr = smem_u32(sR), b_addr = smem_u32(sC);
 #pragma unroll
@@ -226,9 +228,9 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
 #else
 #define TMARK(role, hh, what)
 #endif
-  if (warp < 8) {
+  if (warp < kScanWarpsScale) {
     // =================================== scale warps ===================================
-    const int lg = warp & 3, sub = warp >> 2;      // 32-row lane group, 64-column sub-block of the half-tile
+    const int lg = warp & 3, sub = warp >> 2;      // 32-row lane group, column slice of the half-tile
     const int r = lg * 32 + lane, ri = r0 + r;
     const uint32_t lane_sel = (uint32_t)(lg * 32) << 16;
     const int warp_row_min = r0 + lg * 32, warp_row_max = warp_row_min + 31;
@@ -243,10 +245,13 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
         const int slot = unit & 1, use = unit >> 1;
         if (use > 0) mbar_wait(&g_empty[slot], (use - 1) & 1);
         TMARK("scale", hh, "slot_free");
-        uint8_t* gdst = sG + slot * 32768 + (size_t)sub * (128 * 128) + r * 128;
+        constexpr int kChunks = 128 / (32 * (kScanWarpsScale / 4));  // 32-column chunks per warp per half-tile
 #pragma unroll
-        for (int kq = 0; kq < 2; ++kq) {
-          const int kcol = half * 128 + sub * 64 + kq * 32;  // column inside the CB tile
+        for (int cq = 0; cq < kChunks; ++cq) {
+          const int c32 = sub * kChunks + cq;              // 32-column chunk index (0..3) inside the half-tile
+          uint8_t* gdst = sG + slot * 32768 + (size_t)(c32 >> 1) * (128 * 128) + r * 128;
+          const int kq = c32 & 1;                          // which 32-column half of the 64-column k-block
+          const int kcol = half * 128 + c32 * 32;          // column inside the CB tile
           const int cj0 = c0 + kcol;
           const bool skip = BWD ? (cj0 + 31 < warp_row_min) : (cj0 > warp_row_max);  // warp-uniform
           uint32_t pk[16];  // 32 bf16 results, packed as soon as they are produced
@@ -286,13 +291,14 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
                 make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
         }
         fence_proxy_async_smem();
-        mbar_arrive(&g_full[slot]);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&g_full[slot]);
         TMARK("scale", hh, "half_done");
       }
     }
-  } else if (warp < 12) {
+  } else if (warp < kScanWarpsScale + 4) {
     // =================================== epilogue warps ===================================
-    const int et = tid - 256;                      // 0..127
+    const int et = tid - kScanWarpsScale * 32;     // 0..127
     const int lg = warp & 3;
     const int r = lg * 32 + lane, ri = r0 + r;
     const uint32_t lane_sel = (uint32_t)(lg * 32) << 16;
@@ -302,7 +308,8 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
       if (hh >= 1 && hh + 1 < hgs) {  // the prefetch issued last iteration (head hh+1) has to land and be published
         cp_async_wait<0>();
         fence_proxy_async_smem();
-        mbar_arrive(&tiles_full[(hh + 1) & 1]);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tiles_full[(hh + 1) & 1]);
       }
       TMARK("epi", hh, "wait_acc");
       mbar_wait(&acc_full[acc], (hh >> 1) & 1);
@@ -321,32 +328,32 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
       const float el = __expf(s_a[kL - 1] - a_i);
       const float ea = __expf(a_i);
 #pragma unroll
-      for (int ph = 0; ph < 2; ++ph) {
-        const int p0 = ph * 32;
-        uint32_t vo[32], vd[32];
-        tmem_ld32(tOff + lane_sel + p0, vo);
-        tmem_ld32(tDiag + lane_sel + p0, vd);
+      for (int ph = 0; ph < 4; ++ph) {  // 16 head-dim columns at a time (register budget: 96 / thread)
+        const int p0 = ph * 16;
+        uint32_t vo[16], vd[16];
+        tmem_ld16(tOff + lane_sel + p0, vo);
+        tmem_ld16(tDiag + lane_sel + p0, vd);
         tmem_ld_wait();
-        float xv[32];
+        float xv[16];
 #pragma unroll
-        for (int q = 0; q < 4; ++q)
+        for (int q = 0; q < 2; ++q)
           unpack8(*reinterpret_cast<const bf16x8*>(sV + vrow * 128 + ((((p0 >> 3) + q) ^ (vrow & 7)) << 4)), xv + 8 * q);
-        float o[32];
+        float o[16];
         if (!BWD) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) o[j] = ea * __uint_as_float(vo[j]);
+          for (int j = 0; j < 16; ++j) o[j] = ea * __uint_as_float(vo[j]);
           if (ri < valid) {  // y_off = exp(a_t) C_t S_prev^T alone is kept for backward (see ssd_bwd_finalize)
             bf16* dst2 = out2 + (row_base + ri) * ldo + h * kP + p0;
 #pragma unroll
-            for (int q = 0; q < 4; ++q) st8(dst2 + 8 * q, pack8(o + 8 * q));
+            for (int q = 0; q < 2; ++q) st8(dst2 + 8 * q, pack8(o + 8 * q));
           }
 #pragma unroll
-          for (int j = 0; j < 32; ++j) o[j] += __uint_as_float(vd[j]) + Dh * xv[j];
+          for (int j = 0; j < 16; ++j) o[j] += __uint_as_float(vd[j]) + Dh * xv[j];
         } else {
           if (ri < valid) {
             const bf16* xr = xsrc + (row_base + ri) * ldx + h * kP + p0;
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
+            for (int q = 0; q < 2; ++q) {
               float xx[8];
               unpack8(ld8(xr + 8 * q), xx);
 #pragma unroll
@@ -359,12 +366,12 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
           }
           const float w = el * dt_i;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) o[j] = dt_i * __uint_as_float(vd[j]) + w * __uint_as_float(vo[j]) + Dh * xv[j];
+          for (int j = 0; j < 16; ++j) o[j] = dt_i * __uint_as_float(vd[j]) + w * __uint_as_float(vo[j]) + Dh * xv[j];
         }
         if (ri < valid) {
           bf16* dst = outp + (row_base + ri) * ldo + h * kP + p0;
 #pragma unroll
-          for (int q = 0; q < 4; ++q) st8(dst + 8 * q, pack8(o + 8 * q));
+          for (int q = 0; q < 2; ++q) st8(dst + 8 * q, pack8(o + 8 * q));
         }
       }
       if (BWD) {
@@ -379,7 +386,8 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
         if (lane == 0) atomicAdd(dD + h, sd);
       }
       tc_fence_before();
-      mbar_arrive(&acc_empty[acc]);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[acc]);
       TMARK("epi", hh, "epi_done");
       if (hh + 2 < hgs) {
         // all four epilogue warps must be done reading sV / a / dt of head hh before any of them
@@ -424,7 +432,7 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 12) tmem_dealloc(tmem, 512);
+  if (warp == kScanWarpsScale + 4) tmem_dealloc(tmem, 512);
 #ifdef MB_SSD_TIMING
   if (tprint && tid == 0) {
     const int n = min(g_tcount, 2048);
