@@ -127,7 +127,9 @@ constexpr int kScanSmem = 128 * 2 * 128     /* sR  row operand  [128][2 kblk]   
                         + 2 * (128 * 128 * 2) /* sG ring: 2 x [128][128] bf16 (aliases sC)     64 KB */
                         + 2 * kL * 128      /* sV  X_h / dY_h   [256][1 atom]   x2 buffers   64 KB */
                         + 2 * kP * 2 * 128  /* sS  S_prev_h / dS_h [64][2 kblk] x2           32 KB */
-                        + 2 * 2 * kL * 4 + 128 + 1024;
+                        + 6 * 2 * kL * 4    /* a | dt of every head of the group (<= 6), loaded once   12 KB */
+                        + 16 * 64 * 4       /* per-scale-warp column-factor scratch                     4 KB */
+                        + 128 + 1024;
 
 template <bool BWD>
 __global__ void __launch_bounds__(kScanThreads, 1)
@@ -144,8 +146,9 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
   uint8_t* sC = sG;
   uint8_t* sV0 = sG + 2 * 32768;
   uint8_t* sS0 = sV0 + 2 * kL * 128;
-  float* s_ad = reinterpret_cast<float*>(sS0 + 2 * kP * 2 * 128);  // [2][a(256) | dt(256)]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_ad + 2 * 2 * kL);
+  float* s_ad = reinterpret_cast<float*>(sS0 + 2 * kP * 2 * 128);  // [hgs <= 6][a(256) | dt(256)]
+  float* s_wscr = s_ad + 6 * 2 * kL;                                 // [scale warp][2][32] column factors
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_wscr + kScanWarpsScale * 64);
   uint64_t* cb_bar = bars;            // 1
   uint64_t* g_full = bars + 1;        // [2]  one arrival per scale warp
   uint64_t* g_empty = bars + 3;       // [2]  tcgen05.commit
@@ -182,12 +185,6 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
   auto prefetch_head = [&](int hh, int t, int nthr) {
     const int h = h_first + hh;
     const int bsel = hh & 1;
-    const size_t sb = ((size_t)bc * H + h) * kL;
-    const uint32_t ad = smem_u32(s_ad + bsel * 2 * kL);
-    for (int i = t; i < kL; i += nthr) {
-      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(ad + i * 4), "l"(av + sb + i) : "memory");
-      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(ad + (kL + i) * 4), "l"(dtv + sb + i) : "memory");
-    }
     load_tile<1, false>(sV0 + bsel * kL * 128, vsrc + (row_base + c0) * ldv + h * kP, ldv, ncols,
                         max(0, min(ncols, valid - c0)), NoScale(), t, nthr);
     load_tile<2, false>(sS0 + bsel * kP * 2 * 128, ssrc + ((size_t)bc * H + h) * kP * kN, kN, kP, kP, NoScale(), t, nthr);
@@ -199,6 +196,15 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
                       NoScale(), tid, kScanThreads);
   load_tile<2, false>(sC, colop + (row_base + c0) * ldbc + g * kN, ldbc, ncols, max(0, min(ncols, valid - c0)),
                       NoScale(), tid, kScanThreads);
+  // a | dt of every head of the group up front (2 KB each): the scale warps then never wait for a
+  // per-head prefetch, only the MMA issuer does (for the X / state tiles)
+  for (int i = tid; i < hgs * kL; i += kScanThreads) {
+    const int hh = i / kL, t = i % kL;
+    const size_t sb = ((size_t)bc * H + h_first + hh) * kL;
+    const uint32_t ad = smem_u32(s_ad + hh * 2 * kL);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(ad + t * 4), "l"(av + sb + t) : "memory");
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(ad + (kL + t) * 4), "l"(dtv + sb + t) : "memory");
+  }
   cp_async_commit();
   prefetch_head(0, tid, kScanThreads);
   if (hgs > 1) prefetch_head(1, tid, kScanThreads);
@@ -234,13 +240,15 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
     const int r = lg * 32 + lane, ri = r0 + r;
     const uint32_t lane_sel = (uint32_t)(lg * 32) << 16;
     const int warp_row_min = r0 + lg * 32, warp_row_max = warp_row_min + 31;
+    float* wscr = s_wscr + warp * 64;
     int unit = 0;
     for (int hh = 0; hh < hgs; ++hh) {
-      if (hh >= 2) mbar_wait(&tiles_full[hh & 1], ((hh >> 1) - 1) & 1);
       TMARK("scale", hh, "tiles_ready");
-      const float* s_a = s_ad + (hh & 1) * 2 * kL;
+      const float* s_a = s_ad + hh * 2 * kL;
       const float* s_dt = s_a + kL;
       const float a_i = s_a[ri];
+      const float a_ref = s_a[BWD ? warp_row_max : warp_row_min];
+      const float rowf = __expf(fminf(BWD ? a_ref - a_i : a_i - a_ref, 0.f));
       for (int half = 0; half < nhalves; ++half, ++unit) {
         const int slot = unit & 1, use = unit >> 1;
         if (use > 0) mbar_wait(&g_empty[slot], (use - 1) & 1);
@@ -254,8 +262,34 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
           const int kcol = half * 128 + c32 * 32;          // column inside the CB tile
           const int cj0 = c0 + kcol;
           const bool skip = BWD ? (cj0 + 31 < warp_row_min) : (cj0 > warp_row_max);  // warp-uniform
+          // strictly off-diagonal chunk: every (i, j) of the 32 x 32 block is unmasked and
+          // a_i <= a_ref <= a_j (fwd; mirrored in bwd), so exp(a_i - a_j) factors into a per-row and a
+          // per-column term that are both <= 1 -- 2 multiplies per element instead of an exp + mask
+          const bool fast = BWD ? (cj0 > warp_row_max) : (cj0 + 31 < warp_row_min);          // warp-uniform
           uint32_t pk[16];  // 32 bf16 results, packed as soon as they are produced
-          if (!skip) {
+          if (fast) {
+            float* scr = wscr + cq * 32;
+            {
+              const float aj = s_a[cj0 + lane];
+              float cf = __expf(fminf(BWD ? aj - a_ref : a_ref - aj, 0.f));
+              if (!BWD) cf *= s_dt[cj0 + lane];
+              scr[lane] = cf;
+            }
+            uint32_t v[32];
+            tmem_ld32(tCB + lane_sel + kcol, v);
+            __syncwarp();
+            tmem_ld_wait();
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+              const float4 c4 = *reinterpret_cast<const float4*>(scr + 4 * q);
+              const bf162 lo = __floats2bfloat162_rn(__uint_as_float(v[4 * q]) * rowf * c4.x,
+                                                     __uint_as_float(v[4 * q + 1]) * rowf * c4.y);
+              const bf162 hi = __floats2bfloat162_rn(__uint_as_float(v[4 * q + 2]) * rowf * c4.z,
+                                                     __uint_as_float(v[4 * q + 3]) * rowf * c4.w);
+              pk[2 * q] = *reinterpret_cast<const uint32_t*>(&lo);
+              pk[2 * q + 1] = *reinterpret_cast<const uint32_t*>(&hi);
+            }
+          } else if (!skip) {
             uint32_t v[32];
             tmem_ld32(tCB + lane_sel + kcol, v);
             tmem_ld_wait();
@@ -315,7 +349,7 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
       mbar_wait(&acc_full[acc], (hh >> 1) & 1);
       tc_fence_after();
       TMARK("epi", hh, "acc_ready");
-      const float* s_a = s_ad + acc * 2 * kL;
+      const float* s_a = s_ad + hh * 2 * kL;
       const float* s_dt = s_a + kL;
       const uint8_t* sV = sV0 + acc * kL * 128;
       const uint32_t tOff = tmem + 256 + acc * 128, tDiag = tOff + 64;
@@ -487,7 +521,7 @@ extern "C" int mb_ssd_chunk_scan_fwd(const void* Cm, const void* Bm, long long l
                                      cudaStream_t stream) {
   SSD_SHAPE_CHECK("ssd_chunk_scan_fwd");
   const int nc = cdiv(T, L);
-  const int hgs = pick_head_group(H / G);
+  const int hgs = pick_head_group(H / G);  // <= 6 (smem holds a | dt of the whole group)
   static bool once = false;
   if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_scan_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kScanSmem)); once = true; }
   dim3 grid(B * nc * 2, H / hgs);
