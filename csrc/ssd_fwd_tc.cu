@@ -107,34 +107,37 @@ ssd_outer_kernel(const bf16* __restrict__ arow, long long lda, const bf16* __res
 // ------------------------------------------------------------------------------------------
 // scan kernel (FWD: y ; BWD: dx, ddt partials) — warp-specialised, software-pipelined over heads
 //
-//   warps 0-15  "scale"     read the CB tile from TMEM, apply decay / mask / dt, write the bf16
+//   warps 0-7   "scale"     read the CB tile from TMEM, apply decay / mask / dt, write the bf16
 //                           operand G one 128-column half-tile at a time into a 2-slot smem ring
-//   warps 16-19 "epilogue"  read the finished accumulators of the previous head from TMEM, add the
-//                           skip terms, store y / dx; then prefetch (cp.async) the tiles of head+2
-//   warp 20     "mma"       one lane issues tcgen05.mma: C.S^T (per head) and G.X (per half-tile);
+//   warps 8-11  "epilogue"  read the finished accumulators of the previous head from TMEM, add the
+//                           skip terms, store y / dx
+//   warp 12     "mma"       one lane issues tcgen05.mma: C.S^T (per head) and G.X (per half-tile);
 //                           tcgen05.commit frees G slots and publishes accumulators
+//   warp 13     "producer"  one lane issues the TMA loads: row / column operands, then the X / state
+//                           tiles of head+2 as soon as the epilogue warps hold their X rows of head
 // Accumulators are double-buffered in TMEM (CB 256 cols + 2 x (64 + 64)), per-head tiles in smem, so
 // head h+1 is being scaled while head h is multiplied and head h-1 is written out.
 // ------------------------------------------------------------------------------------------
 #ifdef MB_SSD_TIMING
-__device__ long long g_tlog[2048];
-__device__ int g_tmeta[2048];
-__device__ int g_tcount = 0;
+__device__ long long g_tlog[32][64];   // [warp][event]: store-only marks (no atomics -> ~tens of cycles each)
+__device__ int g_tmeta[32][64];
 #endif
 constexpr int kScanWarpsScale = 8;   // measured: 16 scale warps (one 32-column chunk each) is not faster
-constexpr int kScanThreads = (kScanWarpsScale + 4 + 1) * 32;
+constexpr int kScanWarpsProd = 1;    // one lane of it issues every TMA load (operands, per-head X / state tiles)
+constexpr int kScanThreads = (kScanWarpsScale + 4 + 1 + kScanWarpsProd) * 32;
+constexpr int kScanMaxHeads = 8;     // heads per CTA sharing one C.B^T (amortises the prologue)
 constexpr int kScanSmem = 128 * 2 * 128     /* sR  row operand  [128][2 kblk]               32 KB */
                         + 2 * (128 * 128 * 2) /* sG ring: 2 x [128][128] bf16 (aliases sC)     64 KB */
                         + 2 * kL * 128      /* sV  X_h / dY_h   [256][1 atom]   x2 buffers   64 KB */
                         + 2 * kP * 2 * 128  /* sS  S_prev_h / dS_h [64][2 kblk] x2           32 KB */
-                        + 6 * 2 * kL * 4    /* a | dt of every head of the group (<= 6), loaded once   12 KB */
+                        + kScanMaxHeads * 2 * kL * 4 /* a | dt of every head of the group, loaded once    16 KB */
                         + 16 * 64 * 4       /* per-scale-warp column-factor scratch                     4 KB */
                         + 128 + 1024;
 
 template <bool BWD>
 __global__ void __launch_bounds__(kScanThreads, 1)
-ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, long long ldbc,
-                const bf16* __restrict__ vsrc, long long ldv, const bf16* __restrict__ ssrc,
+ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant__ CUtensorMap tmCol,
+                const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmS,
                 const float* __restrict__ dtv, const float* __restrict__ av, const float* __restrict__ Dp,
                 bf16* __restrict__ outp, long long ldo, bf16* __restrict__ out2, const bf16* __restrict__ xsrc,
                 long long ldx, float* __restrict__ ddt1, float* __restrict__ ddt2, float* __restrict__ dD, int T,
@@ -146,16 +149,18 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
   uint8_t* sC = sG;
   uint8_t* sV0 = sG + 2 * 32768;
   uint8_t* sS0 = sV0 + 2 * kL * 128;
-  float* s_ad = reinterpret_cast<float*>(sS0 + 2 * kP * 2 * 128);  // [hgs <= 6][a(256) | dt(256)]
-  float* s_wscr = s_ad + 6 * 2 * kL;                                 // [scale warp][2][32] column factors
+  float* s_ad = reinterpret_cast<float*>(sS0 + 2 * kP * 2 * 128);  // [hgs <= kScanMaxHeads][a(256) | dt(256)]
+  float* s_wscr = s_ad + kScanMaxHeads * 2 * kL;                                 // [scale warp][2][32] column factors
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_wscr + kScanWarpsScale * 64);
   uint64_t* cb_bar = bars;            // 1
   uint64_t* g_full = bars + 1;        // [2]  one arrival per scale warp
   uint64_t* g_empty = bars + 3;       // [2]  tcgen05.commit
   uint64_t* acc_full = bars + 5;      // [2]  tcgen05.commit
   uint64_t* acc_empty = bars + 7;     // [2]  one arrival per epilogue warp
-  uint64_t* tiles_full = bars + 9;    // [2]  one arrival per epilogue warp after its cp.async landed
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
+  uint64_t* tiles_full = bars + 9;    // [2]  TMA transaction barrier (expect_tx by the producer lane)
+  uint64_t* tiles_empty = bars + 11;  // [2]  one arrival per epilogue warp once its X row is in registers
+  uint64_t* ld_bar = bars + 13;       // 1    TMA transaction barrier for the row / column operands
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int rh = blockIdx.x & 1;
@@ -172,32 +177,30 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
 
   if (tid == 0) {
     mbar_init(cb_bar, 1);
+    mbar_init(ld_bar, 1);
     for (int i = 0; i < 2; ++i) {
       // one arrival per WARP (after __syncwarp): hundreds of per-thread arrivals on one mbarrier word serialise
       mbar_init(&g_full[i], kScanWarpsScale); mbar_init(&g_empty[i], 1); mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], 4); mbar_init(&tiles_full[i], 4);
+      mbar_init(&acc_empty[i], 4); mbar_init(&tiles_full[i], 1); mbar_init(&tiles_empty[i], 4);
     }
     fence_mbar_init();
   }
   if (warp == kScanWarpsScale + 4) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
 
-  // per-head tiles: a | dt (2 KB), V tile [ncols][64], state tile [64][128]; issued by `nthr` threads
-  auto prefetch_head = [&](int hh, int t, int nthr) {
+  // per-head tiles by TMA (one lane): V tile [ncols][64] as 128-row boxes, state tile [64][128] as two
+  // 64-column boxes; both land 128B-swizzled exactly as the UMMA descriptors expect them
+  auto issue_head = [&](int hh) {
     const int h = h_first + hh;
     const int bsel = hh & 1;
-    load_tile<1, false>(sV0 + bsel * kL * 128, vsrc + (row_base + c0) * ldv + h * kP, ldv, ncols,
-                        max(0, min(ncols, valid - c0)), NoScale(), t, nthr);
-    load_tile<2, false>(sS0 + bsel * kP * 2 * 128, ssrc + ((size_t)bc * H + h) * kP * kN, kN, kP, kP, NoScale(), t, nthr);
-    cp_async_commit();
+    uint64_t* bar = &tiles_full[bsel];
+    mbar_arrive_expect_tx(bar, (uint32_t)(ncols * 128 + kP * 2 * 128));
+    for (int rb = 0; rb < nhalves; ++rb)
+      tma_load_3d(sV0 + bsel * kL * 128 + rb * 128 * 128, &tmV, bar, h * kP, c * kL + c0 + rb * 128, b);
+    for (int kb = 0; kb < 2; ++kb)
+      tma_load_2d(sS0 + bsel * kP * 2 * 128 + kb * kP * 128, &tmS, bar, kb * 64, (bc * H + h) * kP);
   };
 
-  // ---- prologue: row / column operands, heads 0 and 1, CB (or its transpose) into TMEM ----
-  load_tile<2, false>(sR, rowop + (row_base + r0) * ldbc + g * kN, ldbc, 128, max(0, min(128, valid - r0)),
-                      NoScale(), tid, kScanThreads);
-  load_tile<2, false>(sC, colop + (row_base + c0) * ldbc + g * kN, ldbc, ncols, max(0, min(ncols, valid - c0)),
-                      NoScale(), tid, kScanThreads);
-  // a | dt of every head of the group up front (2 KB each): the scale warps then never wait for a
-  // per-head prefetch, only the MMA issuer does (for the X / state tiles)
+  // ---- prologue: a | dt of every head of the group (2 KB each, cp.async by everyone) ----
   for (int i = tid; i < hgs * kL; i += kScanThreads) {
     const int hh = i / kL, t = i % kL;
     const size_t sb = ((size_t)bc * H + h_first + hh) * kL;
@@ -206,16 +209,26 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(ad + (kL + t) * 4), "l"(dtv + sb + t) : "memory");
   }
   cp_async_commit();
-  prefetch_head(0, tid, kScanThreads);
-  if (hgs > 1) prefetch_head(1, tid, kScanThreads);
   cp_async_wait<0>();
-  fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   const uint32_t tCB = tmem;
+  if (warp == kScanWarpsScale + 5 && lane == 0) {
+    // row / column operands, then the tiles of heads 0 and 1
+    mbar_arrive_expect_tx(ld_bar, (uint32_t)((128 + ncols) * 2 * 128));
+    for (int kb = 0; kb < 2; ++kb) {
+      tma_load_3d(sR + kb * 128 * 128, &tmRow, ld_bar, g * kN + kb * 64, c * kL + r0, b);
+      for (int rb = 0; rb < nhalves; ++rb)
+        tma_load_3d(sC + kb * ncols * 128 + rb * 128 * 128, &tmCol, ld_bar, g * kN + kb * 64, c * kL + c0 + rb * 128, b);
+    }
+    issue_head(0);
+    if (hgs > 1) issue_head(1);
+  }
   if (warp == kScanWarpsScale + 4 && lane == 0) {
+    mbar_wait(ld_bar, 0);
+    tc_fence_after();
     const uint32_t idesc = make_idesc_bf16(128, ncols, MAJOR_K, MAJOR_K);
     const uint32_t a_addr = smem_u32(sR), b_addr = smem_u32(sC);
 #pragma unroll
@@ -230,7 +243,8 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
 #ifdef MB_SSD_TIMING
   const bool tprint = blockIdx.x == 5 && blockIdx.y == 0 && !BWD;
   const long long t_start = clock64();
-#define TMARK(role, hh, what) if (tprint && lane == 0) { int i_ = atomicAdd(&g_tcount, 1); if (i_ < 2048) { g_tlog[i_] = clock64() - t_start; g_tmeta[i_] = (warp << 16) | ((hh) << 8) | (what[0]); } }
+  int tidx = 0;
+#define TMARK(role, hh, what) if (tprint && lane == 0 && tidx < 64) { g_tlog[warp][tidx] = clock64() - t_start; g_tmeta[warp][tidx] = ((hh) << 8) | (what[0]); ++tidx; }
 #else
 #define TMARK(role, hh, what)
 #endif
@@ -332,19 +346,12 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
     }
   } else if (warp < kScanWarpsScale + 4) {
     // =================================== epilogue warps ===================================
-    const int et = tid - kScanWarpsScale * 32;     // 0..127
     const int lg = warp & 3;
     const int r = lg * 32 + lane, ri = r0 + r;
     const uint32_t lane_sel = (uint32_t)(lg * 32) << 16;
     for (int hh = 0; hh < hgs; ++hh) {
       const int h = h_first + hh;
       const int acc = hh & 1;
-      if (hh >= 1 && hh + 1 < hgs) {  // the prefetch issued last iteration (head hh+1) has to land and be published
-        cp_async_wait<0>();
-        fence_proxy_async_smem();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&tiles_full[(hh + 1) & 1]);
-      }
       TMARK("epi", hh, "wait_acc");
       mbar_wait(&acc_full[acc], (hh >> 1) & 1);
       tc_fence_after();
@@ -352,11 +359,20 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
       const float* s_a = s_ad + hh * 2 * kL;
       const float* s_dt = s_a + kL;
       const uint8_t* sV = sV0 + acc * kL * 128;
+      const int vrow = ri - c0;
+      // The accumulators being complete means the tensor core is done with this head's X / state tiles.
+      // Take this thread's X row (128 B) into registers; once all four epilogue warps have theirs the
+      // slot is free and the producer warps stream the tiles of head hh+2 in underneath this epilogue.
+      mbar_wait(&tiles_full[acc], (hh >> 1) & 1);  // long complete; makes the TMA-written tile visible to this thread
+      uint4 xrow[8];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) xrow[q] = *reinterpret_cast<const uint4*>(sV + vrow * 128 + ((q ^ (vrow & 7)) << 4));
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tiles_empty[acc]);
       const uint32_t tOff = tmem + 256 + acc * 128, tDiag = tOff + 64;
       const size_t sbase = ((size_t)bc * H + h) * kL;
       const float a_i = s_a[ri];
       const float Dh = Dp[h];
-      const int vrow = ri - c0;
       float s1 = 0.f, s2 = 0.f, sd = 0.f;
       const float dt_i = s_dt[ri];
       const float el = __expf(s_a[kL - 1] - a_i);
@@ -370,8 +386,11 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
         tmem_ld_wait();
         float xv[16];
 #pragma unroll
-        for (int q = 0; q < 2; ++q)
-          unpack8(*reinterpret_cast<const bf16x8*>(sV + vrow * 128 + ((((p0 >> 3) + q) ^ (vrow & 7)) << 4)), xv + 8 * q);
+        for (int q = 0; q < 2; ++q) {
+          bf16x8 t8;
+          memcpy(&t8, &xrow[2 * ph + q], 16);
+          unpack8(t8, xv + 8 * q);
+        }
         float o[16];
         if (!BWD) {
 #pragma unroll
@@ -423,15 +442,9 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[acc]);
       TMARK("epi", hh, "epi_done");
-      if (hh + 2 < hgs) {
-        // all four epilogue warps must be done reading sV / a / dt of head hh before any of them
-        // overwrites that slot (named barrier over the 128 epilogue threads only)
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        prefetch_head(hh + 2, et, 128);
-      }
     }
-    cp_async_wait<0>();
-  } else if (lane == 0) {
+  } else if (warp == kScanWarpsScale + 4) {
+    if (lane == 0) {
     // =================================== MMA issuer ===================================
     const uint32_t r_addr = smem_u32(sR);
     constexpr uint32_t idesc_off = make_idesc_bf16(128, kP, MAJOR_K, MAJOR_K);
@@ -439,11 +452,10 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
     int unit = 0;
     for (int hh = 0; hh < hgs; ++hh) {
       const int acc = hh & 1;
-      if (hh >= 2) {
-        mbar_wait(&acc_empty[acc], ((hh >> 1) - 1) & 1);
-        mbar_wait(&tiles_full[acc], ((hh >> 1) - 1) & 1);
-      }
+      if (hh >= 2) mbar_wait(&acc_empty[acc], ((hh >> 1) - 1) & 1);
+      mbar_wait(&tiles_full[acc], (hh >> 1) & 1);
       tc_fence_after();
+      TMARK("mma", hh, "ready");
       const uint32_t tOff = tmem + 256 + acc * 128, tDiag = tOff + 64;
       const uint32_t s_addr = smem_u32(sS0 + acc * kP * 2 * 128), v_addr = smem_u32(sV0 + acc * kL * 128);
 #pragma unroll
@@ -454,6 +466,7 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
         const int slot = unit & 1;
         mbar_wait(&g_full[slot], (unit >> 1) & 1);
         tc_fence_after();
+        TMARK("mma", hh, "g_full");
         const uint32_t g_addr = smem_u32(sG + slot * 32768);
 #pragma unroll
         for (int k = 0; k < 8; ++k)  // G half-tile [128 x 128] . V[128 x 64]
@@ -463,26 +476,46 @@ ssd_scan_kernel(const bf16* __restrict__ rowop, const bf16* __restrict__ colop, 
       }
       mma_commit(&acc_full[acc]);
     }
+    }
+  } else {
+    // =================================== TMA producer ===================================
+    if (lane == 0) {
+      for (int hh = 2; hh < hgs; ++hh) {
+        mbar_wait(&tiles_empty[hh & 1], ((hh >> 1) - 1) & 1);
+        issue_head(hh);
+      }
+    }
   }
   tc_fence_before();
   __syncthreads();
   if (warp == kScanWarpsScale + 4) tmem_dealloc(tmem, 512);
 #ifdef MB_SSD_TIMING
-  if (tprint && tid == 0) {
-    const int n = min(g_tcount, 2048);
-    for (int i = 0; i < n; ++i) printf("T %d %d %c %lld\n", g_tmeta[i] >> 16, (g_tmeta[i] >> 8) & 255, (char)(g_tmeta[i] & 255), g_tlog[i]);
-    g_tcount = 0;
+  if (tprint && lane == 0) {
+    for (int i = 0; i < tidx; ++i) printf("T %d %d %c %lld\n", warp, (g_tmeta[warp][i] >> 8) & 255, (char)(g_tmeta[warp][i] & 255), g_tlog[warp][i]);
   }
 #endif
 }
 
-static int pick_head_group(int heads_per_group) {
-  for (int s = 6; s >= 1; --s)
-    if (heads_per_group % s == 0) return s;
-  return 1;
+// Heads per CTA: more heads amortise the C.B^T prologue (~ one head's worth of time), fewer heads
+// quantise better into waves of one CTA per SM.  Pick the divisor that minimises the modelled time.
+static int pick_head_group(int heads_per_group, int ctas_per_head, int heads) {
+  int dev = 0, sms = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  int best = 1;
+  long long best_cost = -1;
+  for (int s = 1; s <= kScanMaxHeads; ++s) {
+    if (heads_per_group % s) continue;
+    const long long ctas = (long long)ctas_per_head * (heads / s);
+    const long long cost = ((ctas + sms - 1) / sms) * (s + 1);
+    if (best_cost < 0 || cost <= best_cost) { best = s; best_cost = cost; }
+  }
+  return best;
 }
 
 }  // namespace ssd
+// tensor-map builders shared with the GEMM (gemm.cu)
+int make_tmap_bf16_2d(CUtensorMap* map, const void* ptr, long long rows, long long cols, long long ld, int box_rows);
+int make_tmap_bf16_3d(CUtensorMap* map, const void* ptr, long long d2, long long d1, long long cols, long long ld, int box_rows);
 }  // namespace mb
 using namespace mb;
 using namespace mb::ssd;
@@ -521,12 +554,15 @@ extern "C" int mb_ssd_chunk_scan_fwd(const void* Cm, const void* Bm, long long l
                                      cudaStream_t stream) {
   SSD_SHAPE_CHECK("ssd_chunk_scan_fwd");
   const int nc = cdiv(T, L);
-  const int hgs = pick_head_group(H / G);  // <= 6 (smem holds a | dt of the whole group)
+  const int hgs = pick_head_group(H / G, B * nc * 2, H);  // <= kScanMaxHeads (smem holds a | dt of the group)
   static bool once = false;
   if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_scan_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kScanSmem)); once = true; }
   dim3 grid(B * nc * 2, H / hgs);
-  ssd_scan_kernel<false><<<grid, kScanThreads, kScanSmem, stream>>>((const bf16*)Cm, (const bf16*)Bm, ldbc, (const bf16*)x, ldx,
-                                                                (const bf16*)sprev_bf16, dt, a, D, (bf16*)y, ldy, (bf16*)y_off,
+  CUtensorMap tmRow, tmCol, tmV, tmS;
+  if (make_tmap_bf16_3d(&tmRow, Cm, B, T, (long long)G * N, ldbc, 128) || make_tmap_bf16_3d(&tmCol, Bm, B, T, (long long)G * N, ldbc, 128) ||
+      make_tmap_bf16_3d(&tmV, x, B, T, (long long)H * P, ldx, 128) ||
+      make_tmap_bf16_2d(&tmS, sprev_bf16, (long long)B * nc * H * P, N, N, 64)) return 1;
+  ssd_scan_kernel<false><<<grid, kScanThreads, kScanSmem, stream>>>(tmRow, tmCol, tmV, tmS, dt, a, D, (bf16*)y, ldy, (bf16*)y_off,
                                                                 nullptr, 0, nullptr, nullptr, nullptr, T, H, G, nc, hgs);
   return check_launch("ssd_chunk_scan_fwd");
 }
@@ -541,12 +577,15 @@ extern "C" int mb_ssd_chunk_scan_bwd_dx(const void* Bm, const void* Cm, long lon
                                         cudaStream_t stream) {
   SSD_SHAPE_CHECK("ssd_chunk_scan_bwd_dx");
   const int nc = cdiv(T, L);
-  const int hgs = pick_head_group(H / G);
+  const int hgs = pick_head_group(H / G, B * nc * 2, H);
   static bool once = false;
   if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_scan_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kScanSmem)); once = true; }
   dim3 grid(B * nc * 2, H / hgs);
-  ssd_scan_kernel<true><<<grid, kScanThreads, kScanSmem, stream>>>((const bf16*)Bm, (const bf16*)Cm, ldbc, (const bf16*)dy, lddy,
-                                                               (const bf16*)ds_bf16, dt, a, D, (bf16*)dx, lddx, nullptr,
+  CUtensorMap tmRow, tmCol, tmV, tmS;
+  if (make_tmap_bf16_3d(&tmRow, Bm, B, T, (long long)G * N, ldbc, 128) || make_tmap_bf16_3d(&tmCol, Cm, B, T, (long long)G * N, ldbc, 128) ||
+      make_tmap_bf16_3d(&tmV, dy, B, T, (long long)H * P, lddy, 128) ||
+      make_tmap_bf16_2d(&tmS, ds_bf16, (long long)B * nc * H * P, N, N, 64)) return 1;
+  ssd_scan_kernel<true><<<grid, kScanThreads, kScanSmem, stream>>>(tmRow, tmCol, tmV, tmS, dt, a, D, (bf16*)dx, lddx, nullptr,
                                                                (const bf16*)x, ldx, ddt1, ddt2, dD, T, H, G, nc, hgs);
   return check_launch("ssd_chunk_scan_bwd_dx");
 }
