@@ -367,19 +367,21 @@ int make_tmap_bf16_2d(CUtensorMap* map, const void* ptr, long long rows, long lo
 }
 
 // 3-D bf16 [d2][d1][cols] view of a row-major matrix whose rows are (d2, d1) pairs (row stride ld elements),
-// box {64, box_rows, 1}, 128B swizzle.  Rows past d1 inside a box read as zeros (ragged last chunk of a sequence).
+// box {box_cols, box_rows, 1}; box_cols 64 -> 128B swizzle, 32 -> 64B swizzle.  Rows past d1 inside a box read
+// as zeros and are dropped on stores (ragged last chunk of a sequence).
 int make_tmap_bf16_3d(CUtensorMap* map, const void* ptr, long long d2, long long d1, long long cols, long long ld,
-                      int box_rows) {
+                      int box_rows, int box_cols) {
   EncodeTiledFn enc = get_encode_fn();
   MB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point not available");
   MB_REQUIRE(((uintptr_t)ptr & 15) == 0 && (ld * 2) % 16 == 0,
              "TMA operand must be 16-byte aligned with a row stride that is a multiple of 8 elements (ptr=%p ld=%lld)", ptr, ld);
   cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)d1, (cuuint64_t)d2};
   cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)d1 * (cuuint64_t)ld * 2};
-  cuuint32_t box[3] = {64, (cuuint32_t)box_rows, 1};
+  MB_REQUIRE(box_cols == 64 || box_cols == 32, "make_tmap_bf16_3d: box_cols must be 64 or 32");
+  cuuint32_t box[3] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows, 1};
   cuuint32_t estr[3] = {1, 1, 1};
   CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, box_cols == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   MB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(3d) failed with %d (d2=%lld d1=%lld cols=%lld ld=%lld)", (int)r, d2, d1, cols, ld);
   return 0;

@@ -109,38 +109,43 @@ ssd_outer_kernel(const bf16* __restrict__ arow, long long lda, const bf16* __res
 //
 //   warps 0-7   "scale"     read the CB tile from TMEM, apply decay / mask / dt, write the bf16
 //                           operand G one 128-column half-tile at a time into a 2-slot smem ring
-//   warps 8-11  "epilogue"  read the finished accumulators of the previous head from TMEM, add the
+//   warps 8-15  "epilogue"  read the finished accumulators of the previous head from TMEM, add the
 //                           skip terms, store y / dx
-//   warp 12     "mma"       one lane issues tcgen05.mma: C.S^T (per head) and G.X (per half-tile);
+//   warp 16     "mma"       one lane issues tcgen05.mma: C.S^T (per head) and G.X (per half-tile);
 //                           tcgen05.commit frees G slots and publishes accumulators
-//   warp 13     "producer"  one lane issues the TMA loads: row / column operands, then the X / state
+//   warp 17     "producer"  one lane issues the TMA loads: row / column operands, then the X / state
 //                           tiles of head+2 as soon as the epilogue warps hold their X rows of head
 // Accumulators are double-buffered in TMEM (CB 256 cols + 2 x (64 + 64)), per-head tiles in smem, so
 // head h+1 is being scaled while head h is multiplied and head h-1 is written out.
 // ------------------------------------------------------------------------------------------
+#ifndef MB_EXP_NOSTORE
+#define MB_EXP_NOSTORE 0
+#endif
 #ifdef MB_SSD_TIMING
 __device__ long long g_tlog[32][64];   // [warp][event]: store-only marks (no atomics -> ~tens of cycles each)
 __device__ int g_tmeta[32][64];
 #endif
 constexpr int kScanWarpsScale = 8;   // measured: 16 scale warps (one 32-column chunk each) is not faster
 constexpr int kScanWarpsProd = 1;    // one lane of it issues every TMA load (operands, per-head X / state tiles)
-constexpr int kScanThreads = (kScanWarpsScale + 4 + 1 + kScanWarpsProd) * 32;
-constexpr int kScanMaxHeads = 8;     // heads per CTA sharing one C.B^T (amortises the prologue)
+constexpr int kScanWarpsEpi = 8;     // two per 32-row TMEM lane group, 32 head-dim columns each
+constexpr int kScanThreads = (kScanWarpsScale + kScanWarpsEpi + 1 + kScanWarpsProd) * 32;
+constexpr int kScanMaxHeads = 6;     // heads per CTA sharing one C.B^T (amortises the prologue)
 constexpr int kScanSmem = 128 * 2 * 128     /* sR  row operand  [128][2 kblk]               32 KB */
                         + 2 * (128 * 128 * 2) /* sG ring: 2 x [128][128] bf16 (aliases sC)     64 KB */
                         + 2 * kL * 128      /* sV  X_h / dY_h   [256][1 atom]   x2 buffers   64 KB */
                         + 2 * kP * 2 * 128  /* sS  S_prev_h / dS_h [64][2 kblk] x2           32 KB */
                         + kScanMaxHeads * 2 * kL * 4 /* a | dt of every head of the group, loaded once    16 KB */
-                        + 16 * 64 * 4       /* per-scale-warp column-factor scratch                     4 KB */
-                        + 128 + 1024;
+                        + kScanWarpsScale * 64 * 4 /* per-scale-warp column-factor scratch                2 KB */
+                        + kScanWarpsEpi * 2048 /* per-epilogue-warp TMA-store staging [32][64 B]      16 KB */
+                        + 256 + 1024;
 
 template <bool BWD>
 __global__ void __launch_bounds__(kScanThreads, 1)
 ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant__ CUtensorMap tmCol,
                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmS,
+                const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmOut2,
                 const float* __restrict__ dtv, const float* __restrict__ av, const float* __restrict__ Dp,
-                bf16* __restrict__ outp, long long ldo, bf16* __restrict__ out2, const bf16* __restrict__ xsrc,
-                long long ldx, float* __restrict__ ddt1, float* __restrict__ ddt2, float* __restrict__ dD, int T,
+ float* __restrict__ ddt1, float* __restrict__ ddt2, float* __restrict__ dD, int T,
                 int H, int G, int nc, int hgs) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align1024(smem_raw);
@@ -150,7 +155,8 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
   uint8_t* sV0 = sG + 2 * 32768;
   uint8_t* sS0 = sV0 + 2 * kL * 128;
   float* s_ad = reinterpret_cast<float*>(sS0 + 2 * kP * 2 * 128);  // [hgs <= kScanMaxHeads][a(256) | dt(256)]
-  float* s_wscr = s_ad + kScanMaxHeads * 2 * kL;                                 // [scale warp][2][32] column factors
+  uint8_t* s_stage = reinterpret_cast<uint8_t*>(s_ad + kScanMaxHeads * 2 * kL);  // [epilogue warp][32 rows][64 B], 64B swizzle
+  float* s_wscr = reinterpret_cast<float*>(s_stage + kScanWarpsEpi * 2048);      // [scale warp][2][32] column factors
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_wscr + kScanWarpsScale * 64);
   uint64_t* cb_bar = bars;            // 1
   uint64_t* g_full = bars + 1;        // [2]  one arrival per scale warp
@@ -160,7 +166,8 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
   uint64_t* tiles_full = bars + 9;    // [2]  TMA transaction barrier (expect_tx by the producer lane)
   uint64_t* tiles_empty = bars + 11;  // [2]  one arrival per epilogue warp once its X row is in registers
   uint64_t* ld_bar = bars + 13;       // 1    TMA transaction barrier for the row / column operands
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
+  uint64_t* x_full = bars + 14;       // [kScanWarpsEpi]  backward: per-warp TMA load of its 32 x 32 tile of x
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14 + kScanWarpsEpi);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int rh = blockIdx.x & 1;
@@ -173,19 +180,19 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
   const int c0 = BWD ? rh * 128 : 0;
   const int ncols = BWD ? (2 - rh) * 128 : (rh + 1) * 128;
   const int nhalves = ncols >> 7;
-  const size_t row_base = (size_t)b * T + (size_t)c * kL;
 
   if (tid == 0) {
     mbar_init(cb_bar, 1);
     mbar_init(ld_bar, 1);
+    for (int i = 0; i < kScanWarpsEpi; ++i) mbar_init(&x_full[i], 1);
     for (int i = 0; i < 2; ++i) {
       // one arrival per WARP (after __syncwarp): hundreds of per-thread arrivals on one mbarrier word serialise
       mbar_init(&g_full[i], kScanWarpsScale); mbar_init(&g_empty[i], 1); mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], 4); mbar_init(&tiles_full[i], 1); mbar_init(&tiles_empty[i], 4);
+      mbar_init(&acc_empty[i], kScanWarpsEpi); mbar_init(&tiles_full[i], 1); mbar_init(&tiles_empty[i], kScanWarpsEpi);
     }
     fence_mbar_init();
   }
-  if (warp == kScanWarpsScale + 4) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
+  if (warp == kScanWarpsScale + kScanWarpsEpi) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
 
   // per-head tiles by TMA (one lane): V tile [ncols][64] as 128-row boxes, state tile [64][128] as two
   // 64-column boxes; both land 128B-swizzled exactly as the UMMA descriptors expect them
@@ -215,7 +222,7 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   const uint32_t tCB = tmem;
-  if (warp == kScanWarpsScale + 5 && lane == 0) {
+  if (warp == kScanWarpsScale + kScanWarpsEpi + 1 && lane == 0) {
     // row / column operands, then the tiles of heads 0 and 1
     mbar_arrive_expect_tx(ld_bar, (uint32_t)((128 + ncols) * 2 * 128));
     for (int kb = 0; kb < 2; ++kb) {
@@ -226,7 +233,7 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
     issue_head(0);
     if (hgs > 1) issue_head(1);
   }
-  if (warp == kScanWarpsScale + 4 && lane == 0) {
+  if (warp == kScanWarpsScale + kScanWarpsEpi && lane == 0) {
     mbar_wait(ld_bar, 0);
     tc_fence_after();
     const uint32_t idesc = make_idesc_bf16(128, ncols, MAJOR_K, MAJOR_K);
@@ -344,14 +351,23 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
         TMARK("scale", hh, "half_done");
       }
     }
-  } else if (warp < kScanWarpsScale + 4) {
+  } else if (warp < kScanWarpsScale + kScanWarpsEpi) {
     // =================================== epilogue warps ===================================
     const int lg = warp & 3;
+    const int pc0 = ((warp - kScanWarpsScale) >> 2) * 32;   // this warp's 32 of the 64 head-dim columns
     const int r = lg * 32 + lane, ri = r0 + r;
     const uint32_t lane_sel = (uint32_t)(lg * 32) << 16;
+    const int ew = warp - kScanWarpsScale;
+    uint8_t* stg = s_stage + ew * 2048;            // this warp's [32 rows][64 B] staging tile (64B swizzle)
+    const int trow = c * kL + r0 + lg * 32;
     for (int hh = 0; hh < hgs; ++hh) {
       const int h = h_first + hh;
       const int acc = hh & 1;
+      if (BWD && lane == 0) {  // backward also needs x[rows, h, cols]: TMA it into the staging tile while waiting
+        tma_store_wait_read<0>();
+        mbar_arrive_expect_tx(&x_full[ew], 2048);
+        tma_load_3d(stg, &tmOut2, &x_full[ew], h * kP + pc0, trow, b);
+      }
       TMARK("epi", hh, "wait_acc");
       mbar_wait(&acc_full[acc], (hh >> 1) & 1);
       tc_fence_after();
@@ -364,9 +380,10 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
       // Take this thread's X row (128 B) into registers; once all four epilogue warps have theirs the
       // slot is free and the producer warps stream the tiles of head hh+2 in underneath this epilogue.
       mbar_wait(&tiles_full[acc], (hh >> 1) & 1);  // long complete; makes the TMA-written tile visible to this thread
-      uint4 xrow[8];
+      uint4 xrow[4];
 #pragma unroll
-      for (int q = 0; q < 8; ++q) xrow[q] = *reinterpret_cast<const uint4*>(sV + vrow * 128 + ((q ^ (vrow & 7)) << 4));
+      for (int q = 0; q < 4; ++q)
+        xrow[q] = *reinterpret_cast<const uint4*>(sV + vrow * 128 + ((((pc0 >> 3) + q) ^ (vrow & 7)) << 4));
       __syncwarp();
       if (lane == 0) mbar_arrive(&tiles_empty[acc]);
       const uint32_t tOff = tmem + 256 + acc * 128, tDiag = tOff + 64;
@@ -377,9 +394,11 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
       const float dt_i = s_dt[ri];
       const float el = __expf(s_a[kL - 1] - a_i);
       const float ea = __expf(a_i);
+      if (BWD) mbar_wait(&x_full[ew], hh & 1);
+      uint4 pk_y[4], pk_off[4];  // this row's 32 output columns (and, forward, the y_off ones), packed bf16
 #pragma unroll
-      for (int ph = 0; ph < 4; ++ph) {  // 16 head-dim columns at a time (register budget: 96 / thread)
-        const int p0 = ph * 16;
+      for (int ph = 0; ph < 2; ++ph) {  // 16 head-dim columns at a time
+        const int p0 = pc0 + ph * 16;
         uint32_t vo[16], vd[16];
         tmem_ld16(tOff + lane_sel + p0, vo);
         tmem_ld16(tDiag + lane_sel + p0, vd);
@@ -395,20 +414,21 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
         if (!BWD) {
 #pragma unroll
           for (int j = 0; j < 16; ++j) o[j] = ea * __uint_as_float(vo[j]);
-          if (ri < valid) {  // y_off = exp(a_t) C_t S_prev^T alone is kept for backward (see ssd_bwd_finalize)
-            bf16* dst2 = out2 + (row_base + ri) * ldo + h * kP + p0;
 #pragma unroll
-            for (int q = 0; q < 2; ++q) st8(dst2 + 8 * q, pack8(o + 8 * q));
+          for (int q = 0; q < 2; ++q) {  // y_off = exp(a_t) C_t S_prev^T alone is kept for backward (see ssd_bwd_finalize)
+            const bf16x8 t8 = pack8(o + 8 * q);
+            memcpy(&pk_off[2 * ph + q], &t8, 16);
           }
 #pragma unroll
           for (int j = 0; j < 16; ++j) o[j] += __uint_as_float(vd[j]) + Dh * xv[j];
         } else {
-          if (ri < valid) {
-            const bf16* xr = xsrc + (row_base + ri) * ldx + h * kP + p0;
+          {  // rows past the end of the sequence read as zeros (TMA fill), so no guard is needed
 #pragma unroll
             for (int q = 0; q < 2; ++q) {
               float xx[8];
-              unpack8(ld8(xr + 8 * q), xx);
+              bf16x8 t8;
+              memcpy(&t8, stg + lane * 64 + (((2 * ph + q) ^ ((lane >> 1) & 3)) << 4), 16);
+              unpack8(t8, xx);
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
                 s1 += xx[j] * __uint_as_float(vd[8 * q + j]);
@@ -421,29 +441,46 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
 #pragma unroll
           for (int j = 0; j < 16; ++j) o[j] = dt_i * __uint_as_float(vd[j]) + w * __uint_as_float(vo[j]) + Dh * xv[j];
         }
-        if (ri < valid) {
-          bf16* dst = outp + (row_base + ri) * ldo + h * kP + p0;
 #pragma unroll
-          for (int q = 0; q < 2; ++q) st8(dst + 8 * q, pack8(o + 8 * q));
+        for (int q = 0; q < 2; ++q) {
+          const bf16x8 t8 = pack8(o + 8 * q);
+          memcpy(&pk_y[2 * ph + q], &t8, 16);
         }
       }
+      // the accumulators are in registers: hand the TMEM buffer back before the stores
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[acc]);
+      // Row-per-thread global stores would touch 32 different lines with 16 bytes each.  Instead the warp
+      // lays its 32 x 32 tile out in shared memory (64B-swizzled rows) and one lane issues a TMA store;
+      // the tensor map is [B][T][H*P], so rows past the end of the sequence are dropped by the hardware.
+      auto stage_and_store = [&](const uint4* pk, const CUtensorMap* map) {
+        if (lane == 0) tma_store_wait_read<0>();  // the previous store has finished reading the staging tile
+        __syncwarp();
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          *reinterpret_cast<uint4*>(stg + lane * 64 + ((q ^ ((lane >> 1) & 3)) << 4)) = pk[q];
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_3d(map, stg, h * kP + pc0, trow, b);
+          tma_store_commit();
+        }
+      };
+      if (!BWD) stage_and_store(pk_off, &tmOut2);
+      stage_and_store(pk_y, &tmOut);
       if (BWD) {
-        if (ri < valid) {  // one thread owns a (b, c, h, row): plain stores, no pre-zeroing needed
-          ddt1[sbase + ri] = s1;
-          ddt2[sbase + ri] = el * s2;
-        } else if (ri < kL) {
-          ddt1[sbase + ri] = 0.f;
-          ddt2[sbase + ri] = 0.f;
+        if (ri < valid) {  // two threads (one per column half) own a (b, c, h, row): buffers are pre-zeroed
+          atomicAdd(ddt1 + sbase + ri, s1);
+          atomicAdd(ddt2 + sbase + ri, el * s2);
         }
         sd = warp_sum(sd);
         if (lane == 0) atomicAdd(dD + h, sd);
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&acc_empty[acc]);
       TMARK("epi", hh, "epi_done");
     }
-  } else if (warp == kScanWarpsScale + 4) {
+    if (lane == 0) tma_store_wait_read<0>();  // staging must outlive the last store's read
+  } else if (warp == kScanWarpsScale + kScanWarpsEpi) {
     if (lane == 0) {
     // =================================== MMA issuer ===================================
     const uint32_t r_addr = smem_u32(sR);
@@ -488,7 +525,7 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == kScanWarpsScale + 4) tmem_dealloc(tmem, 512);
+  if (warp == kScanWarpsScale + kScanWarpsEpi) tmem_dealloc(tmem, 512);
 #ifdef MB_SSD_TIMING
   if (tprint && lane == 0) {
     for (int i = 0; i < tidx; ++i) printf("T %d %d %c %lld\n", warp, (g_tmeta[warp][i] >> 8) & 255, (char)(g_tmeta[warp][i] & 255), g_tlog[warp][i]);
@@ -515,7 +552,7 @@ static int pick_head_group(int heads_per_group, int ctas_per_head, int heads) {
 }  // namespace ssd
 // tensor-map builders shared with the GEMM (gemm.cu)
 int make_tmap_bf16_2d(CUtensorMap* map, const void* ptr, long long rows, long long cols, long long ld, int box_rows);
-int make_tmap_bf16_3d(CUtensorMap* map, const void* ptr, long long d2, long long d1, long long cols, long long ld, int box_rows);
+int make_tmap_bf16_3d(CUtensorMap* map, const void* ptr, long long d2, long long d1, long long cols, long long ld, int box_rows, int box_cols);
 }  // namespace mb
 using namespace mb;
 using namespace mb::ssd;
@@ -559,17 +596,20 @@ extern "C" int mb_ssd_chunk_scan_fwd(const void* Cm, const void* Bm, long long l
   if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_scan_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kScanSmem)); once = true; }
   dim3 grid(B * nc * 2, H / hgs);
   CUtensorMap tmRow, tmCol, tmV, tmS;
-  if (make_tmap_bf16_3d(&tmRow, Cm, B, T, (long long)G * N, ldbc, 128) || make_tmap_bf16_3d(&tmCol, Bm, B, T, (long long)G * N, ldbc, 128) ||
-      make_tmap_bf16_3d(&tmV, x, B, T, (long long)H * P, ldx, 128) ||
+  if (make_tmap_bf16_3d(&tmRow, Cm, B, T, (long long)G * N, ldbc, 128, 64) || make_tmap_bf16_3d(&tmCol, Bm, B, T, (long long)G * N, ldbc, 128, 64) ||
+      make_tmap_bf16_3d(&tmV, x, B, T, (long long)H * P, ldx, 128, 64) ||
       make_tmap_bf16_2d(&tmS, sprev_bf16, (long long)B * nc * H * P, N, N, 64)) return 1;
-  ssd_scan_kernel<false><<<grid, kScanThreads, kScanSmem, stream>>>(tmRow, tmCol, tmV, tmS, dt, a, D, (bf16*)y, ldy, (bf16*)y_off,
-                                                                nullptr, 0, nullptr, nullptr, nullptr, T, H, G, nc, hgs);
+  CUtensorMap tmOut, tmOut2;
+  if (make_tmap_bf16_3d(&tmOut, y, B, T, (long long)H * P, ldy, 32, 32) ||
+      make_tmap_bf16_3d(&tmOut2, y_off, B, T, (long long)H * P, ldy, 32, 32)) return 1;
+  ssd_scan_kernel<false><<<grid, kScanThreads, kScanSmem, stream>>>(tmRow, tmCol, tmV, tmS, tmOut, tmOut2, dt, a, D,
+                                                                nullptr, nullptr, nullptr, T, H, G, nc, hgs);
   return check_launch("ssd_chunk_scan_fwd");
 }
 
 // dx[s,h,:] = dt_s sum_{t>=s} (B_s.C_t) exp(a_t - a_s) dy_t + exp(a_last - a_s) dt_s B_s dS^T + D_h dy_s
 // ddt1[s] += sum_p x (M-part / dt_s),  ddt2[s] += exp(a_last - a_s) sum_p x (B dS^T),  dD[h] += sum dy.x
-// (dD is pre-zeroed by the caller; ddt1 / ddt2 are fully overwritten)
+// (dD, ddt1 and ddt2 are pre-zeroed by the caller: each gets two commutative fp32 atomic adds per element)
 extern "C" int mb_ssd_chunk_scan_bwd_dx(const void* Bm, const void* Cm, long long ldbc, const void* dy, long long lddy,
                                         const void* ds_bf16, const float* dt, const float* a, const float* D,
                                         void* dx, long long lddx, const void* x, long long ldx, float* ddt1,
@@ -582,10 +622,12 @@ extern "C" int mb_ssd_chunk_scan_bwd_dx(const void* Bm, const void* Cm, long lon
   if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_scan_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kScanSmem)); once = true; }
   dim3 grid(B * nc * 2, H / hgs);
   CUtensorMap tmRow, tmCol, tmV, tmS;
-  if (make_tmap_bf16_3d(&tmRow, Bm, B, T, (long long)G * N, ldbc, 128) || make_tmap_bf16_3d(&tmCol, Cm, B, T, (long long)G * N, ldbc, 128) ||
-      make_tmap_bf16_3d(&tmV, dy, B, T, (long long)H * P, lddy, 128) ||
+  if (make_tmap_bf16_3d(&tmRow, Bm, B, T, (long long)G * N, ldbc, 128, 64) || make_tmap_bf16_3d(&tmCol, Cm, B, T, (long long)G * N, ldbc, 128, 64) ||
+      make_tmap_bf16_3d(&tmV, dy, B, T, (long long)H * P, lddy, 128, 64) ||
       make_tmap_bf16_2d(&tmS, ds_bf16, (long long)B * nc * H * P, N, N, 64)) return 1;
-  ssd_scan_kernel<true><<<grid, kScanThreads, kScanSmem, stream>>>(tmRow, tmCol, tmV, tmS, dt, a, D, (bf16*)dx, lddx, nullptr,
-                                                               (const bf16*)x, ldx, ddt1, ddt2, dD, T, H, G, nc, hgs);
+  CUtensorMap tmOut, tmX;  // the kernel's second output map is unused in backward: it carries x instead
+  if (make_tmap_bf16_3d(&tmOut, dx, B, T, (long long)H * P, lddx, 32, 32) ||
+      make_tmap_bf16_3d(&tmX, x, B, T, (long long)H * P, ldx, 32, 32)) return 1;
+  ssd_scan_kernel<true><<<grid, kScanThreads, kScanSmem, stream>>>(tmRow, tmCol, tmV, tmS, tmOut, tmX, dt, a, D, ddt1, ddt2, dD, T, H, G, nc, hgs);
   return check_launch("ssd_chunk_scan_bwd_dx");
 }

@@ -11,5 +11,5 @@ lines=[l.split() for l in open('gpurun_out/timeline.txt') if l.startswith('T ')]
 n=len(lines)//3
 ev=sorted(((int(w),int(h),c,int(t)) for _,w,h,c,t in lines[-n:]), key=lambda e:e[3])
 for w,h,c,t in ev:
-    if w in (0,4,8,12): print(f"w{w:2d} h{h} {c} {t}")
+    if w in (0,3,7,8,16): print(f"w{w:2d} h{h} {c} {t}")
 PY
