@@ -16,7 +16,7 @@ namespace ssd {
 
 constexpr int kThreadsB = 256;
 
-constexpr int kDcbSmem = 2 * 2 * (128 * 128) + 2 * 2 * kL * 4 + 64 + 1024;  // double-buffered per-head tiles
+constexpr int kDcbSmem = 2 * 2 * (128 * 128) + 2 * 2 * kL * 4 + 2 * 4 * 128 * 4 + 64 + 1024;  // double-buffered per-head tiles + column factors
 
 __global__ void __launch_bounds__(kThreadsB, 2)
 ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restrict__ x, long long ldx,
@@ -26,7 +26,9 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align1024(smem_raw);
   float* s_ad = reinterpret_cast<float*>(smem + 2 * 2 * 128 * 128);  // [2][a(256) | dt(256)]
-  uint64_t* bar = reinterpret_cast<uint64_t*>(s_ad + 2 * 2 * kL);
+  float* s_cf = s_ad + 2 * 2 * kL;                                   // [4 lane groups][128]  exp(a_ref - a_j)
+  float* s_cd = s_cf + 4 * 128;                                      // [4 lane groups][128]  exp(a_ref - a_j) dt_j
+  uint64_t* bar = reinterpret_cast<uint64_t*>(s_cd + 4 * 128);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 1);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -82,7 +84,7 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
   const int r = lg * 32 + lane;
   const int ri = ri0 + r;
   const uint32_t lane_sel = (uint32_t)(lg * 32) << 16;
-  const int warp_row_max = ri0 + lg * 32 + 31;
+  const int warp_row_min = ri0 + lg * 32, warp_row_max = warp_row_min + 31;
   float acc[64];
 #pragma unroll
   for (int j = 0; j < 64; ++j) acc[j] = 0.f;
@@ -121,10 +123,23 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
         mma_bf16_ss(tmem, desc_kmajor(a_addr, 128, 0, ks), desc_kmajor(b_addr, 128, 0, ks), idesc, ks > 0 ? 1u : 0u);
       mma_commit(bar);
     }
+    {  // per (lane group, column) decay factors for the blocks strictly below the diagonal, where
+       // exp(a_i - a_j) = exp(a_i - a_ref) exp(a_ref - a_j) with both factors <= 1 (a_ref = first row of the group)
+      const int lgq = tid >> 6, col = (tid & 63) * 2;
+      const float aref = s_a[ri0 + lgq * 32];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const float cf = __expf(fminf(aref - s_a[cj0 + col + u], 0.f));
+        s_cf[lgq * 128 + col + u] = cf;
+        s_cd[lgq * 128 + col + u] = cf * s_dt[cj0 + col + u];
+      }
+    }
+    __syncthreads();
     mbar_wait(bar, phase);
     phase ^= 1;
     tc_fence_after();
     const float a_i = s_a[ri];
+    const float rowf = __expf(fminf(a_i - s_a[warp_row_min], 0.f));
     float rsum = 0.f;  // sum_j (dM o M)[ri, j] over this thread's columns, with M rounded exactly as
                        // the dx kernel rounds it (see ssd_bwd_finalize: makes row - column sums cancel)
 #pragma unroll
@@ -135,21 +150,38 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
       tmem_ld16(tmem + lane_sel + k0, v);
       tmem_ld16(tCB + lane_sel + k0, cbv);
       tmem_ld_wait();
+      if (cj0 + k0 + 15 < warp_row_min) {  // warp-uniform: strictly below the diagonal, no mask, no exp
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {  // branch-free, 128-bit broadcast loads of a_j / dt_j
-        const float4 a4 = *reinterpret_cast<const float4*>(s_a + cj0 + k0 + 4 * q);
-        const float4 d4 = *reinterpret_cast<const float4*>(s_dt + cj0 + k0 + 4 * q);
-        const float aj[4] = {a4.x, a4.y, a4.z, a4.w}, dj[4] = {d4.x, d4.y, d4.z, d4.w};
+        for (int q = 0; q < 4; ++q) {
+          const float4 f4 = *reinterpret_cast<const float4*>(s_cf + lg * 128 + k0 + 4 * q);
+          const float4 d4 = *reinterpret_cast<const float4*>(s_cd + lg * 128 + k0 + 4 * q);
+          const float4 t4 = *reinterpret_cast<const float4*>(s_dt + cj0 + k0 + 4 * q);
+          const float cf[4] = {f4.x, f4.y, f4.z, f4.w}, cd[4] = {d4.x, d4.y, d4.z, d4.w}, dj[4] = {t4.x, t4.y, t4.z, t4.w};
 #pragma unroll
-        for (int t = 0; t < 4; ++t) {
-          const int cj = cj0 + k0 + 4 * q + t;
-          const float e = __expf(fminf(a_i - aj[t], 0.f));
-          const float pd = __uint_as_float(v[4 * q + t]) * dj[t];   // P * dt_j
-          const unsigned keep = (cj <= ri) ? 0xffffffffu : 0u;
-          acc[ch * 16 + 4 * q + t] += __uint_as_float(__float_as_uint(pd * e) & keep);
-          // M'[ri,cj] = bf16(CB * e), the operand value the dx kernel multiplies with
-          const float mr = __bfloat162float(__float2bfloat16(__uint_as_float(cbv[4 * q + t]) * e));
-          rsum += __uint_as_float(__float_as_uint(pd * mr) & keep);
+          for (int t = 0; t < 4; ++t) {
+            const float p = __uint_as_float(v[4 * q + t]);
+            acc[ch * 16 + 4 * q + t] += p * (rowf * cd[t]);
+            const float mr = __bfloat162float(__float2bfloat16(__uint_as_float(cbv[4 * q + t]) * (rowf * cf[t])));
+            rsum += (p * dj[t]) * mr;
+          }
+        }
+      } else {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {  // branch-free, 128-bit broadcast loads of a_j / dt_j
+          const float4 a4 = *reinterpret_cast<const float4*>(s_a + cj0 + k0 + 4 * q);
+          const float4 d4 = *reinterpret_cast<const float4*>(s_dt + cj0 + k0 + 4 * q);
+          const float aj[4] = {a4.x, a4.y, a4.z, a4.w}, dj[4] = {d4.x, d4.y, d4.z, d4.w};
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            const int cj = cj0 + k0 + 4 * q + t;
+            const float e = __expf(fminf(a_i - aj[t], 0.f));
+            const float pd = __uint_as_float(v[4 * q + t]) * dj[t];   // P * dt_j
+            const unsigned keep = (cj <= ri) ? 0xffffffffu : 0u;
+            acc[ch * 16 + 4 * q + t] += __uint_as_float(__float_as_uint(pd * e) & keep);
+            // M'[ri,cj] = bf16(CB * e), the operand value the dx kernel multiplies with
+            const float mr = __bfloat162float(__float2bfloat16(__uint_as_float(cbv[4 * q + t]) * e));
+            rsum += __uint_as_float(__float_as_uint(pd * mr) & keep);
+          }
         }
       }
     }
