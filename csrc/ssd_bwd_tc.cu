@@ -196,9 +196,13 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
 }
 
 // ------------------------------------------------------------------------------------------
-constexpr int kDbdcStage = 128 * 128 + 64 * 2 * 128;  // A tile 16 KB + B tile 16 KB
-constexpr int kDbdcSmem = 2 * kDbdcStage + 64 + 1024;
+constexpr int kDbdcStages = 3;
+constexpr int kDbdcStage = 128 * 128 + 64 * 2 * 128 + 2048;  // A tile 16 KB + B tile 16 KB + a | dt | a_last of the rows
+constexpr int kDbdcSmem = kDbdcStages * kDbdcStage + 64 + 1024;
 
+// Software pipeline: every operand travels by cp.async into a 3-stage ring, two stages ahead of the MMA.
+// The activation tiles need a per-row factor (e^{a_i} or w_j); each thread scales, in place, exactly the
+// 16-byte chunks its own cp.async brought in, so that pass needs no barrier of its own.
 template <bool IS_DB>
 __global__ void __launch_bounds__(kThreadsB, 2)
 ssd_dbdc_kernel(const bf16* __restrict__ dcb,                       // [B,nc,G,256,256]
@@ -210,8 +214,8 @@ ssd_dbdc_kernel(const bf16* __restrict__ dcb,                       // [B,nc,G,2
                 int T, int H, int G, int nc) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align1024(smem_raw);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * kDbdcStage);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kDbdcStages * kDbdcStage);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + kDbdcStages);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int rb = blockIdx.x & 1;
@@ -224,7 +228,10 @@ ssd_dbdc_kernel(const bf16* __restrict__ dcb,                       // [B,nc,G,2
   const size_t row_base = (size_t)b * T + (size_t)c * kL;
   const bf16* G_base = dcb + ((size_t)bc * G + g) * kL * kL;
 
-  if (tid == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); fence_mbar_init(); }
+  if (tid == 0) {
+    for (int i = 0; i < kDbdcStages; ++i) mbar_init(&bars[i], 1);
+    fence_mbar_init();
+  }
   if (warp == 0) { tmem_alloc(tmem_slot, 128); tmem_relinquish(); }
   tc_fence_before();
   __syncthreads();
@@ -236,42 +243,73 @@ ssd_dbdc_kernel(const bf16* __restrict__ dcb,                       // [B,nc,G,2
   const int k_end = IS_DB ? kL : m0 + 128;
   const int n_part1 = (k_end - k_begin) / 64;
   const int n_stages = n_part1 + hpg;
+  const int valid_m = max(0, min(128, valid - m0));
 
-  for (int s = 0; s < n_stages; ++s) {
-    const int buf = s & 1;
-    const int use = s >> 1;
-    if (use > 0) mbar_wait(&bars[buf], (use - 1) & 1);  // MMAs that read this buffer have retired
-    uint8_t* sA = smem + buf * kDbdcStage;
+  auto issue = [&](int s) {
+    uint8_t* sA = smem + (s % kDbdcStages) * kDbdcStage;
     uint8_t* sB = sA + 128 * 128;
-    bool a_mn;
     if (s < n_part1) {
       const int kk = k_begin + s * 64;
       const int kvalid = max(0, min(64, valid - kk));
-      if (!IS_DB) {
-        // A = G[m0 + r, kk .. kk+63]  (K-major, 128 rows) ; B = Bm[kk + krow, n]  (MN-major, 64 k-rows)
+      if (!IS_DB)  // A = G[m0 + r, kk .. kk+63]  (K-major, 128 rows) ; B = Bm[kk + krow, n]  (MN-major, 64 k-rows)
         load_tile<1, false>(sA, G_base + (size_t)m0 * kL + kk, kL, 128, 128, NoScale(), tid, kThreadsB);
-        a_mn = false;
-      } else {
-        // A = G[kk + krow, m0 .. m0+127]  (MN-major: 64 k-rows x 2 atoms)
+      else         // A = G[kk + krow, m0 .. m0+127]  (MN-major: 64 k-rows x 2 atoms)
         load_tile<2, false>(sA, G_base + (size_t)kk * kL + m0, kL, 64, 64, NoScale(), tid, kThreadsB);
-        a_mn = true;
-      }
       load_tile<2, false>(sB, bc_op + (row_base + kk) * ldbc + g * kN, ldbc, 64, kvalid, NoScale(), tid, kThreadsB);
     } else {
       const int h = g * hpg + (s - n_part1);
       const size_t sbase = ((size_t)bc * H + h) * kL;
-      const float a_last = av[sbase + kL - 1];
-      auto scale = [&](int row, int /*blk*/) {
-        const float a = av[sbase + m0 + row];
-        return IS_DB ? __expf(a_last - a) * dtv[sbase + m0 + row] : __expf(a);
-      };
-      load_tile<1, true>(sA, act + (row_base + m0) * ldact + h * kP, ldact, 128, max(0, min(128, valid - m0)), scale,
-                         tid, kThreadsB);
-      a_mn = false;
+      load_tile<1, false>(sA, act + (row_base + m0) * ldact + h * kP, ldact, 128, valid_m, NoScale(), tid, kThreadsB);
       load_tile<2, false>(sB, st + ((size_t)bc * H + h) * kP * kN, kN, kP, kP, NoScale(), tid, kThreadsB);
+      const uint32_t sc = smem_u32(sB + 64 * 2 * 128);
+      if (tid < 128) {
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sc + tid * 4), "l"(av + sbase + m0 + tid) : "memory");
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sc + 512 + tid * 4), "l"(dtv + sbase + m0 + tid) : "memory");
+      } else if (tid == 128) {
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sc + 1024), "l"(av + sbase + kL - 1) : "memory");
+      }
     }
-    cp_async_commit();
-    cp_async_wait<0>();
+  };
+
+  issue(0);
+  cp_async_commit();
+  if (n_stages > 1) issue(1);
+  cp_async_commit();
+  for (int s = 0; s < n_stages; ++s) {
+    const int buf = s % kDbdcStages;
+    if (s + 2 < n_stages) {
+      // the ring slot of stage s+2 was last read by the MMAs of stage s-1
+      if (s >= 1) mbar_wait(&bars[(s + 2) % kDbdcStages], ((s - 1) / kDbdcStages) & 1);
+      issue(s + 2);
+    }
+    cp_async_commit();   // (possibly empty) keeps one group per stage
+    cp_async_wait<2>();  // this thread's copies of stage s have landed
+    uint8_t* sA = smem + buf * kDbdcStage;
+    uint8_t* sB = sA + 128 * 128;
+    const bool a_mn = IS_DB && s < n_part1;
+    if (s >= n_part1) {
+      // the scale vectors were copied by other threads: one barrier for them, then in-place scaling of own chunks
+      __syncthreads();
+      const float* s_a = reinterpret_cast<const float*>(sB + 64 * 2 * 128);
+      const float a_last = s_a[256];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int idx = tid + k * kThreadsB;
+        const int cc = idx & 7, row = idx >> 3;
+        if (row < valid_m) {
+          const float f = IS_DB ? __expf(a_last - s_a[row]) * s_a[128 + row] : __expf(s_a[row]);
+          uint8_t* ptr = sA + row * 128 + ((cc ^ (row & 7)) << 4);
+          bf16x8 t8;
+          memcpy(&t8, ptr, 16);
+          float v[8];
+          unpack8(t8, v);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) v[e] *= f;
+          t8 = pack8(v);
+          memcpy(ptr, &t8, 16);
+        }
+      }
+    }
     fence_proxy_async_smem();
     __syncthreads();
     if (tid == 0) {
@@ -288,7 +326,7 @@ ssd_dbdc_kernel(const bf16* __restrict__ dcb,                       // [B,nc,G,2
   }
   {
     const int s_last = n_stages - 1;
-    mbar_wait(&bars[s_last & 1], (s_last >> 1) & 1);  // MMAs retire in order: the last commit covers all
+    mbar_wait(&bars[s_last % kDbdcStages], (s_last / kDbdcStages) & 1);  // MMAs retire in order: the last commit covers all
     tc_fence_after();
   }
   const int lg = warp & 3, half = warp >> 2;
