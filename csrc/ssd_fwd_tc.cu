@@ -25,8 +25,8 @@ constexpr int kOuterSmem = 2 * (kOuterHalf * 2 * 128) + 2 * kL * 4 + 64 + 1024;
 template <bool DSTATE>
 __global__ void __launch_bounds__(kThreads, 3)
 ssd_outer_kernel(const bf16* __restrict__ arow, long long lda, const bf16* __restrict__ bop, long long ldb,
-                 const float* __restrict__ dtv, const float* __restrict__ av, float* __restrict__ out, int T,
-                 int H, int G, int nc, int hpc) {
+                 const float* __restrict__ dtv, const float* __restrict__ av, const __grid_constant__ CUtensorMap tmOut,
+                 int T, int H, int G, int nc, int hpc) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align1024(smem_raw);
   uint8_t* sA = smem;                                // [128 k-rows][2 atoms]  MN-major A
@@ -81,23 +81,30 @@ ssd_outer_kernel(const bf16* __restrict__ arow, long long lda, const bf16* __res
     tc_fence_after();
   }
 
+  // Epilogue: a thread owns one accumulator row, so direct stores would hit 32 different lines with 16 bytes
+  // each.  Every warp instead stages its [32 rows][32 fp32] blocks in the (now idle) operand buffers,
+  // 128B-swizzled, and one lane hands each block to a TMA store.
   const int lg = warp & 3, colhalf = warp >> 2;
-  const int r = lg * 32 + lane;
-  const int hh = r / kP, p = r % kP;
+  if (lg * 32 < hpc * kP) {
 #pragma unroll
-  for (int ch = 0; ch < 2; ++ch) {
-    const int col = colhalf * 64 + ch * 32;
-    uint32_t v[32];
-    tmem_ld32(tmem + ((uint32_t)(lg * 32) << 16) + col, v);
-    tmem_ld_wait();
-    if (hh < hpc) {
-      float* dst = out + (((size_t)bc * H + h0 + hh) * kP + p) * kN + col;
+    for (int ch = 0; ch < 2; ++ch) {
+      const int col = colhalf * 64 + ch * 32;
+      uint32_t v[32];
+      tmem_ld32(tmem + ((uint32_t)(lg * 32) << 16) + col, v);
+      tmem_ld_wait();
+      uint8_t* stg = smem + warp * 8192 + ch * 4096;
 #pragma unroll
-      for (int j = 0; j < 8; ++j)
-        *reinterpret_cast<float4*>(dst + 4 * j) =
-            make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]),
-                        __uint_as_float(v[4 * j + 3]));
+      for (int q = 0; q < 8; ++q)
+        *reinterpret_cast<uint4*>(stg + lane * 128 + ((q ^ (lane & 7)) << 4)) =
+            make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        tma_store_2d(&tmOut, stg, col, (bc * H + h0) * kP + lg * 32);
+        tma_store_commit();
+      }
     }
+    if (lane == 0) tma_store_wait_read<0>();
   }
   tc_fence_before();
   __syncthreads();
@@ -551,6 +558,7 @@ static int pick_head_group(int heads_per_group, int ctas_per_head, int heads) {
 
 }  // namespace ssd
 // tensor-map builders shared with the GEMM (gemm.cu)
+int make_tmap_f32_2d(CUtensorMap* map, const void* ptr, long long rows, long long cols, long long ld);
 int make_tmap_bf16_2d(CUtensorMap* map, const void* ptr, long long rows, long long cols, long long ld, int box_rows);
 int make_tmap_bf16_3d(CUtensorMap* map, const void* ptr, long long d2, long long d1, long long cols, long long ld, int box_rows, int box_cols);
 }  // namespace mb
@@ -572,14 +580,16 @@ extern "C" int mb_ssd_chunk_state(const void* arow, long long lda, const void* b
   const int nc = cdiv(T, L);
   const int hpc = ((H / G) % 2 == 0) ? 2 : 1;
   dim3 grid(B * nc, H / hpc);
+  CUtensorMap tmOut;
+  if (make_tmap_f32_2d(&tmOut, out, (long long)B * nc * H * P, N, N)) return 1;
   if (dstate) {
     static bool once = false;
     if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_outer_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kOuterSmem)); once = true; }
-    ssd_outer_kernel<true><<<grid, kThreads, kOuterSmem, stream>>>((const bf16*)arow, lda, (const bf16*)bop, ldb, dt, a, out, T, H, G, nc, hpc);
+    ssd_outer_kernel<true><<<grid, kThreads, kOuterSmem, stream>>>((const bf16*)arow, lda, (const bf16*)bop, ldb, dt, a, tmOut, T, H, G, nc, hpc);
   } else {
     static bool once = false;
     if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_outer_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kOuterSmem)); once = true; }
-    ssd_outer_kernel<false><<<grid, kThreads, kOuterSmem, stream>>>((const bf16*)arow, lda, (const bf16*)bop, ldb, dt, a, out, T, H, G, nc, hpc);
+    ssd_outer_kernel<false><<<grid, kThreads, kOuterSmem, stream>>>((const bf16*)arow, lda, (const bf16*)bop, ldb, dt, a, tmOut, T, H, G, nc, hpc);
   }
   return check_launch("ssd_chunk_state");
 }
