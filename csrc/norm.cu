@@ -302,97 +302,85 @@ gated_rmsnorm_bwd_kernel(const bf16* __restrict__ x, int ldx, const bf16* __rest
 }
 
 
-// Gated RMSNorm backward, G == 1 fast path, split in two so neither half is register-bound:
-//   (a) per-row kernel: dx, dz  (one warp per row, no cross-row state -> high occupancy)
-//   (b) column-strip kernel: dw[col] += sum_rows dout * x * silu(z) * rstd   (fp32 atomics per strip)
+// Gated RMSNorm backward, G == 1 fast path: persistent warps, one row at a time, two passes over the row.
+// The second pass re-reads the row (9 KB per warp, L1-resident) instead of parking 72 registers of packed
+// inputs; that leaves room for the 8 x NV weight-gradient accumulators a lane owns (its columns are the
+// same for every row), so dw costs one FFMA per element here and no second sweep over x / z / dout.
+// Per-block partials go to dw_partial[blockIdx][D]; colsum_partials_kernel folds them.
 template <int NV>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 gated_rmsnorm_bwd_rows_kernel(const bf16* __restrict__ x, int ldx, const bf16* __restrict__ z, int ldz,
                               const float* __restrict__ weight, const float* __restrict__ rstd_in,
                               const bf16* __restrict__ dout, int ldo, bf16* __restrict__ dx, int lddx,
-                              bf16* __restrict__ dz, int lddz, int M, int D) {
-  const int lane = threadIdx.x & 31;
-  const int row = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
-  if (row >= M) return;
+                              bf16* __restrict__ dz, int lddz, float* __restrict__ dw_partial, int M, int D) {
+  __shared__ float red[kWarpsPerBlock][32 * 8 + 8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nvec = D >> 3;
-  const float rstd = rstd_in[row];
-  // two passes over the row; the second re-reads it (9 KB per warp: L1-resident) instead of
-  // parking 72 registers of packed inputs, which keeps the kernel at full occupancy
-  float c = 0.f;
+  float dw[NV][8];
 #pragma unroll
-  for (int i = 0; i < NV; ++i) {
-    const int vec = lane + 32 * i;
-    if (vec < nvec) {
-      const int col = vec * 8;
-      float xv[8], zz[8], go[8], w[8];
-      unpack8(ld8(x + (size_t)row * ldx + col), xv);
-      unpack8(ld8(z + (size_t)row * ldz + col), zz);
-      unpack8(ld8(dout + (size_t)row * ldo + col), go);
-      ld8f(weight + col, w);
+  for (int i = 0; i < NV; ++i)
 #pragma unroll
-      for (int j = 0; j < 8; ++j) c += xv[j] * silu_f(zz[j]) * go[j] * w[j];
-    }
-  }
-  c = warp_sum(c) * rstd / (float)D;  // mean(xhat * w * dout)
+    for (int j = 0; j < 8; ++j) dw[i][j] = 0.f;
+  for (int row = blockIdx.x * kWarpsPerBlock + warp; row < M; row += gridDim.x * kWarpsPerBlock) {
+    const float rstd = rstd_in[row];
+    float c = 0.f;
 #pragma unroll
-  for (int i = 0; i < NV; ++i) {
-    const int vec = lane + 32 * i;
-    if (vec < nvec) {
-      const int col = vec * 8;
-      float xv[8], zz[8], go[8], w[8], ox[8], oz[8];
-      unpack8(ld8(x + (size_t)row * ldx + col), xv);
-      unpack8(ld8(z + (size_t)row * ldz + col), zz);
-      unpack8(ld8(dout + (size_t)row * ldo + col), go);
-      ld8f(weight + col, w);
+    for (int i = 0; i < NV; ++i) {
+      const int vec = lane + 32 * i;
+      if (vec < nvec) {
+        const int col = vec * 8;
+        float xv[8], zz[8], go[8], w[8];
+        unpack8(ld8(x + (size_t)row * ldx + col), xv);
+        unpack8(ld8(z + (size_t)row * ldz + col), zz);
+        unpack8(ld8(dout + (size_t)row * ldo + col), go);
+        ld8f(weight + col, w);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float sg, dsg;
-        silu_both(zz[j], sg, dsg);
-        const float xh = xv[j] * sg * rstd;
-        const float dxs = (go[j] * w[j] - xh * c) * rstd;
-        ox[j] = dxs * sg;
-        oz[j] = dxs * xv[j] * dsg;
+        for (int j = 0; j < 8; ++j) c += xv[j] * silu_f(zz[j]) * go[j] * w[j];
       }
-      st8(dx + (size_t)row * lddx + col, pack8(ox));
-      st8(dz + (size_t)row * lddz + col, pack8(oz));
+    }
+    c = warp_sum(c) * rstd / (float)D;  // mean(xhat * w * dout)
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vec = lane + 32 * i;
+      if (vec < nvec) {
+        const int col = vec * 8;
+        float xv[8], zz[8], go[8], w[8], ox[8], oz[8];
+        unpack8(ld8(x + (size_t)row * ldx + col), xv);
+        unpack8(ld8(z + (size_t)row * ldz + col), zz);
+        unpack8(ld8(dout + (size_t)row * ldo + col), go);
+        ld8f(weight + col, w);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float sg, dsg;
+          silu_both(zz[j], sg, dsg);
+          const float xh = xv[j] * sg * rstd;
+          const float dxs = (go[j] * w[j] - xh * c) * rstd;
+          ox[j] = dxs * sg;
+          oz[j] = dxs * xv[j] * dsg;
+          dw[i][j] += go[j] * xh;
+        }
+        st8(dx + (size_t)row * lddx + col, pack8(ox));
+        st8(dz + (size_t)row * lddz + col, pack8(oz));
+      }
     }
   }
-}
-
-constexpr int kDwRows = 64;  // rows per strip: 8 atomics per strip-thread
-__global__ void __launch_bounds__(128)
-gated_rmsnorm_bwd_dw_kernel(const bf16* __restrict__ x, int ldx, const bf16* __restrict__ z, int ldz,
-                            const float* __restrict__ rstd_in, const bf16* __restrict__ dout, int ldo,
-                            float* __restrict__ dw, int M, int D) {
-  const int vec = blockIdx.x * 128 + threadIdx.x;
-  if (vec * 8 >= D) return;
-  const int col = vec * 8;
-  const int r0 = blockIdx.y * kDwRows, r1 = min(r0 + kDwRows, M);
-  float acc[8];
+  float* my_partial = dw_partial + (size_t)blockIdx.x * D;
 #pragma unroll
-  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
-  constexpr int U = 4;
-  for (int rb = r0; rb < r1; rb += U) {
-    bf16x8 px[U], pz[U], pg[U];
-    float rs[U];
+  for (int i = 0; i < NV; ++i) {
 #pragma unroll
-    for (int u = 0; u < U; ++u) {  // clamped, unconditional loads (issued back to back); tail rows get weight 0
-      const int rr = min(rb + u, r1 - 1);
-      px[u] = ld8(x + (size_t)rr * ldx + col);
-      pz[u] = ld8(z + (size_t)rr * ldz + col);
-      pg[u] = ld8(dout + (size_t)rr * ldo + col);
-      rs[u] = rb + u < r1 ? rstd_in[rr] : 0.f;
+    for (int j = 0; j < 8; ++j) red[warp][lane * 8 + j] = dw[i][j];
+    __syncthreads();
+    for (int k = threadIdx.x; k < 256; k += blockDim.x) {
+      const int col = i * 256 + k;
+      if (col < D) {
+        float sum = 0.f;
+#pragma unroll
+        for (int ww = 0; ww < kWarpsPerBlock; ++ww) sum += red[ww][k];
+        my_partial[col] = sum;
+      }
     }
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      float xv[8], zz[8], go[8];
-      unpack8(px[u], xv); unpack8(pz[u], zz); unpack8(pg[u], go);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) acc[j] += go[j] * xv[j] * silu_f(zz[j]) * rs[u];
-    }
+    __syncthreads();
   }
-#pragma unroll
-  for (int j = 0; j < 8; ++j) atomicAdd(dw + col + j, acc[j]);
 }
 
 static int bwd_grid(int rows) {
@@ -484,17 +472,20 @@ extern "C" int mb_gated_rmsnorm_bwd(const void* x, int ldx, const void* z, int l
   if (M == 0) return 0;
   const int G = D / group_size, nv = cdiv(group_size, 256);
   if (G == 1) {
-    if (!dw_accumulate) MB_CUDA(cudaMemsetAsync(dw, 0, (size_t)D * sizeof(float), stream));
+    int grid1 = bwd_grid(M);
     DISPATCH_NV(nv, {
-      gated_rmsnorm_bwd_rows_kernel<NV><<<cdiv(M, kWarpsPerBlock), kWarpsPerBlock * 32, 0, stream>>>(
+      // persistent: exactly one wave of resident blocks (never more than the scratch rows bwd_grid allows)
+      static int per_sm = 0;
+      if (per_sm == 0)
+        MB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gated_rmsnorm_bwd_rows_kernel<NV>, kWarpsPerBlock * 32, 0));
+      if (per_sm > 0 && grid1 > num_sms() * per_sm) grid1 = num_sms() * per_sm;
+      gated_rmsnorm_bwd_rows_kernel<NV><<<grid1, kWarpsPerBlock * 32, 0, stream>>>(
           (const bf16*)x, ldx, (const bf16*)z, ldz, weight, rstd, (const bf16*)dout, ldo, (bf16*)dx, lddx, (bf16*)dz, lddz,
-          M, D);
+          scratch, M, D);
     });
     if (check_launch("gated_rmsnorm_bwd/rows")) return 1;
-    dim3 g2(cdiv(D / 8, 128), cdiv(M, kDwRows));
-    gated_rmsnorm_bwd_dw_kernel<<<g2, 128, 0, stream>>>((const bf16*)x, ldx, (const bf16*)z, ldz, rstd, (const bf16*)dout,
-                                                        ldo, dw, M, D);
-    return check_launch("gated_rmsnorm_bwd/dw");
+    colsum_partials_kernel<<<cdiv(D, 32), 1024, 0, stream>>>(scratch, dw, grid1, D, dw_accumulate);
+    return check_launch("gated_rmsnorm_bwd/colsum");
   }
   const int grid = bwd_grid(M * G);
   if (G > 1) MB_CUDA(cudaMemsetAsync(scratch, 0, (size_t)grid * D * sizeof(float), stream));
