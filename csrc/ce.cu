@@ -14,7 +14,7 @@ namespace mb {
 constexpr int kCeThreads = 512;
 
 // exp(m - nm) with the empty-partial case (m = -inf, possibly nm = -inf too) mapped to 0, not NaN
-__device__ __forceinline__ float scale_to(float m, float nm) { return m == -INFINITY ? 0.f : __expf(m - nm); }
+__device__ __forceinline__ float scale_to(float m, float nm) { return m == -INFINITY ? 0.f : fast_exp(m - nm); }
 
 __global__ void __launch_bounds__(kCeThreads)
 ce_slab_kernel(const float* __restrict__ logits, long long ld, const long long* __restrict__ targets,
@@ -29,13 +29,13 @@ ce_slab_kernel(const float* __restrict__ logits, long long ld, const long long* 
   for (int i = tid; i < nvec; i += kCeThreads) {
     const float4 v = *reinterpret_cast<const float4*>(lr + 4 * i);
     const float vm = fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w));
-    if (vm > m) { s *= __expf(m - vm); m = vm; }
-    s += __expf(v.x - m) + __expf(v.y - m) + __expf(v.z - m) + __expf(v.w - m);
+    if (vm > m) { s *= fast_exp(m - vm); m = vm; }
+    s += fast_exp(v.x - m) + fast_exp(v.y - m) + fast_exp(v.z - m) + fast_exp(v.w - m);
   }
   for (int i = (nvec << 2) + tid; i < V; i += kCeThreads) {
     const float v = lr[i];
-    if (v > m) { s *= __expf(m - v); m = v; }
-    s += __expf(v - m);
+    if (v > m) { s *= fast_exp(m - v); m = v; }
+    s += fast_exp(v - m);
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
@@ -71,14 +71,14 @@ ce_slab_kernel(const float* __restrict__ logits, long long ld, const long long* 
     ld8f(lr + 8 * i, f);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      float p = __expf(f[j] - lse);
+      float p = fast_exp(f[j] - lse);
       if (8 * i + j == t) p -= 1.f;
       f[j] = p * scale;
     }
     st8(dr + 8 * i, pack8(f));
   }
   for (int i = (nv8 << 3) + tid; i < V; i += kCeThreads) {
-    float p = __expf(lr[i] - lse);
+    float p = fast_exp(lr[i] - lse);
     if (i == t) p -= 1.f;
     dr[i] = __float2bfloat16(p * scale);
   }

@@ -37,7 +37,15 @@ __device__ __forceinline__ float rcp_approx(float x) {
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
   return r;
 }
-__device__ __forceinline__ float sigmoid_f(float x) { return rcp_approx(1.f + __expf(-x)); }
+// exp through one FMUL + one MUFU.EX2.  (__expf without -use_fast_math wraps the same MUFU in a range
+// fix-up — FSETP + two extra FMULs per call — to keep denormal results; here they flush to zero, which is
+// what every caller wants: decays and sigmoids whose results are rounded to bf16 or multiplied away.)
+__device__ __forceinline__ float fast_exp(float x) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x * 1.4426950408889634f));
+  return r;
+}
+__device__ __forceinline__ float sigmoid_f(float x) { return rcp_approx(1.f + fast_exp(-x)); }
 __device__ __forceinline__ float silu_f(float x) { return x * sigmoid_f(x); }
 // d/dx silu(x) = s + x*s*(1-s), s = sigmoid(x)
 __device__ __forceinline__ float dsilu_f(float x) {

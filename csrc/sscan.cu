@@ -62,7 +62,7 @@ sscan_local_kernel(SScanArgs a, float* __restrict__ P, float* __restrict__ S) {
     const float Bn = __bfloat162float(a.Bm[row * a.ldb + n]);
     const float la = dt * An;
     lp += la;
-    h = __expf(la) * h + dt * Bn * uu;
+    h = fast_exp(la) * h + dt * Bn * uu;
   }
   const size_t o = (((size_t)b * a.ntiles + tile) * a.Dn + d) * kSN + n;
   P[o] = lp;  // log of the decay product (kept in log space: no underflow surprises)
@@ -79,7 +79,7 @@ __global__ void sscan_carry_fwd_kernel(const float* __restrict__ P, const float*
   for (int c = 0; c < ntiles; ++c) {
     const size_t o = ((size_t)b * ntiles + c) * DnN + e;
     hin[o] = h;
-    h = __expf(P[o]) * h + S[o];
+    h = fast_exp(P[o]) * h + S[o];
   }
 }
 
@@ -102,7 +102,7 @@ sscan_fwd_kernel(SScanArgs a, const float* __restrict__ hin, bf16* __restrict__ 
     const float uu = __bfloat162float(a.u[row * a.ldu + d]);
     const float Bn = __bfloat162float(a.Bm[row * a.ldb + n]);
     const float Cn = __bfloat162float(a.Cm[row * a.ldc + n]);
-    h = __expf(dt * An) * h + dt * Bn * uu;
+    h = fast_exp(dt * An) * h + dt * Bn * uu;
     float yy = half_warp_sum(Cn * h);
     if (n == 0) {
       yy += Dd * uu;
@@ -138,7 +138,7 @@ sscan_bwd_local_kernel(SScanArgs a, const bf16* __restrict__ dy, long long lddy,
       dyy *= silu_f(__bfloat162float(a.z[row * a.ldz + d]));
     }
     const float Cn = __bfloat162float(a.Cm[row * a.ldc + n]);
-    g = (g + Cn * dyy) * __expf(dt * An);  // after this line g = dL/dh_{t-1} contribution through h_t
+    g = (g + Cn * dyy) * fast_exp(dt * An);  // after this line g = dL/dh_{t-1} contribution through h_t
   }
   (void)Dd;
   Gl[(((size_t)b * a.ntiles + tile) * a.Dn + d) * kSN + n] = g;
@@ -155,7 +155,7 @@ __global__ void sscan_carry_bwd_kernel(const float* __restrict__ P, const float*
   for (int c = ntiles - 1; c >= 0; --c) {
     const size_t o = ((size_t)b * ntiles + c) * DnN + e;
     gin[o] = g;
-    g = Gl[o] + __expf(P[o]) * g;  // gradient w.r.t. the state entering tile c
+    g = Gl[o] + fast_exp(P[o]) * g;  // gradient w.r.t. the state entering tile c
   }
 }
 
@@ -187,7 +187,7 @@ sscan_bwd_kernel(SScanArgs a, const bf16* __restrict__ dy, long long lddy, const
       if (a.softplus) dt = softplus_f(dt);
       const float uu = __bfloat162float(a.u[row * a.ldu + d]);
       const float Bn = __bfloat162float(a.Bm[row * a.ldb + n]);
-      h = __expf(dt * An) * h + dt * Bn * uu;
+      h = fast_exp(dt * An) * h + dt * Bn * uu;
     }
     hist[i + 1] = h;
   }
@@ -210,7 +210,7 @@ sscan_bwd_kernel(SScanArgs a, const bf16* __restrict__ dy, long long lddy, const
       const float h_t = hist[i + 1], h_prev = hist[i];
       const float ssm = half_warp_sum(Cn * h_t);
       g += Cn * dyy;                                      // dL/dh_t (total)
-      const float dec = __expf(dt * An);
+      const float dec = fast_exp(dt * An);
       // contributions of this step
       const float ddt_n = g * (An * dec * h_prev + Bn * uu);
       const float du_n = g * dt * Bn;
@@ -252,7 +252,7 @@ __global__ void sscan_update_kernel(float* __restrict__ state, const bf16* __res
   if (softplus) dt = softplus_f(dt);
   const float uu = __bfloat162float(x[(size_t)b * ldx + d]);
   float h = state[(size_t)bd * kSN + n];
-  h = __expf(dt * A[d * kSN + n]) * h + dt * __bfloat162float(Bm[(size_t)b * ldb + n]) * uu;
+  h = fast_exp(dt * A[d * kSN + n]) * h + dt * __bfloat162float(Bm[(size_t)b * ldb + n]) * uu;
   state[(size_t)bd * kSN + n] = h;
   float yy = half_warp_sum(__bfloat162float(Cm[(size_t)b * ldc + n]) * h);
   if (n == 0) {

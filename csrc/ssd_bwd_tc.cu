@@ -129,7 +129,7 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
       const float aref = s_a[ri0 + lgq * 32];
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
-        const float cf = __expf(fminf(aref - s_a[cj0 + col + u], 0.f));
+        const float cf = fast_exp(fminf(aref - s_a[cj0 + col + u], 0.f));
         s_cf[lgq * 128 + col + u] = cf;
         s_cd[lgq * 128 + col + u] = cf * s_dt[cj0 + col + u];
       }
@@ -139,7 +139,7 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
     phase ^= 1;
     tc_fence_after();
     const float a_i = s_a[ri];
-    const float rowf = __expf(fminf(a_i - s_a[warp_row_min], 0.f));
+    const float rowf = fast_exp(fminf(a_i - s_a[warp_row_min], 0.f));
     float rsum = 0.f;  // sum_j (dM o M)[ri, j] over this thread's columns, with M rounded exactly as
                        // the dx kernel rounds it (see ssd_bwd_finalize: makes row - column sums cancel)
 #pragma unroll
@@ -174,7 +174,7 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
 #pragma unroll
           for (int t = 0; t < 4; ++t) {
             const int cj = cj0 + k0 + 4 * q + t;
-            const float e = __expf(fminf(a_i - aj[t], 0.f));
+            const float e = fast_exp(fminf(a_i - aj[t], 0.f));
             const float pd = __uint_as_float(v[4 * q + t]) * dj[t];   // P * dt_j
             const unsigned keep = (cj <= ri) ? 0xffffffffu : 0u;
             acc[ch * 16 + 4 * q + t] += __uint_as_float(__float_as_uint(pd * e) & keep);
@@ -297,7 +297,7 @@ ssd_dbdc_kernel(const bf16* __restrict__ dcb,                       // [B,nc,G,2
         const int idx = tid + k * kThreadsB;
         const int cc = idx & 7, row = idx >> 3;
         if (row < valid_m) {
-          const float f = IS_DB ? __expf(a_last - s_a[row]) * s_a[128 + row] : __expf(s_a[row]);
+          const float f = IS_DB ? fast_exp(a_last - s_a[row]) * s_a[128 + row] : fast_exp(s_a[row]);
           uint8_t* ptr = sA + row * 128 + ((cc ^ (row & 7)) << 4);
           bf16x8 t8;
           memcpy(&t8, ptr, 16);

@@ -48,7 +48,7 @@ ssd_outer_kernel(const bf16* __restrict__ arow, long long lda, const bf16* __res
     const int hh = idx / kL, t = idx % kL;
     const size_t base = ((size_t)bc * H + h0 + hh) * kL;
     const float a = av[base + t];
-    s_scale[hh * kL + t] = DSTATE ? __expf(a) : __expf(av[base + kL - 1] - a) * dtv[base + t];
+    s_scale[hh * kL + t] = DSTATE ? fast_exp(a) : fast_exp(av[base + kL - 1] - a) * dtv[base + t];
   }
   tc_fence_before();
   __syncthreads();
@@ -276,7 +276,7 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
       const float* s_dt = s_a + kL;
       const float a_i = s_a[ri];
       const float a_ref = s_a[BWD ? warp_row_max : warp_row_min];
-      const float rowf = __expf(fminf(BWD ? a_ref - a_i : a_i - a_ref, 0.f));
+      const float rowf = fast_exp(fminf(BWD ? a_ref - a_i : a_i - a_ref, 0.f));
       for (int half = 0; half < nhalves; ++half, ++unit) {
         const int slot = unit & 1, use = unit >> 1;
         if (use > 0) mbar_wait(&g_empty[slot], (use - 1) & 1);
@@ -293,18 +293,26 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
           // strictly off-diagonal chunk: every (i, j) of the 32 x 32 block is unmasked and
           // a_i <= a_ref <= a_j (fwd; mirrored in bwd), so exp(a_i - a_j) factors into a per-row and a
           // per-column term that are both <= 1 -- 2 multiplies per element instead of an exp + mask
+#ifdef MB_EXP_ALLFAST
+          const bool fast = !skip;
+#else
           const bool fast = BWD ? (cj0 > warp_row_max) : (cj0 + 31 < warp_row_min);          // warp-uniform
+#endif
           uint32_t pk[16];  // 32 bf16 results, packed as soon as they are produced
           if (fast) {
             float* scr = wscr + cq * 32;
             {
               const float aj = s_a[cj0 + lane];
-              float cf = __expf(fminf(BWD ? aj - a_ref : a_ref - aj, 0.f));
+              float cf = fast_exp(fminf(BWD ? aj - a_ref : a_ref - aj, 0.f));
               if (!BWD) cf *= s_dt[cj0 + lane];
               scr[lane] = cf;
             }
             uint32_t v[32];
+#ifdef MB_EXP_NOSCALELD
+            for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(a_i + j);
+#else
             tmem_ld32(tCB + lane_sel + kcol, v);
+#endif
             __syncwarp();
             tmem_ld_wait();
 #pragma unroll
@@ -319,7 +327,11 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
             }
           } else if (!skip) {
             uint32_t v[32];
+#ifdef MB_EXP_NOSCALELD
+            for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(a_i + j);
+#else
             tmem_ld32(tCB + lane_sel + kcol, v);
+#endif
             tmem_ld_wait();
             // branch-free (the causal mask is a bit mask) and in groups of 4 columns whose a_j / dt_j
             // come from one 128-bit broadcast load each: keeps ~16 independent exp chains in flight
@@ -334,7 +346,7 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
 #pragma unroll
               for (int t = 0; t < 4; ++t) {
                 const int cj = cj0 + 4 * q + t;
-                const float e = __expf(fminf(BWD ? aj[t] - a_i : a_i - aj[t], 0.f));
+                const float e = fast_exp(fminf(BWD ? aj[t] - a_i : a_i - aj[t], 0.f));
                 const float val = __uint_as_float(v[4 * q + t]) * e * dj[t];
                 const unsigned keep = (BWD ? (cj >= ri) : (cj <= ri)) ? 0xffffffffu : 0u;
                 o4[t] = __uint_as_float(__float_as_uint(val) & keep);
@@ -399,8 +411,8 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
       const float Dh = Dp[h];
       float s1 = 0.f, s2 = 0.f, sd = 0.f;
       const float dt_i = s_dt[ri];
-      const float el = __expf(s_a[kL - 1] - a_i);
-      const float ea = __expf(a_i);
+      const float el = fast_exp(s_a[kL - 1] - a_i);
+      const float ea = fast_exp(a_i);
       if (BWD) mbar_wait(&x_full[ew], hh & 1);
       uint4 pk_y[4], pk_off[4];  // this row's 32 output columns (and, forward, the y_off ones), packed bf16
 #pragma unroll

@@ -29,7 +29,7 @@ __global__ void ssd_prep_kernel(const bf16* __restrict__ dt_raw, long long ld_dt
     float dt = 0.f;
     if (valid) dt = softplus_f(__bfloat162float(src[h]) + dt_bias[h]);
     dt_o[(size_t)h * L + t] = dt;
-    sm[h * L + t] = dt * (-__expf(A_log[h]));
+    sm[h * L + t] = dt * (-fast_exp(A_log[h]));
   }
   __syncthreads();
   // inclusive scan over t for each h: warp w handles heads w, w+nw, ...
@@ -65,7 +65,7 @@ __global__ void ssd_state_passing_fwd_kernel(const float* __restrict__ states, c
     bf162 lo = __floats2bfloat162_rn(prev.x, prev.y), hi = __floats2bfloat162_rn(prev.z, prev.w);
     *reinterpret_cast<bf162*>(sprev_bf16 + base) = lo;
     *reinterpret_cast<bf162*>(sprev_bf16 + base + 2) = hi;
-    const float decay = __expf(a[((size_t)(b * nc + c) * H + h) * L + (L - 1)]);
+    const float decay = fast_exp(a[((size_t)(b * nc + c) * H + h) * L + (L - 1)]);
     const float4 s = *reinterpret_cast<const float4*>(states + base);
     prev.x = decay * prev.x + s.x; prev.y = decay * prev.y + s.y;
     prev.z = decay * prev.z + s.z; prev.w = decay * prev.w + s.w;
@@ -88,7 +88,7 @@ __global__ void ssd_state_passing_bwd_kernel(const float* __restrict__ dstates_d
   __shared__ float red[32];
   for (int c = nc - 1; c >= 0; --c) {
     const size_t base = ((size_t)(b * nc + c) * H + h) * PN + e;
-    const float decay = __expf(a[((size_t)(b * nc + c) * H + h) * L + (L - 1)]);
+    const float decay = fast_exp(a[((size_t)(b * nc + c) * H + h) * L + (L - 1)]);
     float part = 0.f;
     if (active) {
       *reinterpret_cast<bf162*>(ds_bf16 + base) = __floats2bfloat162_rn(g.x, g.y);
@@ -140,7 +140,7 @@ __global__ void ssd_bwd_finalize_kernel(const bf16* __restrict__ dy, long long l
   {
     const int h = blockIdx.y;
     const size_t sidx = ((size_t)(b * nc + c) * H + h) * L + t;
-    const float A = -__expf(A_log[h]);
+    const float A = -fast_exp(A_log[h]);
     const float dtv = dt[sidx];
     float rowpart = 0.f;
     if (valid) {

@@ -37,3 +37,17 @@ tot = sum(v[1] for v in rows.values())
 print(f"total kernel time {tot/1e3:.1f} ms")
 for name, (n, t) in sorted(rows.items(), key=lambda kv: -kv[1][1])[:40]:
     print(f"{t/1e3:9.2f} ms {100*t/tot:5.1f}% n={n:5d}  {name}")
+
+# idle gaps on the device timeline (launch-bound stretches show up here)
+evs = sorted(((ev.time_range.start, ev.time_range.end, ev.name) for ev in prof.events()
+              if ev.device_type == torch.autograd.DeviceType.CUDA), key=lambda e: e[0])
+span = evs[-1][1] - evs[0][0]
+busy = sum(e[1] - e[0] for e in evs)
+gaps = {}
+for (s0, e0_, n0), (s1, e1_, n1) in zip(evs, evs[1:]):
+    g = s1 - e0_
+    if g > 0:
+        r = gaps.setdefault(n1[:60], [0, 0.0]); r[0] += 1; r[1] += g
+print(f"device span {span/1e3:.1f} ms, busy {busy/1e3:.1f} ms, idle {(span-busy)/1e3:.1f} ms")
+for name, (n, t) in sorted(gaps.items(), key=lambda kv: -kv[1][1])[:12]:
+    print(f"  idle before {name:60s} n={n:4d} total {t/1e3:7.2f} ms  avg {t/n:6.1f} us")
