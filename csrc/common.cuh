@@ -58,6 +58,30 @@ __device__ __forceinline__ void silu_both(float x, float& f, float& df) {
   f = x * s;
   df = s * (1.f + x * (1.f - s));
 }
+// ---- packed fp32 (sm_100: FFMA2 / FMUL2 / FADD2 do two fp32 lanes per issued instruction) -----------
+// The fp32 pipe does the same number of flops either way; what the pairs buy is issue slots, which is
+// what the elementwise kernels (conv, norms, SSD scaling) run out of first at their occupancy.
+__device__ __forceinline__ float2 f2(float a, float b) { return make_float2(a, b); }
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ float2 add2(float2 a, float2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ float ex2_approx(float x) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ float2 sigmoid2(float2 x) {
+  const float2 t = mul2(x, f2(-1.4426950408889634f, -1.4426950408889634f));
+  const float2 d = add2(f2(ex2_approx(t.x), ex2_approx(t.y)), f2(1.f, 1.f));
+  return f2(rcp_approx(d.x), rcp_approx(d.y));
+}
+__device__ __forceinline__ float2 silu2(float2 x) { return mul2(x, sigmoid2(x)); }
+// silu and its derivative s + x*s*(1-s) = s * (1 + x - x*s) from one sigmoid
+__device__ __forceinline__ void silu_both2(float2 x, float2& f, float2& df) {
+  const float2 s = sigmoid2(x);
+  f = mul2(x, s);
+  df = mul2(s, add2(f2(1.f, 1.f), fma2(f2(-1.f, -1.f), f, x)));  // 1 + (x - x*s)
+}
 __device__ __forceinline__ float softplus_f(float x) { return x > 20.f ? x : log1pf(__expf(x)); }
 
 __device__ __forceinline__ float warp_sum(float v) {

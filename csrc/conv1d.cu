@@ -12,27 +12,55 @@
 namespace mb {
 
 constexpr int kConvThreads = 128;
-constexpr int kConvTile = 64;  // tokens per block
+constexpr int kConvTile = 64;  // smallest token tile per block (the launcher picks the actual one, see conv_tile)
+
+// Forward.  The kernel is a pure stream (read x once, write y once), so what matters is bytes in flight:
+// a thread prefetches its own 16-byte column of the next kFwdDepth batches of U tokens with cp.async into a
+// private slice of shared memory (ring of kFwdRing rows).  Nobody else touches that slice, so the only
+// synchronisation is the thread's own cp.async.wait_group -- no barriers, no registers parked on loads.
+constexpr int kFwdU = 4;                          // tokens per batch (one cp.async group)
+constexpr int kFwdDepth = 6;                      // batches in flight
+constexpr int kFwdRing = (kFwdDepth + 1) * kFwdU; // rows in the ring (the batch being read + those in flight)
+constexpr int kFwdSmem = kFwdRing * kConvThreads * 16;
+
+__device__ __forceinline__ void cp_async16_zfill(uint32_t saddr, const void* g, bool pred) {
+  const int n = pred ? 16 : 0;
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(saddr), "l"(g), "r"(n) : "memory");
+}
 
 template <int W, bool SILU>
-__global__ void __launch_bounds__(kConvThreads, 4)
+__global__ void __launch_bounds__(kConvThreads, 3)
 conv1d_fwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __restrict__ w,
-                  const float* __restrict__ bias, bf16* __restrict__ y, long long ldy, int T, int C) {
+                  const float* __restrict__ bias, bf16* __restrict__ y, long long ldy, int T, int C, int tile) {
+  extern __shared__ __align__(16) uint8_t conv_smem[];
   const int c0 = (blockIdx.x * kConvThreads + threadIdx.x) * 8;
   if (c0 >= C) return;
+  constexpr int U = kFwdU;
   const int b = blockIdx.z;
-  const int t0 = blockIdx.y * kConvTile;
-  const int t1 = min(t0 + kConvTile, T);
-  float wt[8][W], bs[8];
+  const int t0 = blockIdx.y * tile;
+  const int t1 = min(t0 + tile, T);
+  float2 wt[4][W], bs[4];  // channel pairs: the taps run as FFMA2 (two fp32 lanes per issued instruction)
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
+  for (int j = 0; j < 4; ++j) {
 #pragma unroll
-    for (int k = 0; k < W; ++k) wt[j][k] = w[(c0 + j) * W + k];
-    bs[j] = bias != nullptr ? bias[c0 + j] : 0.f;
+    for (int k = 0; k < W; ++k) wt[j][k] = f2(w[(c0 + 2 * j) * W + k], w[(c0 + 2 * j + 1) * W + k]);
+    bs[j] = bias != nullptr ? f2(bias[c0 + 2 * j], bias[c0 + 2 * j + 1]) : f2(0.f, 0.f);
   }
   const bf16* xb = x + ((size_t)b * T) * ldx + c0;
   bf16* yb = y + ((size_t)b * T) * ldy + c0;
-  constexpr int U = 8;  // tokens per register batch: U loads in flight, static indexing, no window shifts
+  uint8_t* my = conv_smem + threadIdx.x * 16;                 // row r of the ring lives at my + r * (threads * 16)
+  const uint32_t my_s = (uint32_t)__cvta_generic_to_shared(my);
+  constexpr int kRowBytes = kConvThreads * 16;
+  // batch i covers tokens t0 + i*U .. +U-1 and ring rows (i % (kFwdDepth+1)) * U ..; rows outside [0, T) are zero-filled
+  auto issue = [&](int i) {
+    const int tb = t0 + i * U, slot = (i % (kFwdDepth + 1)) * U;
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int t = tb + u;
+      cp_async16_zfill(my_s + (slot + u) * kRowBytes, xb + (size_t)min(t, T - 1) * ldx, t < T);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
   bf16x8 halo[W - 1];   // x[tb - (W-1) + k], packed
 #pragma unroll
   for (int k = 0; k < W - 1; ++k) {
@@ -40,41 +68,57 @@ conv1d_fwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __rest
     halo[k] = ld8(xb + (size_t)max(t, 0) * ldx);
     if (t < 0) halo[k].v[0] = halo[k].v[1] = halo[k].v[2] = halo[k].v[3] = __floats2bfloat162_rn(0.f, 0.f);
   }
-  for (int tb = t0; tb < t1; tb += U) {
+  const int nb = (t1 - t0 + U - 1) / U;
+#pragma unroll
+  for (int i = 0; i < kFwdDepth; ++i) {
+    if (i < nb) issue(i);
+    else asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+  for (int i = 0; i < nb; ++i) {
+    asm volatile("cp.async.wait_group %0;" ::"n"(kFwdDepth - 1) : "memory");  // batch i has landed
+    const int tb = t0 + i * U, slot = (i % (kFwdDepth + 1)) * U;
     bf16x8 raw[U + W - 1];
 #pragma unroll
     for (int k = 0; k < W - 1; ++k) raw[k] = halo[k];
 #pragma unroll
-    for (int u = 0; u < U; ++u)  // unconditional (clamped) loads: all U issue back to back
-      raw[W - 1 + u] = ld8(xb + (size_t)min(tb + u, T - 1) * ldx);
+    for (int u = 0; u < U; ++u) {
+      uint4 t4 = *reinterpret_cast<const uint4*>(my + (slot + u) * kRowBytes);
+      memcpy(&raw[W - 1 + u], &t4, 16);
+    }
+    // refill: batch i + depth goes into the slot freed by batch i - 1 (its rows are already in registers / halo)
+    if (i + kFwdDepth < nb) issue(i + kFwdDepth);
+    else asm volatile("cp.async.commit_group;" ::: "memory");
 #pragma unroll
     for (int k = 0; k < W - 1; ++k) halo[k] = raw[U + k];
-    float acc[U][8];
+    float2 acc[U][4];
 #pragma unroll
     for (int u = 0; u < U; ++u)
 #pragma unroll
-      for (int j = 0; j < 8; ++j) acc[u][j] = bs[j];
+      for (int j = 0; j < 4; ++j) acc[u][j] = bs[j];
 #pragma unroll
     for (int r = 0; r < U + W - 1; ++r) {  // each input row feeds up to W outputs
-      float xr[8];
-      unpack8(raw[r], xr);
+      float2 xr[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) xr[j] = __bfloat1622float2(raw[r].v[j]);
 #pragma unroll
       for (int k = 0; k < W; ++k) {
         const int u = r - k;  // out[u] += w[k] * x[u + k]
         if (u >= 0 && u < U) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) acc[u][j] += wt[j][k] * xr[j];
+          for (int j = 0; j < 4; ++j) acc[u][j] = fma2(wt[j][k], xr[j], acc[u][j]);
         }
       }
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       if (tb + u < t1) {
-        if (SILU) {
+        bf16x8 o;
 #pragma unroll
-          for (int j = 0; j < 8; ++j) acc[u][j] = silu_f(acc[u][j]);
+        for (int j = 0; j < 4; ++j) {
+          const float2 v = SILU ? silu2(acc[u][j]) : acc[u][j];
+          o.v[j] = __floats2bfloat162_rn(v.x, v.y);
         }
-        st8(yb + (size_t)(tb + u) * ldy, pack8(acc[u]));
+        st8(yb + (size_t)(tb + u) * ldy, o);
       }
     }
   }
@@ -109,14 +153,14 @@ __global__ void __launch_bounds__(kConvThreads)
 conv1d_bwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __restrict__ w,
                   const float* __restrict__ bias, const bf16* __restrict__ dy, long long lddy,
                   bf16* __restrict__ dx, long long lddx, float* __restrict__ dw,
-                  float* __restrict__ dbias, int T, int C) {
+                  float* __restrict__ dbias, int T, int C, int tile) {
   constexpr int H = W - 1;  // halo
   constexpr int U = 4;      // tokens per register batch
   const int c0 = (blockIdx.x * kConvThreads + threadIdx.x) * 4;
   if (c0 >= C) return;
   const int b = blockIdx.z;
-  const int t0 = blockIdx.y * kConvTile;
-  const int t1 = min(t0 + kConvTile, T);
+  const int t0 = blockIdx.y * tile;
+  const int t1 = min(t0 + tile, T);
   float wt[4][W], bs[4], dwa[4][W], dba[4];
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
@@ -241,6 +285,22 @@ __global__ void conv1d_update_kernel(const bf16* __restrict__ x, long long ldx, 
 
 using namespace mb;
 
+// Token-tile length: the largest number of tiles per sequence (>= 64 tokens each) whose block count still
+// fills whole waves of resident blocks -- a grid of 1.7 waves runs as long as one of 2.
+static int conv_tile(int blocks_x, int B, int T, int blocks_per_sm) {
+  const long long slots = (long long)num_sms() * blocks_per_sm;
+  const int nt_max = cdiv(T, kConvTile);
+  int best_nt = nt_max;
+  double best = 1e30;
+  for (int nt = 1; nt <= nt_max; ++nt) {
+    const int tile = cdiv(T, nt);
+    const long long ctas = (long long)blocks_x * cdiv(T, tile) * B;
+    const double cost = (double)cdiv(ctas, slots) * (tile + 8);  // waves x (tokens + per-block overhead)
+    if (cost < best) { best = cost; best_nt = nt; }
+  }
+  return cdiv(T, best_nt);
+}
+
 #define DISPATCH_W(W_, SILU_, ...)                                                     \
   if (W_ == 4 && SILU_) { constexpr int W = 4; constexpr bool S = true; __VA_ARGS__; }  \
   else if (W_ == 4) { constexpr int W = 4; constexpr bool S = false; __VA_ARGS__; }    \
@@ -255,9 +315,16 @@ extern "C" int mb_conv1d_fwd(const void* x, long long ldx, const float* w, const
   MB_REQUIRE(width >= 2 && width <= 4, "conv1d_fwd: width %d not in [2,4]", width);
   MB_REQUIRE(C % 8 == 0 && ldx % 8 == 0 && ldy % 8 == 0, "conv1d_fwd: C and row strides must be multiples of 8");
   if (B * T == 0) return 0;
-  dim3 grid(cdiv(C / 8, kConvThreads), cdiv(T, kConvTile), B);
   DISPATCH_W(width, silu, {
-    conv1d_fwd_kernel<W, S><<<grid, kConvThreads, 0, stream>>>((const bf16*)x, ldx, w, bias, (bf16*)y, ldy, T, C);
+    static int per_sm = 0;
+    if (per_sm == 0) {
+      MB_CUDA(cudaFuncSetAttribute(conv1d_fwd_kernel<W, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));
+      MB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, conv1d_fwd_kernel<W, S>, kConvThreads, kFwdSmem));
+      if (per_sm < 1) per_sm = 1;
+    }
+    const int tile = conv_tile(cdiv(C / 8, kConvThreads), B, T, per_sm);
+    dim3 grid(cdiv(C / 8, kConvThreads), cdiv(T, tile), B);
+    conv1d_fwd_kernel<W, S><<<grid, kConvThreads, kFwdSmem, stream>>>((const bf16*)x, ldx, w, bias, (bf16*)y, ldy, T, C, tile);
   });
   return check_launch("conv1d_fwd");
 }
@@ -270,10 +337,16 @@ extern "C" int mb_conv1d_bwd(const void* x, long long ldx, const float* w, const
   MB_REQUIRE(C % 8 == 0 && ldx % 8 == 0 && lddy % 8 == 0 && lddx % 8 == 0,
              "conv1d_bwd: C and row strides must be multiples of 8");
   if (B * T == 0) return 0;
-  dim3 grid(cdiv(C / 4, kConvThreads), cdiv(T, kConvTile), B);
   DISPATCH_W(width, silu, {
+    static int per_sm = 0;
+    if (per_sm == 0) {
+      MB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, conv1d_bwd_kernel<W, S>, kConvThreads, 0));
+      if (per_sm < 1) per_sm = 1;
+    }
+    const int tile = conv_tile(cdiv(C / 4, kConvThreads), B, T, per_sm);
+    dim3 grid(cdiv(C / 4, kConvThreads), cdiv(T, tile), B);
     conv1d_bwd_kernel<W, S><<<grid, kConvThreads, 0, stream>>>((const bf16*)x, ldx, w, bias, (const bf16*)dy, lddy,
-                                                               (bf16*)dx, lddx, dw, dbias, T, C);
+                                                               (bf16*)dx, lddx, dw, dbias, T, C, tile);
   });
   return check_launch("conv1d_bwd");
 }
