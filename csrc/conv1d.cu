@@ -161,106 +161,122 @@ conv1d_bwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __rest
   const int b = blockIdx.z;
   const int t0 = blockIdx.y * tile;
   const int t1 = min(t0 + tile, T);
-  float wt[4][W], bs[4], dwa[4][W], dba[4];
+  // all arithmetic on channel PAIRS (float2): FFMA2 / FMUL2 / FADD2 halve the issue slots of this
+  // instruction-bound kernel (~40 instructions per element before)
+  float2 wt[2][W], bs[2], dwa[2][W], dba[2];
 #pragma unroll
-  for (int j = 0; j < 4; ++j) {
+  for (int j = 0; j < 2; ++j) {
 #pragma unroll
-    for (int k = 0; k < W; ++k) { wt[j][k] = w[(c0 + j) * W + k]; dwa[j][k] = 0.f; }
-    bs[j] = bias != nullptr ? bias[c0 + j] : 0.f;
-    dba[j] = 0.f;
+    for (int k = 0; k < W; ++k) {
+      wt[j][k] = f2(w[(c0 + 2 * j) * W + k], w[(c0 + 2 * j + 1) * W + k]);
+      dwa[j][k] = f2(0.f, 0.f);
+    }
+    bs[j] = bias != nullptr ? f2(bias[c0 + 2 * j], bias[c0 + 2 * j + 1]) : f2(0.f, 0.f);
+    dba[j] = f2(0.f, 0.f);
   }
   const bf16* xb = x + ((size_t)b * T) * ldx + c0;
   const bf16* gb = dy + ((size_t)b * T) * lddy + c0;
   bf16* dxb = dx + ((size_t)b * T) * lddx + c0;
-  // Branch-free: out-of-range rows read a clamped (valid) row and are zeroed by a select, so the
+  // Branch-free: out-of-range rows read a clamped (valid) row and are zeroed by a multiply, so the
   // compiler can issue a batch's loads back to back (a conditional load ends the basic block and
   // each load would then pay its full latency in turn — ncu: 67 % long-scoreboard stalls).
-  auto load_x = [&](int t, float* f) {
+  auto load_x = [&](int t, float2* f) {
     const int tc = min(max(t, 0), T - 1);
-    unpack4(ld4(xb + (size_t)tc * ldx), f);
+    const bf16x4 p = ld4(xb + (size_t)tc * ldx);
     const float m = (t >= 0 && t < T) ? 1.f : 0.f;
-    f[0] *= m; f[1] *= m; f[2] *= m; f[3] *= m;
+    f[0] = mul2(__bfloat1622float2(p.v[0]), f2(m, m));
+    f[1] = mul2(__bfloat1622float2(p.v[1]), f2(m, m));
   };
   // g[t] = dy[t] * silu'(pre[t]) from the W x-rows ending at t; also this token's dw / db terms
-  auto make_g = [&](int t, const float (*xw)[4], const float* d4, float* g) {  // xw[k] = x[t - H + k]
+  auto make_g = [&](int t, const float2 (*xw)[2], const float2* d2, float2* g) {  // xw[k] = x[t - H + k]
     const float live = t < T ? 1.f : 0.f, own = t < t1 ? 1.f : 0.f;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      float gg = d4[j] * live;
+    for (int j = 0; j < 2; ++j) {
+      float2 gg = mul2(d2[j], f2(live, live));
       if (SILU) {
-        float a = bs[j];
+        float2 a = bs[j];
 #pragma unroll
-        for (int k = 0; k < W; ++k) a += wt[j][k] * xw[k][j];
-        gg *= dsilu_f(a);
+        for (int k = 0; k < W; ++k) a = fma2(wt[j][k], xw[k][j], a);
+        float2 sv, dsv;
+        silu_both2(a, sv, dsv);
+        gg = mul2(gg, dsv);
       }
       g[j] = gg;
-      const float go = gg * own;  // only the tile that owns token t accumulates its dw / db terms
-      dba[j] += go;
+      const float2 go = mul2(gg, f2(own, own));  // only the tile that owns token t accumulates its dw / db terms
+      dba[j] = add2(dba[j], go);
 #pragma unroll
-      for (int k = 0; k < W; ++k) dwa[j][k] += go * xw[k][j];
+      for (int k = 0; k < W; ++k) dwa[j][k] = fma2(go, xw[k][j], dwa[j][k]);
     }
   };
-  auto load_dy = [&](int t, float* f) { unpack4(ld4(gb + (size_t)min(t, T - 1) * lddy), f); };
+  auto load_dy = [&](int t, float2* f) {
+    const bf16x4 p = ld4(gb + (size_t)min(t, T - 1) * lddy);
+    f[0] = __bfloat1622float2(p.v[0]);
+    f[1] = __bfloat1622float2(p.v[1]);
+  };
 
   // rows carried between batches: xr[0..H) = x[tb .. tb+H), gr[0..H) = g[tb .. tb+H)
-  float xr[H + U][4], gr[H + U][4];
+  float2 xr[H + U][2], gr[H + U][2];
   {
-    float xp[2 * H][4];  // x[t0-H .. t0+H)
+    float2 xp[2 * H][2];  // x[t0-H .. t0+H)
 #pragma unroll
     for (int i = 0; i < 2 * H; ++i) load_x(t0 - H + i, xp[i]);
 #pragma unroll
     for (int i = 0; i < H; ++i) {
-      float xw[W][4];
+      float2 xw[W][2];
 #pragma unroll
       for (int k = 0; k < W; ++k)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) xw[k][j] = xp[i + k][j];
-      float d4[4];
-      load_dy(t0 + i, d4);
-      make_g(t0 + i, xw, d4, gr[i]);
+        for (int jj = 0; jj < 2; ++jj) xw[k][jj] = xp[i + k][jj];
+      float2 d2[2];
+      load_dy(t0 + i, d2);
+      make_g(t0 + i, xw, d2, gr[i]);
 #pragma unroll
-      for (int j = 0; j < 4; ++j) xr[i][j] = xp[H + i][j];
+      for (int jj = 0; jj < 2; ++jj) xr[i][jj] = xp[H + i][jj];
     }
   }
   for (int tb = t0; tb < t1; tb += U) {
     // new rows: tokens tb+H .. tb+H+U-1
-    float dyb[U][4];
+    float2 dyb[U][2];
 #pragma unroll
     for (int u = 0; u < U; ++u) { load_x(tb + H + u, xr[H + u]); load_dy(tb + H + u, dyb[u]); }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      float xw[W][4];
+      float2 xw[W][2];
 #pragma unroll
       for (int k = 0; k < W; ++k)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) xw[k][j] = xr[u + k][j];  // x[(tb+H+u) - H + k] = x[tb + u + k]
+        for (int jj = 0; jj < 2; ++jj) xw[k][jj] = xr[u + k][jj];  // x[(tb+H+u) - H + k] = x[tb + u + k]
       make_g(tb + H + u, xw, dyb[u], gr[H + u]);
     }
     // dx[tb+u] = sum_k w[k] * g[tb+u + H - k]
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       if (tb + u < t1) {
-        float o[4];
+        float2 o[2];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          float a = 0.f;
+        for (int jj = 0; jj < 2; ++jj) {
+          float2 a = mul2(wt[jj][0], gr[u + H][jj]);
 #pragma unroll
-          for (int k = 0; k < W; ++k) a += wt[j][k] * gr[u + H - k][j];
-          o[j] = a;
+          for (int k = 1; k < W; ++k) a = fma2(wt[jj][k], gr[u + H - k][jj], a);
+          o[jj] = a;
         }
-        st4(dxb + (size_t)(tb + u) * lddx, o);
+        const float of[4] = {o[0].x, o[0].y, o[1].x, o[1].y};
+        st4(dxb + (size_t)(tb + u) * lddx, of);
       }
     }
 #pragma unroll
     for (int i = 0; i < H; ++i)
 #pragma unroll
-      for (int j = 0; j < 4; ++j) { xr[i][j] = xr[U + i][j]; gr[i][j] = gr[U + i][j]; }
+      for (int jj = 0; jj < 2; ++jj) { xr[i][jj] = xr[U + i][jj]; gr[i][jj] = gr[U + i][jj]; }
   }
 #pragma unroll
-  for (int j = 0; j < 4; ++j) {
+  for (int jj = 0; jj < 2; ++jj) {
 #pragma unroll
-    for (int k = 0; k < W; ++k) atomicAdd(dw + (c0 + j) * W + k, dwa[j][k]);
-    if (dbias != nullptr) atomicAdd(dbias + c0 + j, dba[j]);
+    for (int k = 0; k < W; ++k) {
+      atomicAdd(dw + (c0 + 2 * jj) * W + k, dwa[jj][k].x);
+      atomicAdd(dw + (c0 + 2 * jj + 1) * W + k, dwa[jj][k].y);
+    }
+    if (dbias != nullptr) { atomicAdd(dbias + c0 + 2 * jj, dba[jj].x); atomicAdd(dbias + c0 + 2 * jj + 1, dba[jj].y); }
   }
 }
 
