@@ -85,9 +85,9 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
   const int ri = ri0 + r;
   const uint32_t lane_sel = (uint32_t)(lg * 32) << 16;
   const int warp_row_min = ri0 + lg * 32, warp_row_max = warp_row_min + 31;
-  float acc[64];
+  float2 acc2[32];  // dCB accumulators, column pairs (FFMA2 operands need aligned register pairs)
 #pragma unroll
-  for (int j = 0; j < 64; ++j) acc[j] = 0.f;
+  for (int j = 0; j < 32; ++j) acc2[j] = f2(0.f, 0.f);
 
   auto prefetch_head = [&](int hh) {
     const int h = g * hpg + hh;
@@ -140,6 +140,7 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
     tc_fence_after();
     const float a_i = s_a[ri];
     const float rowf = fast_exp(fminf(a_i - s_a[warp_row_min], 0.f));
+    float2 rs2 = f2(0.f, 0.f);  // the same sum, even / odd columns of the blocks below the diagonal
     float rsum = 0.f;  // sum_j (dM o M)[ri, j] over this thread's columns, with M rounded exactly as
                        // the dx kernel rounds it (see ssd_bwd_finalize: makes row - column sums cancel)
 #pragma unroll
@@ -151,18 +152,24 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
       tmem_ld16(tCB + lane_sel + k0, cbv);
       tmem_ld_wait();
       if (cj0 + k0 + 15 < warp_row_min) {  // warp-uniform: strictly below the diagonal, no mask, no exp
+        // column pairs through the packed fp32 pipe (FMUL2 / FFMA2): ~4 issued instructions per element
+        const float2 rf2 = f2(rowf, rowf);
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const float4 f4 = *reinterpret_cast<const float4*>(s_cf + lg * 128 + k0 + 4 * q);
           const float4 d4 = *reinterpret_cast<const float4*>(s_cd + lg * 128 + k0 + 4 * q);
           const float4 t4 = *reinterpret_cast<const float4*>(s_dt + cj0 + k0 + 4 * q);
-          const float cf[4] = {f4.x, f4.y, f4.z, f4.w}, cd[4] = {d4.x, d4.y, d4.z, d4.w}, dj[4] = {t4.x, t4.y, t4.z, t4.w};
+          const float2 cf[2] = {f2(f4.x, f4.y), f2(f4.z, f4.w)}, cd[2] = {f2(d4.x, d4.y), f2(d4.z, d4.w)},
+                       dj[2] = {f2(t4.x, t4.y), f2(t4.z, t4.w)};
 #pragma unroll
-          for (int t = 0; t < 4; ++t) {
-            const float p = __uint_as_float(v[4 * q + t]);
-            acc[ch * 16 + 4 * q + t] += p * (rowf * cd[t]);
-            const float mr = __bfloat162float(__float2bfloat16(__uint_as_float(cbv[4 * q + t]) * (rowf * cf[t])));
-            rsum += (p * dj[t]) * mr;
+          for (int t = 0; t < 2; ++t) {
+            const int e0 = 4 * q + 2 * t;
+            const float2 p = f2(__uint_as_float(v[e0]), __uint_as_float(v[e0 + 1]));
+            const float2 cb = f2(__uint_as_float(cbv[e0]), __uint_as_float(cbv[e0 + 1]));
+            acc2[(ch * 16 + e0) >> 1] = fma2(p, mul2(rf2, cd[t]), acc2[(ch * 16 + e0) >> 1]);
+            const float2 m = mul2(cb, mul2(rf2, cf[t]));
+            const float2 mr = __bfloat1622float2(__floats2bfloat162_rn(m.x, m.y));
+            rs2 = fma2(mul2(p, dj[t]), mr, rs2);
           }
         }
       } else {
@@ -177,7 +184,11 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
             const float e = fast_exp(fminf(a_i - aj[t], 0.f));
             const float pd = __uint_as_float(v[4 * q + t]) * dj[t];   // P * dt_j
             const unsigned keep = (cj <= ri) ? 0xffffffffu : 0u;
-            acc[ch * 16 + 4 * q + t] += __uint_as_float(__float_as_uint(pd * e) & keep);
+            {
+              float2& a2 = acc2[(ch * 16 + 4 * q + t) >> 1];
+              const float add = __uint_as_float(__float_as_uint(pd * e) & keep);
+              if (t & 1) a2.y += add; else a2.x += add;
+            }
             // M'[ri,cj] = bf16(CB * e), the operand value the dx kernel multiplies with
             const float mr = __bfloat162float(__float2bfloat16(__uint_as_float(cbv[4 * q + t]) * e));
             rsum += __uint_as_float(__float_as_uint(pd * mr) & keep);
@@ -185,13 +196,19 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
         }
       }
     }
+    rsum += rs2.x + rs2.y;
     if (ri < valid) atomicAdd(rowsum_m + ((size_t)bc * H + h) * kL + ri, rsum);
     tc_fence_before();
     __syncthreads();
   }
   bf16* dst = dcb + (((size_t)bc * G + g) * kL + ri) * kL + cj0 + half * 64;
 #pragma unroll
-  for (int q = 0; q < 8; ++q) st8(dst + 8 * q, pack8(acc + 8 * q));
+  for (int q = 0; q < 8; ++q) {
+    bf16x8 o;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) o.v[e] = __floats2bfloat162_rn(acc2[4 * q + e].x, acc2[4 * q + e].y);
+    st8(dst + 8 * q, o);
+  }
   if (warp == 0) tmem_dealloc(tmem, 256);
 }
 
