@@ -316,51 +316,58 @@ gated_rmsnorm_bwd_rows_kernel(const bf16* __restrict__ x, int ldx, const bf16* _
   __shared__ float red[kWarpsPerBlock][32 * 8 + 8];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nvec = D >> 3;
-  float dw[NV][8];
+  // column pairs in float2 throughout: FMUL2 / FFMA2 halve the issue slots of the arithmetic
+  float2 dw[NV][4];
 #pragma unroll
   for (int i = 0; i < NV; ++i)
 #pragma unroll
-    for (int j = 0; j < 8; ++j) dw[i][j] = 0.f;
+    for (int j = 0; j < 4; ++j) dw[i][j] = f2(0.f, 0.f);
   for (int row = blockIdx.x * kWarpsPerBlock + warp; row < M; row += gridDim.x * kWarpsPerBlock) {
     const float rstd = rstd_in[row];
-    float c = 0.f;
+    float2 c2 = f2(0.f, 0.f);
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int vec = lane + 32 * i;
       if (vec < nvec) {
         const int col = vec * 8;
-        float xv[8], zz[8], go[8], w[8];
-        unpack8(ld8(x + (size_t)row * ldx + col), xv);
-        unpack8(ld8(z + (size_t)row * ldz + col), zz);
-        unpack8(ld8(dout + (size_t)row * ldo + col), go);
-        ld8f(weight + col, w);
+        const bf16x8 px = ld8(x + (size_t)row * ldx + col), pz = ld8(z + (size_t)row * ldz + col),
+                     pg = ld8(dout + (size_t)row * ldo + col);
+        const float4 w0 = *reinterpret_cast<const float4*>(weight + col), w1 = *reinterpret_cast<const float4*>(weight + col + 4);
+        const float2 w[4] = {f2(w0.x, w0.y), f2(w0.z, w0.w), f2(w1.x, w1.y), f2(w1.z, w1.w)};
 #pragma unroll
-        for (int j = 0; j < 8; ++j) c += xv[j] * silu_f(zz[j]) * go[j] * w[j];
+        for (int j = 0; j < 4; ++j) {
+          const float2 xv = __bfloat1622float2(px.v[j]), zz = __bfloat1622float2(pz.v[j]), go = __bfloat1622float2(pg.v[j]);
+          c2 = fma2(mul2(xv, silu2(zz)), mul2(go, w[j]), c2);
+        }
       }
     }
-    c = warp_sum(c) * rstd / (float)D;  // mean(xhat * w * dout)
+    const float c = warp_sum(c2.x + c2.y) * rstd / (float)D;  // mean(xhat * w * dout)
+    const float2 rs2 = f2(rstd, rstd), nc2 = f2(-c, -c);
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int vec = lane + 32 * i;
       if (vec < nvec) {
         const int col = vec * 8;
-        float xv[8], zz[8], go[8], w[8], ox[8], oz[8];
-        unpack8(ld8(x + (size_t)row * ldx + col), xv);
-        unpack8(ld8(z + (size_t)row * ldz + col), zz);
-        unpack8(ld8(dout + (size_t)row * ldo + col), go);
-        ld8f(weight + col, w);
+        const bf16x8 px = ld8(x + (size_t)row * ldx + col), pz = ld8(z + (size_t)row * ldz + col),
+                     pg = ld8(dout + (size_t)row * ldo + col);
+        const float4 w0 = *reinterpret_cast<const float4*>(weight + col), w1 = *reinterpret_cast<const float4*>(weight + col + 4);
+        const float2 w[4] = {f2(w0.x, w0.y), f2(w0.z, w0.w), f2(w1.x, w1.y), f2(w1.z, w1.w)};
+        bf16x8 ox, oz;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          float sg, dsg;
-          silu_both(zz[j], sg, dsg);
-          const float xh = xv[j] * sg * rstd;
-          const float dxs = (go[j] * w[j] - xh * c) * rstd;
-          ox[j] = dxs * sg;
-          oz[j] = dxs * xv[j] * dsg;
-          dw[i][j] += go[j] * xh;
+        for (int j = 0; j < 4; ++j) {
+          const float2 xv = __bfloat1622float2(px.v[j]), zz = __bfloat1622float2(pz.v[j]), go = __bfloat1622float2(pg.v[j]);
+          const float2 sig = sigmoid2(zz);
+          const float2 sg = mul2(zz, sig);                                                   // silu(z)
+          const float2 dsg = mul2(sig, add2(f2(1.f, 1.f), fma2(f2(-1.f, -1.f), sg, zz)));   // silu'(z)
+          const float2 xh = mul2(mul2(xv, sg), rs2);
+          const float2 dxs = mul2(fma2(xh, nc2, mul2(go, w[j])), rs2);                       // (go*w - xh*c) * rstd
+          const float2 o1 = mul2(dxs, sg), o2 = mul2(mul2(dxs, xv), dsg);
+          ox.v[j] = __floats2bfloat162_rn(o1.x, o1.y);
+          oz.v[j] = __floats2bfloat162_rn(o2.x, o2.y);
+          dw[i][j] = fma2(go, xh, dw[i][j]);
         }
-        st8(dx + (size_t)row * lddx + col, pack8(ox));
-        st8(dz + (size_t)row * lddz + col, pack8(oz));
+        st8(dx + (size_t)row * lddx + col, ox);
+        st8(dz + (size_t)row * lddz + col, oz);
       }
     }
   }
@@ -368,7 +375,7 @@ gated_rmsnorm_bwd_rows_kernel(const bf16* __restrict__ x, int ldx, const bf16* _
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) red[warp][lane * 8 + j] = dw[i][j];
+    for (int j = 0; j < 4; ++j) { red[warp][lane * 8 + 2 * j] = dw[i][j].x; red[warp][lane * 8 + 2 * j + 1] = dw[i][j].y; }
     __syncthreads();
     for (int k = threadIdx.x; k < 256; k += blockDim.x) {
       const int col = i * 256 + k;
