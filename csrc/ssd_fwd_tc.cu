@@ -277,6 +277,7 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
       const float a_i = s_a[ri];
       const float a_ref = s_a[BWD ? warp_row_max : warp_row_min];
       const float rowf = fast_exp(fminf(BWD ? a_ref - a_i : a_i - a_ref, 0.f));
+      const bool diag_ok = fabsf(s_a[warp_row_min] - s_a[warp_row_max]) < 60.f;  // warp-uniform
       for (int half = 0; half < nhalves; ++half, ++unit) {
         const int slot = unit & 1, use = unit >> 1;
         if (use > 0) mbar_wait(&g_empty[slot], (use - 1) & 1);
@@ -293,45 +294,53 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
           // strictly off-diagonal chunk: every (i, j) of the 32 x 32 block is unmasked and
           // a_i <= a_ref <= a_j (fwd; mirrored in bwd), so exp(a_i - a_j) factors into a per-row and a
           // per-column term that are both <= 1 -- 2 multiplies per element instead of an exp + mask
-#ifdef MB_EXP_ALLFAST
-          const bool fast = !skip;
-#else
-          const bool fast = BWD ? (cj0 > warp_row_max) : (cj0 + 31 < warp_row_min);          // warp-uniform
-#endif
+          const bool offdiag = BWD ? (cj0 > warp_row_max) : (cj0 + 31 < warp_row_min);  // warp-uniform
+          // The chunk ON the diagonal factors the same way around the same a_ref (the column factor is then
+          // >= 1 instead of <= 1) as long as the decay across its 32 rows stays far from the fp32 range
+          // (diag_ok, checked per head); only the causal mask is added.  Otherwise: the exact path below.
+          const bool fast = offdiag || (!skip && diag_ok);
           uint32_t pk[16];  // 32 bf16 results, packed as soon as they are produced
           if (fast) {
             float* scr = wscr + cq * 32;
             {
               const float aj = s_a[cj0 + lane];
-              float cf = fast_exp(fminf(BWD ? aj - a_ref : a_ref - aj, 0.f));
+              float cf = fast_exp(fminf(BWD ? aj - a_ref : a_ref - aj, offdiag ? 0.f : 64.f));
               if (!BWD) cf *= s_dt[cj0 + lane];
               scr[lane] = cf;
             }
             uint32_t v[32];
-#ifdef MB_EXP_NOSCALELD
-            for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(a_i + j);
-#else
             tmem_ld32(tCB + lane_sel + kcol, v);
-#endif
             __syncwarp();
             tmem_ld_wait();
+            const float2 rf2 = f2(rowf, rowf);
+            if (offdiag) {
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-              const float4 c4 = *reinterpret_cast<const float4*>(scr + 4 * q);
-              const bf162 lo = __floats2bfloat162_rn(__uint_as_float(v[4 * q]) * rowf * c4.x,
-                                                     __uint_as_float(v[4 * q + 1]) * rowf * c4.y);
-              const bf162 hi = __floats2bfloat162_rn(__uint_as_float(v[4 * q + 2]) * rowf * c4.z,
-                                                     __uint_as_float(v[4 * q + 3]) * rowf * c4.w);
-              pk[2 * q] = *reinterpret_cast<const uint32_t*>(&lo);
-              pk[2 * q + 1] = *reinterpret_cast<const uint32_t*>(&hi);
+              for (int q = 0; q < 8; ++q) {  // column pairs: FMUL2 x 2 + one pack per pair
+                const float4 c4 = *reinterpret_cast<const float4*>(scr + 4 * q);
+                const float2 lo2 = mul2(mul2(f2(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1])), rf2), f2(c4.x, c4.y));
+                const float2 hi2 = mul2(mul2(f2(__uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3])), rf2), f2(c4.z, c4.w));
+                const bf162 lo = __floats2bfloat162_rn(lo2.x, lo2.y), hi = __floats2bfloat162_rn(hi2.x, hi2.y);
+                pk[2 * q] = *reinterpret_cast<const uint32_t*>(&lo);
+                pk[2 * q + 1] = *reinterpret_cast<const uint32_t*>(&hi);
+              }
+            } else {
+#pragma unroll
+              for (int q = 0; q < 8; ++q) {  // same, plus the causal mask: column t of the chunk vs row `lane`
+                const float4 c4 = *reinterpret_cast<const float4*>(scr + 4 * q);
+                float2 lo2 = mul2(mul2(f2(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1])), rf2), f2(c4.x, c4.y));
+                float2 hi2 = mul2(mul2(f2(__uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3])), rf2), f2(c4.z, c4.w));
+                lo2.x = (BWD ? (4 * q >= lane) : (4 * q <= lane)) ? lo2.x : 0.f;
+                lo2.y = (BWD ? (4 * q + 1 >= lane) : (4 * q + 1 <= lane)) ? lo2.y : 0.f;
+                hi2.x = (BWD ? (4 * q + 2 >= lane) : (4 * q + 2 <= lane)) ? hi2.x : 0.f;
+                hi2.y = (BWD ? (4 * q + 3 >= lane) : (4 * q + 3 <= lane)) ? hi2.y : 0.f;
+                const bf162 lo = __floats2bfloat162_rn(lo2.x, lo2.y), hi = __floats2bfloat162_rn(hi2.x, hi2.y);
+                pk[2 * q] = *reinterpret_cast<const uint32_t*>(&lo);
+                pk[2 * q + 1] = *reinterpret_cast<const uint32_t*>(&hi);
+              }
             }
           } else if (!skip) {
             uint32_t v[32];
-#ifdef MB_EXP_NOSCALELD
-            for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(a_i + j);
-#else
             tmem_ld32(tCB + lane_sel + kcol, v);
-#endif
             tmem_ld_wait();
             // branch-free (the causal mask is a bit mask) and in groups of 4 columns whose a_j / dt_j
             // come from one 128-bit broadcast load each: keeps ~16 independent exp chains in flight
