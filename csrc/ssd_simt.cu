@@ -200,6 +200,51 @@ __global__ void ssd_bwd_finalize_kernel(const bf16* __restrict__ dy, long long l
   }
 }
 
+
+// K23 (Mamba-2 decode): one token of the recurrence for every (batch, head).
+//   state[p][n] = state[p][n] * exp(dt * A_h) + dt * x[p] * B[n]
+//   y[p]        = sum_n state[p][n] * C[n] + D_h * x[p]        (* silu(z[p]) when z is given)
+// One block per (b, h); a warp walks rows p, each lane owning N/32 consecutive state columns, so the fp32
+// state (the only real traffic: P*N*4 bytes read + written) moves in whole 128-byte lines.
+__global__ void __launch_bounds__(256)
+ssd_state_update_kernel(float* __restrict__ state, const bf16* __restrict__ x, long long ldx,
+                        const bf16* __restrict__ dt_raw, long long lddt, const float* __restrict__ A,
+                        const bf16* __restrict__ Bm, const bf16* __restrict__ Cm, long long ldbc,
+                        const float* __restrict__ D, const bf16* __restrict__ z, long long ldz,
+                        const float* __restrict__ dt_bias, bf16* __restrict__ y, long long ldy, int H, int G,
+                        int P, int N, int softplus) {
+  const int b = blockIdx.x / H, h = blockIdx.x % H;
+  const int g = h / (H / G);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  float dt = __bfloat162float(dt_raw[(size_t)b * lddt + h]) + (dt_bias != nullptr ? dt_bias[h] : 0.f);
+  if (softplus) dt = softplus_f(dt);
+  const float dA = fast_exp(dt * A[h]);
+  const int per = N / 32;  // 4 for d_state 128
+  float bv[8], cv[8];
+  for (int i = 0; i < per; ++i) {
+    bv[i] = __bfloat162float(Bm[(size_t)b * ldbc + g * N + lane * per + i]) * dt;
+    cv[i] = __bfloat162float(Cm[(size_t)b * ldbc + g * N + lane * per + i]);
+  }
+  float* st = state + ((size_t)b * H + h) * P * N;
+  const float Dh = D != nullptr ? D[h] : 0.f;
+  for (int p = warp; p < P; p += nw) {
+    const float xv = __bfloat162float(x[(size_t)b * ldx + h * P + p]);
+    float acc = 0.f;
+    float* row = st + (size_t)p * N + lane * per;
+    for (int i = 0; i < per; ++i) {
+      const float sv = row[i] * dA + bv[i] * xv;
+      row[i] = sv;
+      acc += sv * cv[i];
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) {
+      float o = acc + Dh * xv;
+      if (z != nullptr) o *= silu_f(__bfloat162float(z[(size_t)b * ldz + h * P + p]));
+      y[(size_t)b * ldy + h * P + p] = __float2bfloat16(o);
+    }
+  }
+}
+
 }  // namespace mb
 using namespace mb;
 
@@ -247,4 +292,17 @@ extern "C" int mb_ssd_bwd_finalize(const void* dy, long long lddy, const void* y
                                                     (const bf16*)dt_raw, ld_dt, dt, ddt1, ddt2, rowsum_m, da_last, dt_bias,
                                                     A_log, (bf16*)draw_out, ld_draw, dA_log, ddt_bias, T, H, P, L, nc);
   return check_launch("ssd_bwd_finalize");
+}
+
+extern "C" int mb_ssd_state_update(float* state, const void* x, long long ldx, const void* dt_raw, long long lddt,
+                                   const float* A, const void* Bm, const void* Cm, long long ldbc, const float* D,
+                                   const void* z, long long ldz, const float* dt_bias, void* y, long long ldy,
+                                   int B, int H, int G, int P, int N, int softplus, cudaStream_t stream) {
+  MB_REQUIRE(N % 32 == 0 && N <= 256, "ssd_state_update: d_state %d must be a multiple of 32 and <= 256", N);
+  MB_REQUIRE(H % G == 0, "ssd_state_update: nheads %% ngroups != 0");
+  if (B * H == 0) return 0;
+  ssd_state_update_kernel<<<B * H, 256, 0, stream>>>(state, (const bf16*)x, ldx, (const bf16*)dt_raw, lddt, A,
+                                                     (const bf16*)Bm, (const bf16*)Cm, ldbc, D, (const bf16*)z, ldz,
+                                                     dt_bias, (bf16*)y, ldy, H, G, P, N, softplus);
+  return check_launch("ssd_state_update");
 }

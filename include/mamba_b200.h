@@ -132,6 +132,12 @@ int mb_sscan_bwd(const void* u, long long ldu, const void* delta, long long ldd,
                  const float* scratch, float* scratch2, void* du, long long lddu, void* ddelta,
                  long long lddd, float* dA, float* dB, float* dC, float* dD, void* dz, long long lddz,
                  float* dbias, int B, int T, int Dn, int N, int softplus, cudaStream_t stream);
+/* K23 (Mamba-2 decode, mamba_ssm selective_state_update with heads): in-place fp32 state [B,H,P,N] step for
+ * one token; x, z, y [B, H*P] bf16 rows, dt_raw [B, H] bf16, Bm / Cm [B, G*N] bf16 rows (stride ldbc). */
+int mb_ssd_state_update(float* state, const void* x, long long ldx, const void* dt_raw, long long lddt,
+                        const float* A, const void* Bm, const void* Cm, long long ldbc, const float* D,
+                        const void* z, long long ldz, const float* dt_bias, void* y, long long ldy,
+                        int B, int H, int G, int P, int N, int softplus, cudaStream_t stream);
 int mb_sscan_update(float* state, const void* x, long long ldx, const void* delta, long long ldd,
                     const float* A, const void* Bm, long long ldb, const void* Cm, long long ldc,
                     const float* D, const void* z, long long ldz, const float* delta_bias, void* y,

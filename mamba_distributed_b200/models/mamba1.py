@@ -95,20 +95,21 @@ class Mamba(nn.Module):
         dtype = hidden_states.dtype
         xz = ops.linear(hidden_states.squeeze(1), self.in_proj.weight, self.in_proj.bias)
         x, z = xz.chunk(2, dim=-1)
-        x = ref.causal_conv1d_update_ref(x, conv_state, self.conv1d.weight.squeeze(1),
-                                         self.conv1d.bias, self.activation)
+        x = ops.causal_conv1d_update(x, conv_state, self.conv1d.weight.squeeze(1),
+                                     self.conv1d.bias, self.activation)
         x_db = ops.linear(x, self.x_proj.weight)
         dt, Bm, Cm = torch.split(x_db, [self.dt_rank, self.d_state, self.d_state], dim=-1)
         dt = ops.linear(dt, self.dt_proj.weight)
         A = -torch.exp(self.A_log.float())
-        y = ref.selective_state_update_ref(ssm_state, x, dt, A, Bm, Cm, self.D.float(), z,
-                                           self.dt_proj.bias.float(), True)
+        y = ops.selective_state_update(ssm_state, x, dt, A, Bm, Cm, self.D.float(), z,
+                                       self.dt_proj.bias.float(), True)
         out = ops.linear(y.to(dtype), self.out_proj.weight, self.out_proj.bias)
         return out.unsqueeze(1), conv_state, ssm_state
 
     def allocate_inference_cache(self, batch_size, max_seqlen, dtype=None, **kwargs):
         device = self.out_proj.weight.device
-        conv_dtype = self.conv1d.weight.dtype if dtype is None else dtype
+        conv_dtype = torch.float32 if device.type == "cuda" and dtype is None else \
+            (self.conv1d.weight.dtype if dtype is None else dtype)
         conv_state = torch.zeros(batch_size, self.d_inner, self.d_conv, device=device, dtype=conv_dtype)
         ssm_state = torch.zeros(batch_size, self.d_inner, self.d_state, device=device,
                                 dtype=torch.float32)

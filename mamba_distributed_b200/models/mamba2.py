@@ -131,12 +131,12 @@ class Mamba2(nn.Module):
         zxbcdt = ops.linear(hidden_states.squeeze(1), self.in_proj.weight, self.in_proj.bias)
         d_in, gn = self.d_inner, self.ngroups * self.d_state
         z, xBC, dt = torch.split(zxbcdt, [d_in, d_in + 2 * gn, self.nheads], dim=-1)
-        xBC = ref.causal_conv1d_update_ref(xBC, conv_state, self.conv1d.weight.squeeze(1),
-                                           self.conv1d.bias, self.activation)
+        xBC = ops.causal_conv1d_update(xBC, conv_state, self.conv1d.weight.squeeze(1),
+                                       self.conv1d.bias, self.activation)
         x, Bm, Cm = torch.split(xBC, [d_in, gn, gn], dim=-1)
         A = -torch.exp(self.A_log.float())
         B_ = x.shape[0]
-        y = ref.ssd_state_update_ref(
+        y = ops.ssd_state_update(
             ssm_state, x.reshape(B_, self.nheads, self.headdim), dt, A,
             Bm.reshape(B_, self.ngroups, self.d_state), Cm.reshape(B_, self.ngroups, self.d_state),
             D=self.D, z=None if self.rmsnorm else z.reshape(B_, self.nheads, self.headdim),
@@ -149,7 +149,9 @@ class Mamba2(nn.Module):
 
     def allocate_inference_cache(self, batch_size, max_seqlen, dtype=None, **kwargs):
         device = self.out_proj.weight.device
-        conv_dtype = self.conv1d.weight.dtype if dtype is None else dtype
+        # fp32 on GPU: the decode kernels keep both rolling states in fp32 (mb_conv1d_update / mb_ssd_state_update)
+        conv_dtype = torch.float32 if device.type == "cuda" and dtype is None else \
+            (self.conv1d.weight.dtype if dtype is None else dtype)
         conv_state = torch.zeros(batch_size, self.conv_dim, self.d_conv, device=device,
                                  dtype=conv_dtype)
         ssm_state = torch.zeros(batch_size, self.nheads, self.headdim, self.d_state, device=device,

@@ -5,10 +5,13 @@ from .dispatch import native_enabled, native_mode, use_native, bf16_policy  # no
 from .functional import (  # noqa: F401
     add_rms_norm,
     causal_conv1d,
+    causal_conv1d_update,
     embedding,
     gated_rms_norm,
     linear,
     linear_cross_entropy,
     selective_scan,
+    selective_state_update,
     ssd_combined,
+    ssd_state_update,
 )

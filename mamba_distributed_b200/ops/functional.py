@@ -53,6 +53,33 @@ def selective_scan(u, delta, A, B, C, D=None, z=None, delta_bias=None, delta_sof
     return ref.selective_scan_chunked_ref(u, delta, A, B, C, D, z, delta_bias, delta_softplus)
 
 
+def _native_state(x, state):
+    return use_native(x) and state.is_cuda and state.dtype == torch.float32 and state.is_contiguous() \
+        and not torch.is_grad_enabled()
+
+
+def causal_conv1d_update(x, conv_state, weight, bias=None, activation="silu"):
+    """K3: single-token conv step; ``conv_state [B, C, W]`` rolled in place."""
+    if _native_state(x, conv_state) and 2 <= conv_state.shape[-1] <= 4:
+        return _native().conv1d_update(x, conv_state, weight, bias, activation in ("silu", "swish"))
+    return ref.causal_conv1d_update_ref(x, conv_state, weight, bias, activation)
+
+
+def ssd_state_update(state, x, dt, A, B, C, D=None, z=None, dt_bias=None, dt_softplus=True):
+    """K23: Mamba-2 single-token state update; ``state [B, H, P, N]`` updated in place."""
+    if _native_state(x, state) and state.shape[-1] % 32 == 0 and state.shape[-1] <= 256:
+        return _native().ssd_state_update(state, x, dt, A, B, C, D, z, dt_bias, dt_softplus)
+    return ref.ssd_state_update_ref(state, x, dt, A, B, C, D, z, dt_bias, dt_softplus)
+
+
+def selective_state_update(state, x, dt, A, B, C, D=None, z=None, dt_bias=None, dt_softplus=True):
+    """K23: Mamba-1 single-token state update; ``state [B, Dn, N]`` updated in place."""
+    if _native_state(x, state) and state.shape[-1] == 16:
+        from . import sscan_kernels
+        return sscan_kernels.selective_state_update(state, x, dt, A, B, C, D, z, dt_bias, dt_softplus)
+    return ref.selective_state_update_ref(state, x, dt, A, B, C, D, z, dt_bias, dt_softplus)
+
+
 def linear(x, weight, bias=None):
     """K16: ``x @ weight.T (+ bias)``; tcgen05 GEMM on the native path."""
     if use_native(x):

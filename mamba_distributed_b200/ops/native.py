@@ -292,6 +292,36 @@ def k_conv1d_bwd(x3, w, b, dy3, dx3, dw, db, silu=True):
          w.shape[1], int(silu))
 
 
+def conv1d_update(x, conv_state, weight, bias, silu=True):
+    """K3 (decode): x [B, C]; conv_state fp32 [B, C, W] rolled in place; returns bf16 [B, C].
+    Replaces causal_conv1d_update (reference: mamba_ssm Mamba2.step / Mamba.step)."""
+    Bsz, C = x.shape
+    xb = x.to(torch.bfloat16)
+    if xb.stride(1) != 1:
+        xb = xb.contiguous()
+    w = weight.squeeze(1) if weight.dim() == 3 else weight
+    y = torch.empty(Bsz, C, dtype=torch.bfloat16, device=x.device)
+    call("mb_conv1d_update", xb, xb.stride(0), conv_state, w.float().contiguous(),
+         bias.float().contiguous() if bias is not None else None, y, C, Bsz, C, w.shape[1], int(silu))
+    return y
+
+
+def ssd_state_update(state, x, dt, A, Bm, Cm, D=None, z=None, dt_bias=None, dt_softplus=True):
+    """K23 (Mamba-2 decode): state fp32 [B,H,P,N] updated in place; x, z [B,H,P]; dt [B,H]; B, C [B,G,N]."""
+    Bsz, H, P = x.shape
+    G, N = Bm.shape[1], Bm.shape[2]
+    xb = x.to(torch.bfloat16).reshape(Bsz, H * P).contiguous()
+    dtb = dt.to(torch.bfloat16).contiguous()
+    Bb = Bm.to(torch.bfloat16).reshape(Bsz, G * N).contiguous()
+    Cb = Cm.to(torch.bfloat16).reshape(Bsz, G * N).contiguous()
+    zb = z.to(torch.bfloat16).reshape(Bsz, H * P).contiguous() if z is not None else None
+    y = torch.empty(Bsz, H * P, dtype=torch.bfloat16, device=x.device)
+    call("mb_ssd_state_update", state, xb, H * P, dtb, H, A.float().contiguous(), Bb, Cb, G * N,
+         D.float().contiguous() if D is not None else None, zb, H * P,
+         dt_bias.float().contiguous() if dt_bias is not None else None, y, H * P, Bsz, H, G, P, N, int(dt_softplus))
+    return y.view(Bsz, H, P)
+
+
 class CausalConv1dFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias, silu):
