@@ -10,7 +10,8 @@
 //
 // Structure (one CTA per SM, persistent over output tiles, 6 warps):
 //   warp 0    TMA producer   cp.async.bulk.tensor -> 128B-swizzled smem ring, mbarrier tx-count
-//   warp 1    MMA issuer     tcgen05.mma.cta_group::1.kind::f16, 128 x BN x 16, fp32 accum in TMEM;
+//   warp 1    MMA issuer     tcgen05.mma.kind::f16, fp32 accum in TMEM: 256 x BN x 16 across a CTA pair
+//                            (cta_group::2, the default for BN = 256) or 128 x BN x 16 per CTA (cta_group::1);
 //                            tcgen05.commit releases smem stages and publishes the accumulator
 //   warps 2-5 epilogue       tcgen05.ld (32 lanes x 32 cols) -> registers -> global
 // Two TMEM accumulators (2 x BN columns) let the epilogue of tile i overlap the mainloop of
@@ -44,11 +45,14 @@ __device__ __forceinline__ void decode_tile(int tile, int tiles_m, int tiles_n, 
 
 enum { EPI_BF16 = 0, EPI_F32 = 1, EPI_F32_ATOMIC = 2 };
 
-template <int BN>
+enum { MODE_SINGLE = 0, MODE_MULTICAST = 1, MODE_PAIR = 2 };
+
+template <int BN, int MODE = MODE_SINGLE>
 struct GemmCfg {
-  static constexpr int STAGES = BN == 256 ? 4 : 6;
+  // MODE_PAIR: each CTA of the pair keeps only its half of the B tile, which buys two more stages
+  static constexpr int STAGES = MODE == MODE_PAIR ? 6 : (BN == 256 ? 4 : 6);
   static constexpr int A_BYTES = BM * BK * 2;
-  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int B_BYTES = (MODE == MODE_PAIR ? BN / 2 : BN) * BK * 2;
   static constexpr int STAGING = 4 * 2 * 4096;  // 4 epilogue warps x 2 buffers x [32 rows][128 B]
   static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + STAGING + 1024 /*align slack*/ + 256 /*barriers*/;
 };
@@ -58,13 +62,22 @@ struct GemmCfg {
 // both CTAs, which cuts L2->SM operand traffic per tile from 48 KB to 32 KB per k-block (the
 // mainloop is L2-bandwidth bound otherwise: ncu showed 64 % tensor-pipe activity at 148 x 48 KB
 // per 512 clk).  Stage release needs both CTAs' MMA commits (multicast commit, count 2).
-template <int BN, uint32_t A_MAJOR, uint32_t B_MAJOR, int EPI, bool TMA_STORE, bool MC>
+//
+// MODE_PAIR: the two CTAs of a cluster form one `cta_group::2` MMA: a 256 x BN tile whose A rows and TMEM
+// accumulator rows are split across the two SMs and whose B tile is split in halves of BN/2 rows, one per
+// SM.  Only the even CTA issues tcgen05.mma / tcgen05.commit; both run a TMA producer (whose transaction
+// bytes are all counted on the even CTA's full barrier) and an epilogue over their own TMEM.  Per k-block
+// each SM now reads 16 KB (A) + 16 KB (half of B) from L2 AND from its own shared memory, instead of
+// 16 + 32 KB: the tensor pipe was waiting on the shared-memory operand feed (ncu: 64 % active).
+template <int BN, uint32_t A_MAJOR, uint32_t B_MAJOR, int EPI, bool TMA_STORE, int MODE>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmD, void* __restrict__ Dout, const float* __restrict__ bias, int Mg, int Ng, int Kg,
                  long long ldd, int splitk, int kb_per_split, float alpha) {
-  using Cfg = GemmCfg<BN>;
+  using Cfg = GemmCfg<BN, MODE>;
   constexpr int STAGES = Cfg::STAGES;
+  constexpr bool MC = MODE != MODE_SINGLE;   // launched as clusters of 2 that share an N block
+  constexpr bool PAIR = MODE == MODE_PAIR;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
@@ -91,13 +104,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     prefetch_tensormap(&tmA);
     prefetch_tensormap(&tmB);
     if (TMA_STORE) prefetch_tensormap(&tmD);
-    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], MC ? 2 : 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 4); }
+    // multicast: a stage is free once BOTH CTAs' MMAs released it; pair: one (multicast) commit per CTA
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], (MC && !PAIR) ? 2 : 1); }
+    // pair: the issuing CTA waits for the epilogue warps of both CTAs before it reuses an accumulator
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], PAIR ? 8 : 4); }
     fence_mbar_init();
   }
   if (warp == 1) {
-    tmem_alloc(tmem_slot, 2 * BN);
-    tmem_relinquish();
+    if (PAIR) { tmem_alloc2(tmem_slot, 2 * BN); tmem_relinquish2(); }
+    else { tmem_alloc(tmem_slot, 2 * BN); tmem_relinquish(); }
   }
   tc_fence_before();
   __syncthreads();
@@ -118,9 +133,30 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int kb1 = min(kb0 + kb_per_split, kblocks);
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&full_bar[stage], Cfg::A_BYTES + Cfg::B_BYTES);
           uint8_t* a_dst = sA + stage * Cfg::A_BYTES;
           uint8_t* b_dst = sB + stage * Cfg::B_BYTES;
+          if (PAIR) {
+            // both CTAs' loads complete on the even CTA's barrier, which expects the bytes of both
+            if (crank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * (Cfg::A_BYTES + Cfg::B_BYTES));
+            if (A_MAJOR == MAJOR_K) {
+              tma_load_2d_pair(a_dst, &tmA, &full_bar[stage], kb * BK, m_blk * BM);
+            } else {
+#pragma unroll
+              for (int j = 0; j < BM / 64; ++j)
+                tma_load_2d_pair(a_dst + j * (BK * 128), &tmA, &full_bar[stage], m_blk * BM + j * 64, kb * BK);
+            }
+            if (B_MAJOR == MAJOR_K) {  // tmB here is the half-height (BN/2 rows) box
+              tma_load_2d_pair(b_dst, &tmB, &full_bar[stage], kb * BK, n_blk * BN + crank * (BN / 2));
+            } else {
+#pragma unroll
+              for (int j = 0; j < BN / 128; ++j)
+                tma_load_2d_pair(b_dst + j * (BK * 128), &tmB, &full_bar[stage],
+                                 n_blk * BN + (crank * (BN / 128) + j) * 64, kb * BK);
+            }
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            continue;
+          }
+          mbar_arrive_expect_tx(&full_bar[stage], Cfg::A_BYTES + Cfg::B_BYTES);
           if (A_MAJOR == MAJOR_K) {
             tma_load_2d(a_dst, &tmA, &full_bar[stage], kb * BK, m_blk * BM);
           } else {
@@ -155,8 +191,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ========================================
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MAJOR, B_MAJOR);
+    if (lane == 0 && (!PAIR || crank == 0)) {
+      constexpr uint32_t idesc = make_idesc_bf16(PAIR ? 2 * BM : BM, BN, A_MAJOR, B_MAJOR);
       // K-major: +32 B per UMMA_K inside the swizzle row; MN-major: +16 k-rows * 128 B
       constexpr uint32_t a_kstep = A_MAJOR == MAJOR_K ? 32 : 16 * 128;
       constexpr uint32_t b_kstep = B_MAJOR == MAJOR_K ? 32 : 16 * 128;
@@ -183,14 +219,18 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           for (int k = 0; k < BK / 16; ++k) {
             const uint64_t da = make_smem_desc(a_addr + k * a_kstep, a_lbo, 1024);
             const uint64_t db = make_smem_desc(b_addr + k * b_kstep, b_lbo, 1024);
-            mma_bf16_ss(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            if (PAIR) mma_bf16_ss_pair(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            else mma_bf16_ss(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
           // frees this smem stage when the MMAs above retire (in BOTH CTAs with MC: the peer's
-          // producer multicasts into our stage too)
-          if (MC) mma_commit_mc(&empty_bar[stage], 0b11); else mma_commit(&empty_bar[stage]);
+          // producer multicasts into our stage too; with PAIR the MMA itself read both CTAs' stage)
+          if (PAIR) mma_commit_pair_mc(&empty_bar[stage], 0b11);
+          else if (MC) mma_commit_mc(&empty_bar[stage], 0b11);
+          else mma_commit(&empty_bar[stage]);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
-        mma_commit(&tfull_bar[acc]);  // accumulator complete -> epilogue
+        // accumulator complete -> epilogue (of both CTAs with PAIR)
+        if (PAIR) mma_commit_pair_mc(&tfull_bar[acc], 0b11); else mma_commit(&tfull_bar[acc]);
       }
     }
   } else {
@@ -306,14 +346,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      if (lane == 0) {
+        if (PAIR && crank != 0) mbar_arrive_cluster(&tempty_bar[acc], 0);  // the issuing (even) CTA owns the wait
+        else mbar_arrive(&tempty_bar[acc]);
+      }
     }
     if (TMA_STORE && lane == 0) tma_store_wait<0>();
   }
   tc_fence_before();
   __syncthreads();
   if (MC) cluster_sync_all();  // no CTA leaves while its peer may still signal / write into it
-  if (warp == 1) tmem_dealloc(tmem_base, 2 * BN);
+  if (warp == 1) { if (PAIR) tmem_dealloc2(tmem_base, 2 * BN); else tmem_dealloc(tmem_base, 2 * BN); }
 }
 
 // ---------------------------------------------------------------------------------- host side
@@ -323,6 +366,10 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   CUtensorMapFloatOOBfill);
 
 static EncodeTiledFn get_encode_fn() {
+  // The encode call is a driver-API entry point: it needs the primary context bound to the calling thread.
+  // Runtime calls bind it lazily, but an autograd worker thread may reach this before making any.
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) { cudaFree(nullptr); ctx_bound = true; }
   static EncodeTiledFn fn = nullptr;
   if (fn == nullptr) {
     void* p = nullptr;
@@ -387,14 +434,15 @@ int make_tmap_bf16_3d(CUtensorMap* map, const void* ptr, long long d2, long long
   return 0;
 }
 
-template <int BN, uint32_t AM, uint32_t BMJ, int EPI, bool TS, bool MC>
+template <int BN, uint32_t AM, uint32_t BMJ, int EPI, bool TS, int MODE>
 static int launch_gemm_mc(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, void* D,
                           const float* bias, int M, int N, int K, long long ldd, int splitk, int kb_per_split,
                           float alpha, cudaStream_t stream) {
-  auto kern = gemm_bf16_kernel<BN, AM, BMJ, EPI, TS, MC>;
+  constexpr bool MC = MODE != MODE_SINGLE;
+  auto kern = gemm_bf16_kernel<BN, AM, BMJ, EPI, TS, MODE>;
   static bool attr_set = false;
   if (!attr_set) {
-    MB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<BN>::SMEM));
+    MB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<BN, MODE>::SMEM));
     attr_set = true;
   }
   const int tiles_m = MC ? (cdiv(M, BM) + 1) / 2 : cdiv(M, BM);
@@ -403,7 +451,7 @@ static int launch_gemm_mc(const CUtensorMap& ta, const CUtensorMap& tb, const CU
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(kGemmThreads);
-  cfg.dynamicSmemBytes = GemmCfg<BN>::SMEM;
+  cfg.dynamicSmemBytes = GemmCfg<BN, MODE>::SMEM;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -422,13 +470,21 @@ static bool use_multicast() {
   return v == 1;
 }
 
+static bool use_pair() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("MAMBA_B200_GEMM_PAIR"); v = (e == nullptr || e[0] != '0') ? 1 : 0; }  // default on
+  return v == 1;
+}
+
 template <int BN, uint32_t AM, uint32_t BMJ, int EPI, bool TS>
 static int launch_gemm_ts(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tb_half, const CUtensorMap& td,
                           void* D, const float* bias, int M, int N, int K, long long ldd, int splitk, int kb_per_split,
                           float alpha, cudaStream_t stream) {
+  if (BN == 256 && use_pair() && cdiv(M, BM) >= 2)
+    return launch_gemm_mc<256, AM, BMJ, EPI, TS, MODE_PAIR>(ta, tb_half, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha, stream);
   if (use_multicast() && cdiv(M, BM) >= 2)
-    return launch_gemm_mc<BN, AM, BMJ, EPI, TS, true>(ta, tb_half, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha, stream);
-  return launch_gemm_mc<BN, AM, BMJ, EPI, TS, false>(ta, tb, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha, stream);
+    return launch_gemm_mc<BN, AM, BMJ, EPI, TS, MODE_MULTICAST>(ta, tb_half, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha, stream);
+  return launch_gemm_mc<BN, AM, BMJ, EPI, TS, MODE_SINGLE>(ta, tb, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha, stream);
 }
 
 template <int BN, uint32_t AM, uint32_t BMJ, int EPI>
