@@ -538,15 +538,26 @@ extern "C" int mb_gemm_bf16(const void* A, long long lda, int a_major, const voi
   // half-height box of the K-major B tile for the multicast path (MN-major boxes are per 64-wide atom already)
   if (b_major == 0) { if (make_tmap_bf16_2d(&tbh, B, N, K, ldb, BN / 2)) return 1; }
   else tbh = tb;
-  // split-K only where the epilogue is additive
+  // split-K only where the epilogue is additive.  The persistent grid runs whole waves of work units
+  // (tile pairs x splits when two CTAs share a tile column), so pick the split count that minimises
+  // waves x (k-blocks per split + the cost of one more additive epilogue), not just "enough units".
   const int kblocks = cdiv(K, BK);
   int splitk = 1;
   if (d_mode == 2) {
-    const int tiles = cdiv(M, BM) * cdiv(N, BN);
-    const int target = 4 * num_sms();
-    if (tiles < target) splitk = cdiv(target, tiles);
-    if (splitk > kblocks / 8) splitk = kblocks / 8;  // keep >= 8 k-blocks (512 deep) per split
-    if (splitk < 1) splitk = 1;
+    const bool paired = cdiv(M, BM) >= 2 && (use_multicast() || (BN == 256 && use_pair()));
+    const long long units = (long long)(paired ? (cdiv(M, BM) + 1) / 2 : cdiv(M, BM)) * cdiv(N, BN);
+    const int workers = paired ? num_sms() / 2 : num_sms();
+    int max_split = kblocks / 8;  // keep >= 8 k-blocks (512 deep) per split
+    if (max_split < 1) max_split = 1;
+    if (max_split > 64) max_split = 64;
+    long long best = -1;
+    for (int sk = 1; sk <= max_split; ++sk) {
+      const int per = cdiv(kblocks, sk);
+      const int real = cdiv(kblocks, per);
+      const long long waves = (units * real + workers - 1) / workers;
+      const long long cost = waves * (per + 6);
+      if (best < 0 || cost < best) { best = cost; splitk = real; }
+    }
   }
   int kbps = cdiv(kblocks, splitk);
   splitk = cdiv(kblocks, kbps);
