@@ -48,6 +48,8 @@ def parse_args():
     p.add_argument("--layer", default="Mamba2")
     p.add_argument("--comm", default="auto")
     p.add_argument("--no_e2e", action="store_true")
+    p.add_argument("--graphs", type=int, default=1,
+                   help="1: replay the non-final (no-sync) micro-steps from a CUDA graph (ours only); 0: all eager")
     return p.parse_args()
 
 
@@ -167,9 +169,18 @@ def main():
     host = [torch.randint(0, V, (2, B, T), generator=gen, dtype=torch.long).pin_memory() for _ in range(accum)]
     dev_batches = [h.to(device) for h in host]
 
+    graph = None
+    if fused and args.graphs and accum > 1:
+        # one-time, untimed: capture forward + backward of a no-sync micro-step (same kernels, same math)
+        from mamba_distributed_b200.parallel import MicroStepGraph
+        graph = MicroStepGraph(wrapped, 1.0 / accum, (B, T), device=device)
+        optimizer.zero_grad()
+
     def micro(x, y, last):
         if ddp or fused:
             wrapped.require_backward_grad_sync = last
+        if graph is not None and not last:
+            return graph(x, y).clone()
         with torch.autocast("cuda", dtype=torch.bfloat16):
             _, loss = wrapped(x, y)
         (loss / accum).backward()
@@ -189,7 +200,9 @@ def main():
         optimizer.zero_grad()
         loss_acc = torch.zeros((), device=device)
         for m in range(accum):
-            if from_host:
+            if from_host and graph is not None and m != accum - 1:
+                x, y = host[m][0], host[m][1]   # pinned host -> the graph's static input buffers, one copy
+            elif from_host:
                 xy = host[m].to(device, non_blocking=True)
                 x, y = xy[0], xy[1]
             else:
@@ -214,6 +227,7 @@ def main():
     if rank == 0:
         sampler.start()
     launches0 = _lib.kernel_launches()
+    replays0 = graph.replays if graph is not None else 0
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -221,7 +235,9 @@ def main():
         loss, _ = train_step(args.warmup + i, False)
     e1.record()
     barrier()
-    launches = _lib.kernel_launches() - launches0
+    launches = _lib.kernel_launches() - launches0   # launched through the library's entry points ...
+    if graph is not None:                            # ... plus the same kernels replayed from the captured graph
+        launches += (graph.replays - replays0) * graph.kernels_per_replay
     comm_t = None
     if fused and getattr(wrapped, "symm", None) is not None:
         t_ = wrapped.symm.last_timings()  # last timed step: device ms, this rank
@@ -268,7 +284,9 @@ def main():
                        "grad_accum": accum, "parallelism": f"dp{world}",
                        "optimizer": "AdamW(0.9,0.95) wd0.1 clip1.0, fp32 master + bf16 compute",
                        "l2": "per-step working set (activations, 1.1 GB grads, weights) >> 126 MB L2; no flush needed",
-                       "comm": getattr(wrapped, "comm", "nccl-ddp")},
+                       "comm": getattr(wrapped, "comm", "nccl-ddp"),
+                       "cuda_graph": ("non-final micro-steps replayed from one captured graph (forward+backward)"
+                                      if graph is not None else "off")},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "comm": comm_t,
             "loss_first": loss0, "loss_last": float(loss),
         }

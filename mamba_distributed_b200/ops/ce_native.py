@@ -57,7 +57,9 @@ class LinearCrossEntropyFn(torch.autograd.Function):
         assert ctx.reduction in ("mean", "sum"), "per-token losses are differentiable only via the PyTorch path"
         dh = dh * g.to(dh.dtype)
         if weight.requires_grad:
-            grad_buffer(weight).add_(dW, alpha=float(g))
+            # g stays on the device: float(g) would synchronise the host with the GPU at the start of every
+            # backward (and cannot be captured in a CUDA graph)
+            grad_buffer(weight).addcmul_(dW, g.to(dW.dtype))
             if not getattr(weight, "_tied_embedding", False):
                 notify_grad_ready(weight)
         return dh, None, None, None
