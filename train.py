@@ -68,6 +68,8 @@ def parse_args(argv=None):
     p.add_argument("--device", default=None)
     p.add_argument("--seed", type=int, default=1337)
     p.add_argument("--timers", action="store_true", help="print per-phase device timings")
+    p.add_argument("--cuda_graphs", type=int, default=1,
+                   help="replay the non-final micro-steps of a step from one captured CUDA graph (GPU + fused kernels only)")
     return p.parse_args(argv)
 
 
@@ -154,6 +156,10 @@ def main(argv=None):
     def autocast():
         return torch.autocast(device_type=device_type, dtype=torch.bfloat16)
 
+    from mamba_distributed_b200.ops import native_enabled
+    want_graph = bool(args.cuda_graphs) and use_cuda and grad_accum_steps > 1 and native_enabled()
+    micro_graph = None
+
     for step in range(start_step, max_steps):
         t0 = time.time()
         last_step = step == max_steps - 1
@@ -203,12 +209,21 @@ def main(argv=None):
 
         # ---- one optimisation step (train.py:202-241) --------------------------------------
         model.train()
+        if micro_graph is None and want_graph:
+            # first training step: capture forward + backward of a no-sync micro-step (its warm-up passes
+            # leave gradients in the arena, which the zero_grad below clears)
+            from mamba_distributed_b200.parallel import MicroStepGraph
+            micro_graph = MicroStepGraph(model, 1.0 / grad_accum_steps, (B, T), device=device)
         optimizer.zero_grad()
         loss_accum = torch.zeros((), device=device)
         for micro_step in range(grad_accum_steps):
             with timer("data"):
                 x, y = train_loader.next_batch_device(device)
             model.require_backward_grad_sync = micro_step == grad_accum_steps - 1
+            if micro_graph is not None and micro_step != grad_accum_steps - 1:
+                with timer("fwd+bwd (graph)"):
+                    loss_accum += micro_graph(x, y).float() / grad_accum_steps
+                continue
             with timer("fwd"):
                 with autocast():
                     logits, loss = model(x, y)
