@@ -132,6 +132,7 @@ __global__ void ssd_bwd_finalize_kernel(const bf16* __restrict__ dy, long long l
                                         int T, int H, int P, int L, int nc) {
   __shared__ float wsum[8];
   __shared__ float red3[2][8];
+  __shared__ float s_rowpart[256];
   const int b = blockIdx.x / nc, c = blockIdx.x % nc;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5, nw = blockDim.x >> 5;
   const int tok = c * L + t;
@@ -142,17 +143,29 @@ __global__ void ssd_bwd_finalize_kernel(const bf16* __restrict__ dy, long long l
     const size_t sidx = ((size_t)(b * nc + c) * H + h) * L + t;
     const float A = -fast_exp(A_log[h]);
     const float dtv = dt[sidx];
-    float rowpart = 0.f;
-    if (valid) {
-      const bf16* pdy = dy + row * lddy + h * P;
-      const bf16* py = y + row * ldy + h * P;
-      for (int p = 0; p < P; p += 8) {
-        float a8[8], b8[8];
-        unpack8(ld8(pdy + p), a8); unpack8(ld8(py + p), b8);
+    // sum_p dY[t,p] * y_off[t,p]: 8 lanes share one token row (16 bytes each = one full 128-byte line per
+    // row for P = 64), so every warp load is 4 complete lines instead of 32 partial ones
+    {
+      const int per_row = P >> 3;                   // 16-byte chunks per row (8 for P = 64)
+      const int rows_per_pass = blockDim.x / per_row;
+      const int chunk = t % per_row, r0 = t / per_row;
+      for (int rr = r0; rr < L; rr += rows_per_pass) {
+        const int tk = c * L + rr;
+        float acc = 0.f;
+        if (tk < T) {
+          const size_t ro = (size_t)b * T + tk;
+          float a8[8], b8[8];
+          unpack8(ld8(dy + ro * lddy + h * P + chunk * 8), a8);
+          unpack8(ld8(y + ro * ldy + h * P + chunk * 8), b8);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) rowpart += a8[j] * b8[j];
+          for (int j = 0; j < 8; ++j) acc += a8[j] * b8[j];
+        }
+        for (int o = per_row >> 1; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (chunk == 0) s_rowpart[rr] = acc;
       }
     }
+    __syncthreads();
+    float rowpart = s_rowpart[t];
     const float d1 = ddt1[sidx], d2 = ddt2[sidx];
     rowpart += rowsum_m[sidx];
     float da = rowpart - dtv * (d1 + d2);
@@ -286,7 +299,8 @@ extern "C" int mb_ssd_bwd_finalize(const void* dy, long long lddy, const void* y
                                    const float* A_log, void* draw_out, long long ld_draw, float* dA_log,
                                    float* ddt_bias, int B, int T, int H, int P, int L, cudaStream_t stream) {
   MB_REQUIRE(L == 64 || L == 128 || L == 256, "ssd_bwd_finalize: chunk size %d not in {64,128,256}", L);
-  MB_REQUIRE(P % 8 == 0, "ssd_bwd_finalize: headdim must be a multiple of 8");
+  MB_REQUIRE(P == 8 || P == 16 || P == 32 || P == 64 || P == 128 || P == 256,
+             "ssd_bwd_finalize: headdim %d must be a power of two in [8, 256] (lanes of one row reduce by shuffles)", P);
   const int nc = cdiv(T, L);
   ssd_bwd_finalize_kernel<<<dim3(B * nc, H), L, 0, stream>>>((const bf16*)dy, lddy, (const bf16*)y_off, ldy,
                                                     (const bf16*)dt_raw, ld_dt, dt, ddt1, ddt2, rowsum_m, da_last, dt_bias,
