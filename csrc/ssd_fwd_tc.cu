@@ -128,6 +128,12 @@ ssd_outer_kernel(const bf16* __restrict__ arow, long long lda, const bf16* __res
 #ifndef MB_EXP_NOSTORE
 #define MB_EXP_NOSTORE 0
 #endif
+#ifndef MB_TBLK
+#define MB_TBLK 5
+#endif
+#ifndef MB_TBWD
+#define MB_TBWD 0
+#endif
 #ifdef MB_SSD_TIMING
 __device__ long long g_tlog[32][64];   // [warp][event]: store-only marks (no atomics -> ~tens of cycles each)
 __device__ int g_tmeta[32][64];
@@ -188,19 +194,6 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
   const int ncols = BWD ? (2 - rh) * 128 : (rh + 1) * 128;
   const int nhalves = ncols >> 7;
 
-  if (tid == 0) {
-    mbar_init(cb_bar, 1);
-    mbar_init(ld_bar, 1);
-    for (int i = 0; i < kScanWarpsEpi; ++i) mbar_init(&x_full[i], 1);
-    for (int i = 0; i < 2; ++i) {
-      // one arrival per WARP (after __syncwarp): hundreds of per-thread arrivals on one mbarrier word serialise
-      mbar_init(&g_full[i], kScanWarpsScale); mbar_init(&g_empty[i], 1); mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], kScanWarpsEpi); mbar_init(&tiles_full[i], 1); mbar_init(&tiles_empty[i], kScanWarpsEpi);
-    }
-    fence_mbar_init();
-  }
-  if (warp == kScanWarpsScale + kScanWarpsEpi) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
-
   // per-head tiles by TMA (one lane): V tile [ncols][64] as 128-row boxes, state tile [64][128] as two
   // 64-column boxes; both land 128B-swizzled exactly as the UMMA descriptors expect them
   auto issue_head = [&](int hh) {
@@ -213,6 +206,30 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
     for (int kb = 0; kb < 2; ++kb)
       tma_load_2d(sS0 + bsel * kP * 2 * 128 + kb * kP * 128, &tmS, bar, kb * 64, (bc * H + h) * kP);
   };
+
+  // The producer lane initialises the barriers and, without waiting for anyone, starts the TMA loads of the
+  // row / column operands and of the tiles of heads 0 and 1: they fly while the other warps allocate TMEM
+  // and fetch a | dt (everything else waits for the __syncthreads below before touching a barrier).
+  if (warp == kScanWarpsScale + kScanWarpsEpi + 1 && lane == 0) {
+    mbar_init(cb_bar, 1);
+    mbar_init(ld_bar, 1);
+    for (int i = 0; i < kScanWarpsEpi; ++i) mbar_init(&x_full[i], 1);
+    for (int i = 0; i < 2; ++i) {
+      // one arrival per WARP (after __syncwarp): hundreds of per-thread arrivals on one mbarrier word serialise
+      mbar_init(&g_full[i], kScanWarpsScale); mbar_init(&g_empty[i], 1); mbar_init(&acc_full[i], 1);
+      mbar_init(&acc_empty[i], kScanWarpsEpi); mbar_init(&tiles_full[i], 1); mbar_init(&tiles_empty[i], kScanWarpsEpi);
+    }
+    fence_mbar_init();
+    mbar_arrive_expect_tx(ld_bar, (uint32_t)((128 + ncols) * 2 * 128));
+    for (int kb = 0; kb < 2; ++kb) {
+      tma_load_3d(sR + kb * 128 * 128, &tmRow, ld_bar, g * kN + kb * 64, c * kL + r0, b);
+      for (int rb = 0; rb < nhalves; ++rb)
+        tma_load_3d(sC + kb * ncols * 128 + rb * 128 * 128, &tmCol, ld_bar, g * kN + kb * 64, c * kL + c0 + rb * 128, b);
+    }
+    issue_head(0);
+    if (hgs > 1) issue_head(1);
+  }
+  if (warp == kScanWarpsScale + kScanWarpsEpi) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
 
   // ---- prologue: a | dt of every head of the group (2 KB each, cp.async by everyone) ----
   for (int i = tid; i < hgs * kL; i += kScanThreads) {
@@ -229,17 +246,6 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   const uint32_t tCB = tmem;
-  if (warp == kScanWarpsScale + kScanWarpsEpi + 1 && lane == 0) {
-    // row / column operands, then the tiles of heads 0 and 1
-    mbar_arrive_expect_tx(ld_bar, (uint32_t)((128 + ncols) * 2 * 128));
-    for (int kb = 0; kb < 2; ++kb) {
-      tma_load_3d(sR + kb * 128 * 128, &tmRow, ld_bar, g * kN + kb * 64, c * kL + r0, b);
-      for (int rb = 0; rb < nhalves; ++rb)
-        tma_load_3d(sC + kb * ncols * 128 + rb * 128 * 128, &tmCol, ld_bar, g * kN + kb * 64, c * kL + c0 + rb * 128, b);
-    }
-    issue_head(0);
-    if (hgs > 1) issue_head(1);
-  }
   if (warp == kScanWarpsScale + kScanWarpsEpi && lane == 0) {
     mbar_wait(ld_bar, 0);
     tc_fence_after();
@@ -255,7 +261,7 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
   tc_fence_after();
 
 #ifdef MB_SSD_TIMING
-  const bool tprint = blockIdx.x == 5 && blockIdx.y == 0 && !BWD;
+  const bool tprint = blockIdx.x == MB_TBLK && blockIdx.y == 0 && (BWD == (MB_TBWD != 0));
   const long long t_start = clock64();
   int tidx = 0;
 #define TMARK(role, hh, what) if (tprint && lane == 0 && tidx < 64) { g_tlog[warp][tidx] = clock64() - t_start; g_tmeta[warp][tidx] = ((hh) << 8) | (what[0]); ++tidx; }

@@ -13,7 +13,20 @@ import torch
 from ._lib import call
 from .native import bf16_weight, gemm_nn, gemm_nt, gemm_tn_acc, grad_buffer, notify_grad_ready
 
-SLAB_ROWS = 4096
+SLAB_ROWS = 4096   # upper bound when the device is unknown; see slab_rows()
+
+
+def slab_rows(d_model: int, device) -> int:
+    """Rows per slab.  The dgrad GEMM of a slab (``[R, V] x [V, d]``, K = V = 50304) has only
+    R/256 x ceil(d/256) output tile pairs, each a very long K loop, so R is chosen to make that one full wave
+    of the 74 CTA pairs (d = 768: 24 x 3 = 72 pairs -> R = 6144); the forward / wgrad GEMMs of the slab have
+    thousands of tiles either way."""
+    try:
+        pairs = torch.cuda.get_device_properties(device).multi_processor_count // 2
+    except Exception:  # pragma: no cover
+        return SLAB_ROWS
+    n_tiles = (d_model + 255) // 256
+    return int(min(8192, max(1024, 256 * (pairs // n_tiles))))
 
 
 class LinearCrossEntropyFn(torch.autograd.Function):
@@ -30,11 +43,12 @@ class LinearCrossEntropyFn(torch.autograd.Function):
         dW = torch.zeros(V, d, dtype=torch.float32, device=h2.device) if need_grad else None
         scale = 1.0 / M if reduction == "mean" else 1.0
         targets = targets.contiguous()
-        R = min(SLAB_ROWS, M)
+        slab = slab_rows(d, h2.device)
+        R = min(slab, M)
         logits = torch.empty(R, V, dtype=torch.float32, device=h2.device)
         pb = torch.empty(R, V, dtype=torch.bfloat16, device=h2.device) if need_grad else None
-        for s in range(0, M, SLAB_ROWS):
-            e = min(M, s + SLAB_ROWS)
+        for s in range(0, M, slab):
+            e = min(M, s + slab)
             r = e - s
             gemm_nt(h2[s:e], w, out=logits[:r])                      # tcgen05 GEMM, fp32 slab
             call("mb_ce_slab", logits, V, targets[s:e], losses[s:e], pb, V, r, V, scale)
