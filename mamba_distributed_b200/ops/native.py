@@ -63,6 +63,16 @@ def grad_buffer(p: torch.Tensor) -> torch.Tensor:
     return p.grad
 
 
+def inplace_grad(p):
+    """fp32 gradient buffer of a parameter the backward kernels may add into directly (returning ``None`` to
+    autograd, like the wgrad GEMMs do), or ``None`` when the tensor is not a plain fp32 leaf.  Saves one
+    zero-fill + one AccumulateGrad add kernel per small parameter per layer (~700 launches per micro-step)."""
+    if p is None or not (p.is_leaf and p.requires_grad and p.dtype == torch.float32 and p.is_contiguous()):
+        return None
+    g = grad_buffer(p)
+    return g if (g.dtype == torch.float32 and g.is_contiguous()) else None
+
+
 def notify_grad_ready(p: torch.Tensor):
     """Nothing to do: autograd runs the parameter's post-accumulate-grad hooks right after the
     node that called us returns (even though we return ``None`` for the weight), which is when the
@@ -210,13 +220,15 @@ class AddRMSNormFn(torch.autograd.Function):
         dres_out = dres2 if dres2 is not None else torch.empty(M, D, dtype=torch.float32, device=dy.device)
         need_bf16 = not ctx.x_fp32
         dx_bf16 = torch.empty(M, D, dtype=torch.bfloat16, device=dy.device) if need_bf16 else None
-        dw = torch.empty(D, dtype=torch.float32, device=dy.device)
+        gw = inplace_grad(weight)
+        dw = gw if gw is not None else torch.empty(D, dtype=torch.float32, device=dy.device)
         nbytes = _lib.load().mb_norm_bwd_scratch_bytes(M, D)
         scratch = _get_scratch(dy.device, nbytes)
-        call("mb_add_rmsnorm_bwd", res_out, dy2, rstd, weight, dres2, dres_out, dx_bf16, dw, 0, scratch, M, D)
+        call("mb_add_rmsnorm_bwd", res_out, dy2, rstd, weight, dres2, dres_out, dx_bf16, dw, int(gw is not None),
+             scratch, M, D)
         dres_out = dres_out.view(ctx.shape)
         dx = dx_bf16.view(ctx.shape) if need_bf16 else dres_out
-        return dx, dw.to(weight.dtype), (dres_out if ctx.has_res else None), None, None
+        return dx, (None if gw is not None else dw.to(weight.dtype)), (dres_out if ctx.has_res else None), None, None
 
 
 def add_rms_norm(x, weight, residual, eps, prenorm):
@@ -236,13 +248,14 @@ def k_gated_rmsnorm_fwd(x, z, weight, eps, group_size):
     return out, rstd
 
 
-def k_gated_rmsnorm_bwd(x, z, weight, rstd, dout, dx, dz, group_size):
+def k_gated_rmsnorm_bwd(x, z, weight, rstd, dout, dx, dz, group_size, dw_acc=None):
+    """``dw_acc``: fp32 [D] buffer to ADD the weight gradient into (returned as is); None -> a fresh tensor."""
     M, D = x.shape
-    dw = torch.empty(D, dtype=torch.float32, device=x.device)
+    dw = dw_acc if dw_acc is not None else torch.empty(D, dtype=torch.float32, device=x.device)
     nbytes = _lib.load().mb_norm_bwd_scratch_bytes(M * (D // group_size), D)
     scratch = _get_scratch(x.device, nbytes)
     call("mb_gated_rmsnorm_bwd", x, x.stride(0), z, z.stride(0), weight, rstd, dout, dout.stride(0), dx,
-         dx.stride(0), dz, dz.stride(0), dw, 0, scratch, M, D, group_size)
+         dx.stride(0), dz, dz.stride(0), dw, int(dw_acc is not None), scratch, M, D, group_size)
     return dw
 
 
@@ -450,23 +463,33 @@ class Mamba2MixerFn(torch.autograd.Function):
         # gated norm: dy (SSD output grad) and dz (written into the z columns of d(zxbcdt))
         dzxbcdt = torch.empty_like(zxbcdt)
         dy = torch.empty_like(y)
-        dnorm_w = k_gated_rmsnorm_bwd(y, zxbcdt[:, :d_in], norm_w.float(), rstd, dyn, dy, dzxbcdt[:, :d_in], d_in // G)
+        g_norm = inplace_grad(norm_w)
+        dnorm_w = k_gated_rmsnorm_bwd(y, zxbcdt[:, :d_in], norm_w.float(), rstd, dyn, dy, dzxbcdt[:, :d_in], d_in // G,
+                                      dw_acc=g_norm)
         # SSD: dx|dB|dC -> dxBC ; ddt_raw -> dt columns of d(zxbcdt)
         dxBC = torch.empty_like(xBC)
         from . import ssd_native
-        ddt_bias, dA_log, dD = ssd_native.ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, ssd_saved)
+        # the per-head reductions and the conv weight gradients are atomic adds: straight into the .grad buffers
+        g_small = [inplace_grad(t) for t in (dt_bias, A_log, D)]
+        red_out = tuple(g_small) if all(g is not None for g in g_small) else None
+        ddt_bias, dA_log, dD = ssd_native.ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D,
+                                                  ssd_saved, red_out=red_out)
         # conv
-        dcw = torch.zeros_like(cw)
-        dcb = torch.zeros_like(cb) if cb is not None else None
+        g_cw, g_cb = inplace_grad(conv_w), inplace_grad(conv_b)
+        dcw = g_cw.view(cw.shape) if g_cw is not None else torch.zeros_like(cw)
+        dcb = (g_cb if g_cb is not None else torch.zeros_like(cb)) if cb is not None else None
         k_conv1d_bwd(zxbcdt.view(Bsz, T, -1)[:, :, d_in:d_in + conv_dim], cw, cb, dxBC.view(Bsz, T, conv_dim),
                      dzxbcdt.view(Bsz, T, -1)[:, :, d_in:d_in + conv_dim], dcw, dcb, True)
         # in_proj
         du = gemm_nn(dzxbcdt, w_in).view(Bsz, T, dm)
         gemm_tn_acc(dzxbcdt, u2, grad_buffer(in_w))
         notify_grad_ready(in_w)
-        return (du.to(ctx.udtype), None, dcw.view(conv_w.shape).to(conv_w.dtype),
-                dcb.to(conv_b.dtype) if dcb is not None else None, ddt_bias.to(dt_bias.dtype),
-                dA_log.to(A_log.dtype), dD.to(D.dtype), dnorm_w.to(norm_w.dtype), None, None)
+        small = red_out is not None
+        return (du.to(ctx.udtype), None,
+                None if g_cw is not None else dcw.view(conv_w.shape).to(conv_w.dtype),
+                None if (dcb is None or g_cb is not None) else dcb.to(conv_b.dtype),
+                None if small else ddt_bias.to(dt_bias.dtype), None if small else dA_log.to(A_log.dtype),
+                None if small else dD.to(D.dtype), None if g_norm is not None else dnorm_w.to(norm_w.dtype), None, None)
 
 
 def mamba2_mixer(mod, u):

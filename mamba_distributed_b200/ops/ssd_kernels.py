@@ -51,7 +51,7 @@ def ssd_fwd(xBC, zxbcdt, Bsz, T, cfg, dt_bias, A_log, D):
     return y, (dt, a, sprev, y_ssm)
 
 
-def ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, saved):
+def ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, saved, red_out=None):
     d_in, H, P, G, N, L = (cfg["d_inner"], cfg["nheads"], cfg["headdim"], cfg["ngroups"], cfg["d_state"],
                            cfg["chunk_size"])
     dt, a, sprev, y_ssm = saved
@@ -68,7 +68,10 @@ def ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, s
     call("mb_ssd_state_passing_bwd", dstates, sprev, a, ds, da_last, Bsz, nc, H, P * N, L)
     ddt12 = torch.zeros(3, Bsz, nc, H, L, dtype=torch.float32, device=dev)  # ddt1 | ddt2 | row sums of dM o M
     lddx = dxBC.stride(0)
-    red = torch.zeros(3, H, dtype=torch.float32, device=dev)  # dA_log | ddt_bias | dD
+    if red_out is not None:   # (ddt_bias, dA_log, dD) fp32 [H] buffers the kernels add into (parameter .grad)
+        red = (red_out[1], red_out[0], red_out[2])
+    else:
+        red = torch.zeros(3, H, dtype=torch.float32, device=dev)  # dA_log | ddt_bias | dD
     call("mb_ssd_chunk_scan_bwd_dx", Bm, Cm, ld, dy, lddy, ds, dt, a, D, dxBC, lddx, x, ld, ddt12[0], ddt12[1],
          red[2], Bsz, T, H, G, P, N, L)
     dcb = torch.empty(Bsz, nc, G, L, L, dtype=torch.bfloat16, device=dev)

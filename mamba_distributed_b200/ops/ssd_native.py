@@ -60,11 +60,17 @@ def ssd_fwd(xBC, zxbcdt, Bsz, T, cfg, dt_bias, A_log, D):
     return ssd_kernels.ssd_fwd(xBC, zxbcdt, Bsz, T, cfg, dt_bias, A_log, D)
 
 
-def ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, saved):
+def ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, saved, red_out=None):
+    """``red_out``: optional (ddt_bias, dA_log, dD) fp32 buffers to ADD the per-head gradients into."""
     if _use_torch(cfg):
-        return _torch_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, saved)
+        out = _torch_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, saved)
+        if red_out is not None:
+            for buf, g in zip(red_out, out):
+                buf.add_(g.to(buf.dtype))
+            return red_out
+        return out
     from . import ssd_kernels
-    return ssd_kernels.ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, saved)
+    return ssd_kernels.ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, saved, red_out=red_out)
 
 
 class SSDCombinedFn(torch.autograd.Function):
