@@ -19,8 +19,8 @@ constexpr int kThreadsB = 256;
 constexpr int kDcbSmem = 2 * 2 * (128 * 128) + 2 * 2 * kL * 4 + 2 * 4 * 128 * 4 + 64 + 1024;  // double-buffered per-head tiles + column factors
 
 __global__ void __launch_bounds__(kThreadsB, 2)
-ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restrict__ x, long long ldx,
-               const bf16* __restrict__ Cm, const bf16* __restrict__ Bm, long long ldbc,
+ssd_dcb_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX,
+               const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmB,
                const float* __restrict__ dtv, const float* __restrict__ av, bf16* __restrict__ dcb,
                float* __restrict__ rowsum_m, int T, int H, int G, int nc) {
   extern __shared__ uint8_t smem_raw[];
@@ -29,7 +29,9 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
   float* s_cf = s_ad + 2 * 2 * kL;                                   // [4 lane groups][128]  exp(a_ref - a_j)
   float* s_cd = s_cf + 4 * 128;                                      // [4 lane groups][128]  exp(a_ref - a_j) dt_j
   uint64_t* bar = reinterpret_cast<uint64_t*>(s_cd + 4 * 128);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 1);
+  uint64_t* tile_bar = bar + 1;   // [2] TMA transaction barriers of the double-buffered per-head tiles
+  uint64_t* ld_bar = bar + 3;     // C / B tiles of the prologue
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 4);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int blk = blockIdx.x % 3;
@@ -40,9 +42,17 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
   const int ri0 = blk == 0 ? 0 : 128;
   const int cj0 = blk == 2 ? 128 : 0;
   const int valid = min(kL, T - c * kL);
-  const size_t row_base = (size_t)b * T + (size_t)c * kL;
 
-  if (tid == 0) { mbar_init(bar, 1); fence_mbar_init(); }
+  if (tid == 0) {
+    mbar_init(bar, 1); mbar_init(&tile_bar[0], 1); mbar_init(&tile_bar[1], 1); mbar_init(ld_bar, 1);
+    fence_mbar_init();
+    // C / B tiles for the CB block: two 64-column boxes each, straight away (they borrow the per-head buffers)
+    mbar_arrive_expect_tx(ld_bar, 2 * 2 * 128 * 128);
+    for (int kb = 0; kb < 2; ++kb) {
+      tma_load_3d(smem + kb * 128 * 128, &tmC, ld_bar, g * kN + kb * 64, c * kL + ri0, b);
+      tma_load_3d(smem + 2 * 128 * 128 + kb * 128 * 128, &tmB, ld_bar, g * kN + kb * 64, c * kL + cj0, b);
+    }
+  }
   if (warp == 0) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
   tc_fence_before();
   __syncthreads();
@@ -56,15 +66,8 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
   {
     uint8_t* sCt = smem;
     uint8_t* sBt = smem + 2 * 128 * 128;
-    load_tile<2, false>(sCt, Cm + (row_base + ri0) * ldbc + g * kN, ldbc, 128, max(0, min(128, valid - ri0)), NoScale(),
-                        tid, kThreadsB);
-    load_tile<2, false>(sBt, Bm + (row_base + cj0) * ldbc + g * kN, ldbc, 128, max(0, min(128, valid - cj0)), NoScale(),
-                        tid, kThreadsB);
-    cp_async_commit();
-    cp_async_wait<0>();
-    fence_proxy_async_smem();
-    __syncthreads();
     if (tid == 0) {
+      mbar_wait(ld_bar, 0);
       tc_fence_after();
       constexpr uint32_t idesc = make_idesc_bf16(128, 128, MAJOR_K, MAJOR_K);
       const uint32_t a_addr = smem_u32(sCt), b_addr = smem_u32(sBt);
@@ -96,11 +99,12 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
     const uint32_t ad = smem_u32(s_ad + bsel * 2 * kL);
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(ad + tid * 4), "l"(av + sb + tid) : "memory");
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(ad + (kL + tid) * 4), "l"(dtv + sb + tid) : "memory");
-    uint8_t* t0 = smem + bsel * 2 * 128 * 128;
-    load_tile<1, false>(t0, dy + (row_base + ri0) * lddy + h * kP, lddy, 128, max(0, min(128, valid - ri0)),
-                        NoScale(), tid, kThreadsB);
-    load_tile<1, false>(t0 + 128 * 128, x + (row_base + cj0) * ldx + h * kP, ldx, 128,
-                        max(0, min(128, valid - cj0)), NoScale(), tid, kThreadsB);
+    if (tid == 0) {  // dY rows / X rows of this head by TMA: one 128 x 64 box each, 128B-swizzled
+      uint8_t* t0 = smem + bsel * 2 * 128 * 128;
+      mbar_arrive_expect_tx(&tile_bar[bsel], 2 * 128 * 128);
+      tma_load_3d(t0, &tmDY, &tile_bar[bsel], h * kP, c * kL + ri0, b);
+      tma_load_3d(t0 + 128 * 128, &tmX, &tile_bar[bsel], h * kP, c * kL + cj0, b);
+    }
     cp_async_commit();
   };
   prefetch_head(0);
@@ -115,6 +119,7 @@ ssd_dcb_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restri
     fence_proxy_async_smem();
     __syncthreads();
     if (tid == 0) {
+      mbar_wait(&tile_bar[hh & 1], (hh >> 1) & 1);
       tc_fence_after();
       constexpr uint32_t idesc = make_idesc_bf16(128, 128, MAJOR_K, MAJOR_K);
       const uint32_t a_addr = smem_u32(sDY), b_addr = smem_u32(sX);
@@ -370,6 +375,7 @@ ssd_dbdc_kernel(const bf16* __restrict__ dcb,                       // [B,nc,G,2
 }
 
 }  // namespace ssd
+int make_tmap_bf16_3d(CUtensorMap* map, const void* ptr, long long d2, long long d1, long long cols, long long ld, int box_rows, int box_cols);
 }  // namespace mb
 using namespace mb;
 using namespace mb::ssd;
@@ -384,8 +390,11 @@ extern "C" int mb_ssd_bwd_dcb(const void* dy, long long lddy, const void* x, lon
   static bool once = false;
   if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_dcb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDcbSmem)); once = true; }
   dim3 grid(B * nc * 3, G);
-  ssd_dcb_kernel<<<grid, kThreadsB, kDcbSmem, stream>>>((const bf16*)dy, lddy, (const bf16*)x, ldx, (const bf16*)Cm,
-                                                        (const bf16*)Bm, ldbc, dt, a, (bf16*)dcb, rowsum_m, T, H, G, nc);
+  CUtensorMap tmDY, tmX, tmC, tmB;
+  if (make_tmap_bf16_3d(&tmDY, dy, B, T, (long long)H * P, lddy, 128, 64) || make_tmap_bf16_3d(&tmX, x, B, T, (long long)H * P, ldx, 128, 64) ||
+      make_tmap_bf16_3d(&tmC, Cm, B, T, (long long)G * N, ldbc, 128, 64) || make_tmap_bf16_3d(&tmB, Bm, B, T, (long long)G * N, ldbc, 128, 64))
+    return 1;
+  ssd_dcb_kernel<<<grid, kThreadsB, kDcbSmem, stream>>>(tmDY, tmX, tmC, tmB, dt, a, (bf16*)dcb, rowsum_m, T, H, G, nc);
   return check_launch("ssd_bwd_dcb");
 }
 
