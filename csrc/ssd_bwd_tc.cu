@@ -227,17 +227,18 @@ constexpr int kDbdcSmem = kDbdcStages * kDbdcStage + 64 + 1024;
 // 16-byte chunks its own cp.async brought in, so that pass needs no barrier of its own.
 template <bool IS_DB>
 __global__ void __launch_bounds__(kThreadsB, 2)
-ssd_dbdc_kernel(const bf16* __restrict__ dcb,                       // [B,nc,G,256,256]
-                const bf16* __restrict__ bc_op, long long ldbc,     // dC: Bm base ; dB: Cm base (group 0 column)
-                const bf16* __restrict__ act, long long ldact,      // dC: dy ; dB: x
-                const bf16* __restrict__ st,                        // dC: S_prev bf16 ; dB: dS bf16   [B,nc,H,P,N]
+ssd_dbdc_kernel(const __grid_constant__ CUtensorMap tmG,    // dCB   [B*nc*G*256][256], box 64 x 64
+                const __grid_constant__ CUtensorMap tmBC,   // dC: Bm ; dB: Cm   [B][T][G*N], box 64 x 64
+                const __grid_constant__ CUtensorMap tmAct,  // dC: dy ; dB: x    [B][T][H*P], box 64 x 64
+                const __grid_constant__ CUtensorMap tmSt,   // dC: S_prev bf16 ; dB: dS bf16  [B*nc*H*P][N], box 64 x 64
                 const float* __restrict__ dtv, const float* __restrict__ av,
                 bf16* __restrict__ outp, long long ldo,             // dC / dB column base of group 0 in dxBC
                 int T, int H, int G, int nc) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align1024(smem_raw);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kDbdcStages * kDbdcStage);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + kDbdcStages);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kDbdcStages * kDbdcStage);   // MMAs of a stage retired
+  uint64_t* full = bars + kDbdcStages;                                             // TMA bytes of a stage landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(full + kDbdcStages);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int rb = blockIdx.x & 1;
@@ -248,10 +249,10 @@ ssd_dbdc_kernel(const bf16* __restrict__ dcb,                       // [B,nc,G,2
   const int m0 = rb * 128;  // output row block (i for dC, j for dB)
   const int valid = min(kL, T - c * kL);
   const size_t row_base = (size_t)b * T + (size_t)c * kL;
-  const bf16* G_base = dcb + ((size_t)bc * G + g) * kL * kL;
+  const int g_row0 = (bc * G + g) * kL;   // first row of this (b, c, g) block in the dCB matrix
 
   if (tid == 0) {
-    for (int i = 0; i < kDbdcStages; ++i) mbar_init(&bars[i], 1);
+    for (int i = 0; i < kDbdcStages; ++i) { mbar_init(&bars[i], 1); mbar_init(&full[i], 1); }
     fence_mbar_init();
   }
   if (warp == 0) { tmem_alloc(tmem_slot, 128); tmem_relinquish(); }
@@ -267,22 +268,35 @@ ssd_dbdc_kernel(const bf16* __restrict__ dcb,                       // [B,nc,G,2
   const int n_stages = n_part1 + hpg;
   const int valid_m = max(0, min(128, valid - m0));
 
+  // every tile travels by TMA (one lane issues 4 boxes of 64 x 64 per operand pair and stage); only the 1 KB of
+  // per-row scale factors of the activation stages is copied by the threads themselves
   auto issue = [&](int s) {
     uint8_t* sA = smem + (s % kDbdcStages) * kDbdcStage;
     uint8_t* sB = sA + 128 * 128;
+    uint64_t* fb = &full[s % kDbdcStages];
     if (s < n_part1) {
-      const int kk = k_begin + s * 64;
-      const int kvalid = max(0, min(64, valid - kk));
-      if (!IS_DB)  // A = G[m0 + r, kk .. kk+63]  (K-major, 128 rows) ; B = Bm[kk + krow, n]  (MN-major, 64 k-rows)
-        load_tile<1, false>(sA, G_base + (size_t)m0 * kL + kk, kL, 128, 128, NoScale(), tid, kThreadsB);
-      else         // A = G[kk + krow, m0 .. m0+127]  (MN-major: 64 k-rows x 2 atoms)
-        load_tile<2, false>(sA, G_base + (size_t)kk * kL + m0, kL, 64, 64, NoScale(), tid, kThreadsB);
-      load_tile<2, false>(sB, bc_op + (row_base + kk) * ldbc + g * kN, ldbc, 64, kvalid, NoScale(), tid, kThreadsB);
+      if (tid == 0) {
+        const int kk = k_begin + s * 64;
+        mbar_arrive_expect_tx(fb, 2 * 128 * 128);
+        for (int j2 = 0; j2 < 2; ++j2) {
+          if (!IS_DB)  // A = G[m0 + r, kk .. kk+63]  (K-major, 128 rows as two 64-row boxes)
+            tma_load_2d(sA + j2 * 64 * 128, &tmG, fb, kk, g_row0 + m0 + j2 * 64);
+          else         // A = G[kk + krow, m0 .. m0+127]  (MN-major: 64 k-rows x 2 atoms of 64 columns)
+            tma_load_2d(sA + j2 * 64 * 128, &tmG, fb, m0 + j2 * 64, g_row0 + kk);
+          // B = (Bm | Cm)[kk + krow, n]  (MN-major, 64 k-rows x 2 atoms); rows past the sequence end read as zeros
+          tma_load_3d(sB + j2 * 64 * 128, &tmBC, fb, g * kN + j2 * 64, c * kL + kk, b);
+        }
+      }
     } else {
       const int h = g * hpg + (s - n_part1);
       const size_t sbase = ((size_t)bc * H + h) * kL;
-      load_tile<1, false>(sA, act + (row_base + m0) * ldact + h * kP, ldact, 128, valid_m, NoScale(), tid, kThreadsB);
-      load_tile<2, false>(sB, st + ((size_t)bc * H + h) * kP * kN, kN, kP, kP, NoScale(), tid, kThreadsB);
+      if (tid == 0) {
+        mbar_arrive_expect_tx(fb, 2 * 128 * 128);
+        for (int j2 = 0; j2 < 2; ++j2) {
+          tma_load_3d(sA + j2 * 64 * 128, &tmAct, fb, h * kP, c * kL + m0 + j2 * 64, b);   // [128 rows][64] K-major
+          tma_load_2d(sB + j2 * 64 * 128, &tmSt, fb, j2 * 64, (bc * H + h) * kP);          // [64 p][128 n] MN-major
+        }
+      }
       const uint32_t sc = smem_u32(sB + 64 * 2 * 128);
       if (tid < 128) {
         asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sc + tid * 4), "l"(av + sbase + m0 + tid) : "memory");
@@ -305,12 +319,13 @@ ssd_dbdc_kernel(const bf16* __restrict__ dcb,                       // [B,nc,G,2
       issue(s + 2);
     }
     cp_async_commit();   // (possibly empty) keeps one group per stage
-    cp_async_wait<2>();  // this thread's copies of stage s have landed
+    cp_async_wait<2>();  // this thread's scale-vector copies of stage s have landed
+    mbar_wait(&full[buf], (s / kDbdcStages) & 1);  // ... and so have the stage's TMA tiles
     uint8_t* sA = smem + buf * kDbdcStage;
     uint8_t* sB = sA + 128 * 128;
     const bool a_mn = IS_DB && s < n_part1;
     if (s >= n_part1) {
-      // the scale vectors were copied by other threads: one barrier for them, then in-place scaling of own chunks
+      // the scale vectors were copied by other threads: one barrier for them, then in-place scaling, 4 chunks each
       __syncthreads();
       const float* s_a = reinterpret_cast<const float*>(sB + 64 * 2 * 128);
       const float a_last = s_a[256];
@@ -375,6 +390,7 @@ ssd_dbdc_kernel(const bf16* __restrict__ dcb,                       // [B,nc,G,2
 }
 
 }  // namespace ssd
+int make_tmap_bf16_2d(CUtensorMap* map, const void* ptr, long long rows, long long cols, long long ld, int box_rows);
 int make_tmap_bf16_3d(CUtensorMap* map, const void* ptr, long long d2, long long d1, long long cols, long long ld, int box_rows, int box_cols);
 }  // namespace mb
 using namespace mb;
@@ -412,10 +428,15 @@ extern "C" int mb_ssd_bwd_dbdc(const void* dcb, const void* Bm, const void* Cm, 
     once = true;
   }
   dim3 grid(B * nc * 2, G);
-  ssd_dbdc_kernel<false><<<grid, kThreadsB, kDbdcSmem, stream>>>((const bf16*)dcb, (const bf16*)Bm, ldbc, (const bf16*)dy, lddy,
-                                                                 (const bf16*)sprev_bf16, dt, a, (bf16*)dC, ldo, T, H, G, nc);
+  CUtensorMap tmG, tmBm, tmCm, tmDy, tmX, tmSp, tmDs;
+  if (make_tmap_bf16_2d(&tmG, dcb, (long long)B * nc * G * L, L, L, 64) ||
+      make_tmap_bf16_3d(&tmBm, Bm, B, T, (long long)G * N, ldbc, 64, 64) || make_tmap_bf16_3d(&tmCm, Cm, B, T, (long long)G * N, ldbc, 64, 64) ||
+      make_tmap_bf16_3d(&tmDy, dy, B, T, (long long)H * P, lddy, 64, 64) || make_tmap_bf16_3d(&tmX, x, B, T, (long long)H * P, ldx, 64, 64) ||
+      make_tmap_bf16_2d(&tmSp, sprev_bf16, (long long)B * nc * H * P, N, N, 64) ||
+      make_tmap_bf16_2d(&tmDs, ds_bf16, (long long)B * nc * H * P, N, N, 64))
+    return 1;
+  ssd_dbdc_kernel<false><<<grid, kThreadsB, kDbdcSmem, stream>>>(tmG, tmBm, tmDy, tmSp, dt, a, (bf16*)dC, ldo, T, H, G, nc);
   if (check_launch("ssd_bwd_dbdc/dC")) return 1;
-  ssd_dbdc_kernel<true><<<grid, kThreadsB, kDbdcSmem, stream>>>((const bf16*)dcb, (const bf16*)Cm, ldbc, (const bf16*)x, ldx,
-                                                                (const bf16*)ds_bf16, dt, a, (bf16*)dB, ldo, T, H, G, nc);
+  ssd_dbdc_kernel<true><<<grid, kThreadsB, kDbdcSmem, stream>>>(tmG, tmCm, tmX, tmDs, dt, a, (bf16*)dB, ldo, T, H, G, nc);
   return check_launch("ssd_bwd_dbdc/dB");
 }
