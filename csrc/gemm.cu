@@ -207,12 +207,25 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int kb1 = min(kb0 + kb_per_split, kblocks);
         const int acc = local & 1;
         const uint32_t acc_phase = (local >> 1) & 1;
+#ifdef MB_GEMM_TIMING
+        const long long tt0 = clock64();
+#endif
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
+#ifdef MB_GEMM_TIMING
+        const long long tt1 = clock64();
+        long long twait_full = 0;
+#endif
         const uint32_t d_tmem = tmem_base + acc * BN;
         for (int kb = kb0; kb < kb1; ++kb) {
+#ifdef MB_GEMM_TIMING
+          const long long tf0 = clock64();
+#endif
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
+#ifdef MB_GEMM_TIMING
+          twait_full += clock64() - tf0;
+#endif
           const uint32_t a_addr = smem_u32(sA + stage * Cfg::A_BYTES);
           const uint32_t b_addr = smem_u32(sB + stage * Cfg::B_BYTES);
 #pragma unroll
@@ -231,6 +244,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
         // accumulator complete -> epilogue (of both CTAs with PAIR)
         if (PAIR) mma_commit_pair_mc(&tfull_bar[acc], 0b11); else mma_commit(&tfull_bar[acc]);
+#ifdef MB_GEMM_TIMING
+        if (blockIdx.x == 4 && local < 30)
+          printf("G tile %d start %lld wait_acc %lld wait_full %lld issue_total %lld\n", local, tt0, tt1 - tt0, twait_full, clock64() - tt0);
+#endif
       }
     }
   } else {
