@@ -148,7 +148,10 @@ __device__ __forceinline__ void unpack4(const bf16x4& p, float* f) {
   f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y;
 }
 
-template <int W, bool SILU>
+template <bool E> struct ConvEdgeTag { static constexpr bool value = E; };
+
+// NP = channel pairs per thread: 1 (4-byte accesses, ~70 registers, high occupancy) or 2 (8-byte accesses).
+template <int W, bool SILU, int NP>
 __global__ void __launch_bounds__(kConvThreads)
 conv1d_bwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __restrict__ w,
                   const float* __restrict__ bias, const bf16* __restrict__ dy, long long lddy,
@@ -156,16 +159,16 @@ conv1d_bwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __rest
                   float* __restrict__ dbias, int T, int C, int tile) {
   constexpr int H = W - 1;  // halo
   constexpr int U = 4;      // tokens per register batch
-  const int c0 = (blockIdx.x * kConvThreads + threadIdx.x) * 4;
+  const int c0 = (blockIdx.x * kConvThreads + threadIdx.x) * (2 * NP);
   if (c0 >= C) return;
   const int b = blockIdx.z;
   const int t0 = blockIdx.y * tile;
   const int t1 = min(t0 + tile, T);
   // all arithmetic on channel PAIRS (float2): FFMA2 / FMUL2 / FADD2 halve the issue slots of this
   // instruction-bound kernel (~40 instructions per element before)
-  float2 wt[2][W], bs[2], dwa[2][W], dba[2];
+  float2 wt[NP][W], bs[NP], dwa[NP][W], dba[NP];
 #pragma unroll
-  for (int j = 0; j < 2; ++j) {
+  for (int j = 0; j < NP; ++j) {
 #pragma unroll
     for (int k = 0; k < W; ++k) {
       wt[j][k] = f2(w[(c0 + 2 * j) * W + k], w[(c0 + 2 * j + 1) * W + k]);
@@ -180,19 +183,27 @@ conv1d_bwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __rest
   // Branch-free: out-of-range rows read a clamped (valid) row and are zeroed by a multiply, so the
   // compiler can issue a batch's loads back to back (a conditional load ends the basic block and
   // each load would then pay its full latency in turn — ncu: 67 % long-scoreboard stalls).
-  auto load_x = [&](int t, float2* f) {
-    const int tc = min(max(t, 0), T - 1);
-    const bf16x4 p = ld4(xb + (size_t)tc * ldx);
-    const float m = (t >= 0 && t < T) ? 1.f : 0.f;
-    f[0] = mul2(__bfloat1622float2(p.v[0]), f2(m, m));
-    f[1] = mul2(__bfloat1622float2(p.v[1]), f2(m, m));
+  // `edge` (a compile-time tag): batches that cannot touch a sequence / tile boundary skip the clamps and masks
+  auto load_x = [&](int t, float2* f, auto edge) {
+    constexpr bool E = decltype(edge)::value;
+    const int tc = E ? min(max(t, 0), T - 1) : t;
+    const float m = (!E || (t >= 0 && t < T)) ? 1.f : 0.f;
+    if (NP == 2) {
+      const bf16x4 p = ld4(xb + (size_t)tc * ldx);
+      f[0] = mul2(__bfloat1622float2(p.v[0]), f2(m, m));
+      f[NP - 1] = mul2(__bfloat1622float2(p.v[1]), f2(m, m));
+    } else {
+      const bf162 p = *reinterpret_cast<const bf162*>(xb + (size_t)tc * ldx);
+      f[0] = mul2(__bfloat1622float2(p), f2(m, m));
+    }
   };
   // g[t] = dy[t] * silu'(pre[t]) from the W x-rows ending at t; also this token's dw / db terms
-  auto make_g = [&](int t, const float2 (*xw)[2], const float2* d2, float2* g) {  // xw[k] = x[t - H + k]
-    const float live = t < T ? 1.f : 0.f, own = t < t1 ? 1.f : 0.f;
+  auto make_g = [&](int t, const float2 (*xw)[NP], const float2* d2, float2* g, auto edge) {  // xw[k] = x[t - H + k]
+    constexpr bool E = decltype(edge)::value;
+    const float live = (!E || t < T) ? 1.f : 0.f, own = (!E || t < t1) ? 1.f : 0.f;
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      float2 gg = mul2(d2[j], f2(live, live));
+    for (int j = 0; j < NP; ++j) {
+      float2 gg = E ? mul2(d2[j], f2(live, live)) : d2[j];
       if (SILU) {
         float2 a = bs[j];
 #pragma unroll
@@ -202,75 +213,90 @@ conv1d_bwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __rest
         gg = mul2(gg, dsv);
       }
       g[j] = gg;
-      const float2 go = mul2(gg, f2(own, own));  // only the tile that owns token t accumulates its dw / db terms
+      const float2 go = E ? mul2(gg, f2(own, own)) : gg;  // only the tile that owns token t accumulates its dw / db terms
       dba[j] = add2(dba[j], go);
 #pragma unroll
       for (int k = 0; k < W; ++k) dwa[j][k] = fma2(go, xw[k][j], dwa[j][k]);
     }
   };
-  auto load_dy = [&](int t, float2* f) {
-    const bf16x4 p = ld4(gb + (size_t)min(t, T - 1) * lddy);
-    f[0] = __bfloat1622float2(p.v[0]);
-    f[1] = __bfloat1622float2(p.v[1]);
+  auto load_dy = [&](int t, float2* f, auto edge) {
+    const int tc = decltype(edge)::value ? min(t, T - 1) : t;
+    if (NP == 2) {
+      const bf16x4 p = ld4(gb + (size_t)tc * lddy);
+      f[0] = __bfloat1622float2(p.v[0]);
+      f[NP - 1] = __bfloat1622float2(p.v[1]);
+    } else {
+      f[0] = __bfloat1622float2(*reinterpret_cast<const bf162*>(gb + (size_t)tc * lddy));
+    }
   };
+  ConvEdgeTag<true> edge_t;
+  ConvEdgeTag<false> inner_t;
 
   // rows carried between batches: xr[0..H) = x[tb .. tb+H), gr[0..H) = g[tb .. tb+H)
-  float2 xr[H + U][2], gr[H + U][2];
+  float2 xr[H + U][NP], gr[H + U][NP];
   {
-    float2 xp[2 * H][2];  // x[t0-H .. t0+H)
+    float2 xp[2 * H][NP];  // x[t0-H .. t0+H)
 #pragma unroll
-    for (int i = 0; i < 2 * H; ++i) load_x(t0 - H + i, xp[i]);
+    for (int i = 0; i < 2 * H; ++i) load_x(t0 - H + i, xp[i], edge_t);
 #pragma unroll
     for (int i = 0; i < H; ++i) {
-      float2 xw[W][2];
+      float2 xw[W][NP];
 #pragma unroll
       for (int k = 0; k < W; ++k)
 #pragma unroll
-        for (int jj = 0; jj < 2; ++jj) xw[k][jj] = xp[i + k][jj];
-      float2 d2[2];
-      load_dy(t0 + i, d2);
-      make_g(t0 + i, xw, d2, gr[i]);
+        for (int jj = 0; jj < NP; ++jj) xw[k][jj] = xp[i + k][jj];
+      float2 d2[NP];
+      load_dy(t0 + i, d2, edge_t);
+      make_g(t0 + i, xw, d2, gr[i], edge_t);
 #pragma unroll
-      for (int jj = 0; jj < 2; ++jj) xr[i][jj] = xp[H + i][jj];
+      for (int jj = 0; jj < NP; ++jj) xr[i][jj] = xp[H + i][jj];
     }
   }
   for (int tb = t0; tb < t1; tb += U) {
     // new rows: tokens tb+H .. tb+H+U-1
-    float2 dyb[U][2];
+    float2 dyb[U][NP];
+    auto batch = [&](auto edge) {
 #pragma unroll
-    for (int u = 0; u < U; ++u) { load_x(tb + H + u, xr[H + u]); load_dy(tb + H + u, dyb[u]); }
+      for (int u = 0; u < U; ++u) { load_x(tb + H + u, xr[H + u], edge); load_dy(tb + H + u, dyb[u], edge); }
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      float2 xw[W][2];
+      for (int u = 0; u < U; ++u) {
+        float2 xw[W][NP];
 #pragma unroll
-      for (int k = 0; k < W; ++k)
+        for (int k = 0; k < W; ++k)
 #pragma unroll
-        for (int jj = 0; jj < 2; ++jj) xw[k][jj] = xr[u + k][jj];  // x[(tb+H+u) - H + k] = x[tb + u + k]
-      make_g(tb + H + u, xw, dyb[u], gr[H + u]);
-    }
+          for (int jj = 0; jj < NP; ++jj) xw[k][jj] = xr[u + k][jj];  // x[(tb+H+u) - H + k] = x[tb + u + k]
+        make_g(tb + H + u, xw, dyb[u], gr[H + u], edge);
+      }
+    };
+    if (tb + H + U <= t1) batch(inner_t);   // every token of the batch is inside this tile (hence inside the sequence)
+    else batch(edge_t);
     // dx[tb+u] = sum_k w[k] * g[tb+u + H - k]
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       if (tb + u < t1) {
-        float2 o[2];
+        float2 o[NP];
 #pragma unroll
-        for (int jj = 0; jj < 2; ++jj) {
+        for (int jj = 0; jj < NP; ++jj) {
           float2 a = mul2(wt[jj][0], gr[u + H][jj]);
 #pragma unroll
           for (int k = 1; k < W; ++k) a = fma2(wt[jj][k], gr[u + H - k][jj], a);
           o[jj] = a;
         }
-        const float of[4] = {o[0].x, o[0].y, o[1].x, o[1].y};
-        st4(dxb + (size_t)(tb + u) * lddx, of);
+        if (NP == 2) {
+          const float of[4] = {o[0].x, o[0].y, o[NP - 1].x, o[NP - 1].y};
+          st4(dxb + (size_t)(tb + u) * lddx, of);
+        } else {
+          *reinterpret_cast<bf162*>(dxb + (size_t)(tb + u) * lddx) = __floats2bfloat162_rn(o[0].x, o[0].y);
+        }
       }
     }
 #pragma unroll
     for (int i = 0; i < H; ++i)
 #pragma unroll
-      for (int jj = 0; jj < 2; ++jj) { xr[i][jj] = xr[U + i][jj]; gr[i][jj] = gr[U + i][jj]; }
+      for (int jj = 0; jj < NP; ++jj) { xr[i][jj] = xr[U + i][jj]; gr[i][jj] = gr[U + i][jj]; }
   }
 #pragma unroll
-  for (int jj = 0; jj < 2; ++jj) {
+  for (int jj = 0; jj < NP; ++jj) {
 #pragma unroll
     for (int k = 0; k < W; ++k) {
       atomicAdd(dw + (c0 + 2 * jj) * W + k, dwa[jj][k].x);
@@ -300,6 +326,8 @@ __global__ void conv1d_update_kernel(const bf16* __restrict__ x, long long ldx, 
 }  // namespace mb
 
 using namespace mb;
+
+constexpr int kBwdNP = 2;  // channel pairs per backward thread (1 = more occupancy, measured no faster: issue-bound)
 
 // Token-tile length: the largest number of tiles per sequence (>= 64 tokens each) whose block count still
 // fills whole waves of resident blocks -- a grid of 1.7 waves runs as long as one of 2.
@@ -356,12 +384,12 @@ extern "C" int mb_conv1d_bwd(const void* x, long long ldx, const float* w, const
   DISPATCH_W(width, silu, {
     static int per_sm = 0;
     if (per_sm == 0) {
-      MB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, conv1d_bwd_kernel<W, S>, kConvThreads, 0));
+      MB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, conv1d_bwd_kernel<W, S, kBwdNP>, kConvThreads, 0));
       if (per_sm < 1) per_sm = 1;
     }
-    const int tile = conv_tile(cdiv(C / 4, kConvThreads), B, T, per_sm);
-    dim3 grid(cdiv(C / 4, kConvThreads), cdiv(T, tile), B);
-    conv1d_bwd_kernel<W, S><<<grid, kConvThreads, 0, stream>>>((const bf16*)x, ldx, w, bias, (const bf16*)dy, lddy,
+    const int tile = conv_tile(cdiv(C / (2 * kBwdNP), kConvThreads), B, T, per_sm);
+    dim3 grid(cdiv(C / (2 * kBwdNP), kConvThreads), cdiv(T, tile), B);
+    conv1d_bwd_kernel<W, S, kBwdNP><<<grid, kConvThreads, 0, stream>>>((const bf16*)x, ldx, w, bias, (const bf16*)dy, lddy,
                                                                (bf16*)dx, lddx, dw, dbias, T, C, tile);
   });
   return check_launch("conv1d_bwd");
