@@ -45,14 +45,14 @@ __device__ __forceinline__ void decode_tile(int tile, int tiles_m, int tiles_n, 
 
 enum { EPI_BF16 = 0, EPI_F32 = 1, EPI_F32_ATOMIC = 2 };
 
-enum { MODE_SINGLE = 0, MODE_MULTICAST = 1, MODE_PAIR = 2 };
+enum { MODE_SINGLE = 0, MODE_MULTICAST = 1, MODE_PAIR = 2, MODE_QUAD = 3 };
 
 template <int BN, int MODE = MODE_SINGLE>
 struct GemmCfg {
   // MODE_PAIR: each CTA of the pair keeps only its half of the B tile, which buys two more stages
-  static constexpr int STAGES = MODE == MODE_PAIR ? 6 : (BN == 256 ? 4 : 6);
+  static constexpr int STAGES = MODE >= MODE_PAIR ? 6 : (BN == 256 ? 4 : 6);
   static constexpr int A_BYTES = BM * BK * 2;
-  static constexpr int B_BYTES = (MODE == MODE_PAIR ? BN / 2 : BN) * BK * 2;
+  static constexpr int B_BYTES = (MODE >= MODE_PAIR ? BN / 2 : BN) * BK * 2;
   static constexpr int STAGING = 4 * 2 * 4096;  // 4 epilogue warps x 2 buffers x [32 rows][128 B]
   static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + STAGING + 1024 /*align slack*/ + 256 /*barriers*/;
 };
@@ -76,8 +76,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                  long long ldd, int splitk, int kb_per_split, float alpha) {
   using Cfg = GemmCfg<BN, MODE>;
   constexpr int STAGES = Cfg::STAGES;
-  constexpr bool MC = MODE != MODE_SINGLE;   // launched as clusters of 2 that share an N block
-  constexpr bool PAIR = MODE == MODE_PAIR;
+  constexpr bool MC = MODE != MODE_SINGLE;   // launched as clusters that share an N block
+  constexpr bool PAIR = MODE >= MODE_PAIR;   // cta_group::2 MMA
+  // MODE_QUAD: clusters of 4 = two CTA pairs on vertically adjacent 256-row tiles of the same N block.  The two
+  // CTAs that hold the same half of the B tile (one per pair) each fetch half of it and multicast it to both:
+  // 24 KB instead of 32 KB per k-block per SM out of L2 (the mainloop was waiting on the TMA full barriers).
+  constexpr bool QUAD = MODE == MODE_QUAD;
+  constexpr int CL = QUAD ? 4 : (MC ? 2 : 1);
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
@@ -93,19 +98,21 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tiles_m_real = (Mg + BM - 1) / BM, tiles_n = (Ng + BN - 1) / BN;
   // with MC the scheduler hands out PAIRS of M blocks to a cluster; CTA `crank` takes block 2*pm + crank
-  const int tiles_m = MC ? (tiles_m_real + 1) / 2 : tiles_m_real;
+  const int tiles_m = (tiles_m_real + CL - 1) / CL;
   const int num_tiles = tiles_m * tiles_n * splitk;
   const int kblocks = (Kg + BK - 1) / BK;
   const int crank = MC ? (int)cluster_ctarank() : 0;
-  const int worker = MC ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
-  const int nworkers = MC ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int worker = (int)blockIdx.x / CL;
+  const int nworkers = (int)gridDim.x / CL;
+  const int pair = crank >> 1, qpos = crank & 1;          // which pair of the cluster, position inside the pair
+  const uint16_t pair_mask = (uint16_t)(0b11 << (2 * pair));
 
   if (warp == 0 && lane == 0) {
     prefetch_tensormap(&tmA);
     prefetch_tensormap(&tmB);
     if (TMA_STORE) prefetch_tensormap(&tmD);
     // multicast: a stage is free once BOTH CTAs' MMAs released it; pair: one (multicast) commit per CTA
-    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], (MC && !PAIR) ? 2 : 1); }
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], ((MC && !PAIR) || QUAD) ? 2 : 1); }
     // pair: the issuing CTA waits for the epilogue warps of both CTAs before it reuses an accumulator
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], PAIR ? 8 : 4); }
     fence_mbar_init();
@@ -128,7 +135,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       for (int tile = worker; tile < num_tiles; tile += nworkers) {
         int m_blk, n_blk, split;
         decode_tile(tile, tiles_m, tiles_n, m_blk, n_blk, split);
-        if (MC) m_blk = 2 * m_blk + crank;
+        if (MC) m_blk = CL * m_blk + crank;
         const int kb0 = split * kb_per_split;
         const int kb1 = min(kb0 + kb_per_split, kblocks);
         for (int kb = kb0; kb < kb1; ++kb) {
@@ -137,7 +144,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           uint8_t* b_dst = sB + stage * Cfg::B_BYTES;
           if (PAIR) {
             // both CTAs' loads complete on the even CTA's barrier, which expects the bytes of both
-            if (crank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * (Cfg::A_BYTES + Cfg::B_BYTES));
+            if (qpos == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * (Cfg::A_BYTES + Cfg::B_BYTES));
             if (A_MAJOR == MAJOR_K) {
               tma_load_2d_pair(a_dst, &tmA, &full_bar[stage], kb * BK, m_blk * BM);
             } else {
@@ -145,7 +152,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               for (int j = 0; j < BM / 64; ++j)
                 tma_load_2d_pair(a_dst + j * (BK * 128), &tmA, &full_bar[stage], m_blk * BM + j * 64, kb * BK);
             }
-            if (B_MAJOR == MAJOR_K) {  // tmB here is the half-height (BN/2 rows) box
+            if (QUAD) {
+              // half `qpos` of the B tile is shared with the CTA at the same position of the other pair: each of the
+              // two fetches one quarter of the tile (64 rows / one 64-column atom) and multicasts it to both
+              const uint16_t m2 = (uint16_t)((1u << qpos) | (1u << (qpos + 2)));
+              if (B_MAJOR == MAJOR_K)   // tmB here is the quarter-height (BN/4 rows) box
+                tma_load_2d_pair_mc(b_dst + pair * (BN / 4) * 128, &tmB, &full_bar[stage], kb * BK,
+                                    n_blk * BN + qpos * (BN / 2) + pair * (BN / 4), m2);
+              else
+                tma_load_2d_pair_mc(b_dst + pair * (BK * 128), &tmB, &full_bar[stage],
+                                    n_blk * BN + (qpos * (BN / 128) + pair) * 64, kb * BK, m2);
+            } else if (B_MAJOR == MAJOR_K) {  // tmB here is the half-height (BN/2 rows) box
               tma_load_2d_pair(b_dst, &tmB, &full_bar[stage], kb * BK, n_blk * BN + crank * (BN / 2));
             } else {
 #pragma unroll
@@ -191,7 +208,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ========================================
-    if (lane == 0 && (!PAIR || crank == 0)) {
+    if (lane == 0 && (!PAIR || qpos == 0)) {
       constexpr uint32_t idesc = make_idesc_bf16(PAIR ? 2 * BM : BM, BN, A_MAJOR, B_MAJOR);
       // K-major: +32 B per UMMA_K inside the swizzle row; MN-major: +16 k-rows * 128 B
       constexpr uint32_t a_kstep = A_MAJOR == MAJOR_K ? 32 : 16 * 128;
@@ -237,13 +254,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
           // frees this smem stage when the MMAs above retire (in BOTH CTAs with MC: the peer's
           // producer multicasts into our stage too; with PAIR the MMA itself read both CTAs' stage)
-          if (PAIR) mma_commit_pair_mc(&empty_bar[stage], 0b11);
+          if (QUAD) mma_commit_pair_mc(&empty_bar[stage], 0b1111);   // the other pair's producers write into our stage too
+          else if (PAIR) mma_commit_pair_mc(&empty_bar[stage], 0b11);
           else if (MC) mma_commit_mc(&empty_bar[stage], 0b11);
           else mma_commit(&empty_bar[stage]);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
         // accumulator complete -> epilogue (of both CTAs with PAIR)
-        if (PAIR) mma_commit_pair_mc(&tfull_bar[acc], 0b11); else mma_commit(&tfull_bar[acc]);
+        if (PAIR) mma_commit_pair_mc(&tfull_bar[acc], pair_mask); else mma_commit(&tfull_bar[acc]);
 #ifdef MB_GEMM_TIMING
         if (blockIdx.x == 4 && local < 30)
           printf("G tile %d start %lld wait_acc %lld wait_full %lld issue_total %lld\n", local, tt0, tt1 - tt0, twait_full, clock64() - tt0);
@@ -258,7 +276,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int tile = worker; tile < num_tiles; tile += nworkers, ++local) {
       int m_blk, n_blk, split_unused;
       decode_tile(tile, tiles_m, tiles_n, m_blk, n_blk, split_unused);
-      if (MC) m_blk = 2 * m_blk + crank;
+      if (MC) m_blk = CL * m_blk + crank;
       const int acc = local & 1;
       const uint32_t acc_phase = (local >> 1) & 1;
       mbar_wait(&tfull_bar[acc], acc_phase);
@@ -364,7 +382,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       tc_fence_before();
       __syncwarp();
       if (lane == 0) {
-        if (PAIR && crank != 0) mbar_arrive_cluster(&tempty_bar[acc], 0);  // the issuing (even) CTA owns the wait
+        if (PAIR && qpos != 0) mbar_arrive_cluster(&tempty_bar[acc], 2 * pair);  // the issuing (even) CTA owns the wait
         else mbar_arrive(&tempty_bar[acc]);
       }
     }
@@ -456,15 +474,16 @@ static int launch_gemm_mc(const CUtensorMap& ta, const CUtensorMap& tb, const CU
                           const float* bias, int M, int N, int K, long long ldd, int splitk, int kb_per_split,
                           float alpha, cudaStream_t stream) {
   constexpr bool MC = MODE != MODE_SINGLE;
+  constexpr int CL = MODE == MODE_QUAD ? 4 : (MC ? 2 : 1);
   auto kern = gemm_bf16_kernel<BN, AM, BMJ, EPI, TS, MODE>;
   static bool attr_set = false;
   if (!attr_set) {
     MB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<BN, MODE>::SMEM));
     attr_set = true;
   }
-  const int tiles_m = MC ? (cdiv(M, BM) + 1) / 2 : cdiv(M, BM);
-  const int tiles = tiles_m * cdiv(N, BN) * splitk;       // pairs of tiles when MC
-  int grid = MC ? 2 * (tiles < num_sms() / 2 ? tiles : num_sms() / 2) : (tiles < num_sms() ? tiles : num_sms());
+  const int tiles_m = (cdiv(M, BM) + CL - 1) / CL;
+  const int tiles = tiles_m * cdiv(N, BN) * splitk;       // groups of CL vertically adjacent tiles
+  int grid = CL * (tiles < num_sms() / CL ? tiles : num_sms() / CL);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(kGemmThreads);
@@ -472,11 +491,23 @@ static int launch_gemm_mc(const CUtensorMap& ta, const CUtensorMap& tb, const CU
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = MC ? 2 : 1;
+  attr[0].val.clusterDim.x = CL;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
+  if (CL == 4) {
+    // clusters of 4 do not tile every GPC exactly: size the persistent grid by what can be co-resident
+    static int max_clusters = 0;
+    if (max_clusters == 0) {
+      cfg.gridDim = dim3(num_sms() / CL * CL);
+      MB_CUDA(cudaOccupancyMaxActiveClusters(&max_clusters, kern, &cfg));
+      if (max_clusters < 1) max_clusters = 1;
+      if (getenv("MAMBA_B200_GEMM_DEBUG")) fprintf(stderr, "gemm: %d clusters of 4 can be co-resident\n", max_clusters);
+    }
+    grid = CL * (tiles < max_clusters ? tiles : max_clusters);
+    cfg.gridDim = dim3(grid);
+  }
   MB_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha));
   return check_launch("gemm_bf16");
 }
@@ -493,10 +524,20 @@ static bool use_pair() {
   return v == 1;
 }
 
+static bool use_quad() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("MAMBA_B200_GEMM_QUAD"); v = (e != nullptr && e[0] == '1') ? 1 : 0; }
+  return v == 1;
+}
+// quarter-height box of the K-major B tile (MODE_QUAD); set by mb_gemm_bf16 right before the dispatch
+static thread_local CUtensorMap g_tb_quarter;
+
 template <int BN, uint32_t AM, uint32_t BMJ, int EPI, bool TS>
 static int launch_gemm_ts(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tb_half, const CUtensorMap& td,
                           void* D, const float* bias, int M, int N, int K, long long ldd, int splitk, int kb_per_split,
                           float alpha, cudaStream_t stream) {
+  if (BN == 256 && use_quad() && cdiv(M, BM) >= 4 && num_sms() % 4 == 0)
+    return launch_gemm_mc<256, AM, BMJ, EPI, TS, MODE_QUAD>(ta, g_tb_quarter, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha, stream);
   if (BN == 256 && use_pair() && cdiv(M, BM) >= 2)
     return launch_gemm_mc<256, AM, BMJ, EPI, TS, MODE_PAIR>(ta, tb_half, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha, stream);
   if (use_multicast() && cdiv(M, BM) >= 2)
@@ -555,6 +596,8 @@ extern "C" int mb_gemm_bf16(const void* A, long long lda, int a_major, const voi
   // half-height box of the K-major B tile for the multicast path (MN-major boxes are per 64-wide atom already)
   if (b_major == 0) { if (make_tmap_bf16_2d(&tbh, B, N, K, ldb, BN / 2)) return 1; }
   else tbh = tb;
+  if (b_major == 0) { if (make_tmap_bf16_2d(&g_tb_quarter, B, N, K, ldb, BN / 4)) return 1; }
+  else g_tb_quarter = tb;
   // split-K only where the epilogue is additive.  The persistent grid runs whole waves of work units
   // (tile pairs x splits when two CTAs share a tile column), so pick the split count that minimises
   // waves x (k-blocks per split + the cost of one more additive epilogue), not just "enough units".
@@ -562,8 +605,10 @@ extern "C" int mb_gemm_bf16(const void* A, long long lda, int a_major, const voi
   int splitk = 1;
   if (d_mode == 2) {
     const bool paired = cdiv(M, BM) >= 2 && (use_multicast() || (BN == 256 && use_pair()));
-    const long long units = (long long)(paired ? (cdiv(M, BM) + 1) / 2 : cdiv(M, BM)) * cdiv(N, BN);
-    const int workers = paired ? num_sms() / 2 : num_sms();
+    const bool quad = BN == 256 && use_quad() && cdiv(M, BM) >= 4 && num_sms() % 4 == 0;
+    const int cl = quad ? 4 : (paired ? 2 : 1);
+    const long long units = (long long)((cdiv(M, BM) + cl - 1) / cl) * cdiv(N, BN);
+    const int workers = num_sms() / cl;
     int max_split = kblocks / 8;  // keep >= 8 k-blocks (512 deep) per split
     if (max_split < 1) max_split = 1;
     if (max_split > 64) max_split = 64;
