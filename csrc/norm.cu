@@ -180,33 +180,39 @@ gated_rmsnorm_fwd_kernel(const bf16* __restrict__ x, int ldx, const bf16* __rest
   if (row >= M * G) return;
   const int m = row / G, g = row - m * G;
   const int nvec = gs >> 3;
-  float v[NV][8];
-  float ss = 0.f;
+  float2 v[NV][4];   // column pairs: FMUL2 / FFMA2
+  float2 ss2 = f2(0.f, 0.f);
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
     const int vec = lane + 32 * i;
     if (vec < nvec) {
       const int col = g * gs + vec * 8;
-      float zz[8];
-      unpack8(ld8(x + (size_t)m * ldx + col), v[i]);
-      unpack8(ld8(z + (size_t)m * ldz + col), zz);
+      const bf16x8 px = ld8(x + (size_t)m * ldx + col), pz = ld8(z + (size_t)m * ldz + col);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) { v[i][j] *= silu_f(zz[j]); ss += v[i][j] * v[i][j]; }
+      for (int j = 0; j < 4; ++j) {
+        v[i][j] = mul2(__bfloat1622float2(px.v[j]), silu2(__bfloat1622float2(pz.v[j])));
+        ss2 = fma2(v[i][j], v[i][j], ss2);
+      }
     }
   }
-  ss = warp_sum(ss);
+  const float ss = warp_sum(ss2.x + ss2.y);
   const float rstd = rsqrtf(ss / (float)gs + eps);
   if (lane == 0) rstd_out[row] = rstd;
+  const float2 rs2 = f2(rstd, rstd);
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
     const int vec = lane + 32 * i;
     if (vec < nvec) {
       const int col = g * gs + vec * 8;
-      float w[8], o[8];
-      ld8f(weight + col, w);
+      const float4 w0 = *reinterpret_cast<const float4*>(weight + col), w1 = *reinterpret_cast<const float4*>(weight + col + 4);
+      const float2 w[4] = {f2(w0.x, w0.y), f2(w0.z, w0.w), f2(w1.x, w1.y), f2(w1.z, w1.w)};
+      bf16x8 o;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) o[j] = v[i][j] * rstd * w[j];
-      st8(out + (size_t)m * ldo + col, pack8(o));
+      for (int j = 0; j < 4; ++j) {
+        const float2 r = mul2(mul2(v[i][j], rs2), w[j]);
+        o.v[j] = __floats2bfloat162_rn(r.x, r.y);
+      }
+      st8(out + (size_t)m * ldo + col, o);
     }
   }
 }

@@ -24,7 +24,7 @@ constexpr int kOuterSmem = 2 * (kOuterHalf * 2 * 128) + 2 * kL * 4 + 64 + 1024;
 
 template <bool DSTATE>
 __global__ void __launch_bounds__(kThreads, 3)
-ssd_outer_kernel(const bf16* __restrict__ arow, long long lda, const bf16* __restrict__ bop, long long ldb,
+ssd_outer_kernel(const bf16* __restrict__ arow, long long lda, const __grid_constant__ CUtensorMap tmBop,
                  const float* __restrict__ dtv, const float* __restrict__ av, const __grid_constant__ CUtensorMap tmOut,
                  int T, int H, int G, int nc, int hpc) {
   extern __shared__ uint8_t smem_raw[];
@@ -33,7 +33,8 @@ ssd_outer_kernel(const bf16* __restrict__ arow, long long lda, const bf16* __res
   uint8_t* sB = smem + kOuterHalf * 2 * 128;         // [128 k-rows][2 atoms]  MN-major B
   float* s_scale = reinterpret_cast<float*>(smem + 2 * kOuterHalf * 2 * 128);  // [2][256]
   uint64_t* bar = reinterpret_cast<uint64_t*>(s_scale + 2 * kL);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 1);
+  uint64_t* ld_bar = bar + 1;   // TMA transaction barrier of the B / C operand tile
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 2);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int bc = blockIdx.x;
@@ -42,7 +43,7 @@ ssd_outer_kernel(const bf16* __restrict__ arow, long long lda, const bf16* __res
   const int g = h0 / (H / G);
   const int valid = min(kL, T - c * kL);
 
-  if (tid == 0) { mbar_init(bar, 1); fence_mbar_init(); }
+  if (tid == 0) { mbar_init(bar, 1); mbar_init(ld_bar, 1); fence_mbar_init(); }
   if (warp == 0) { tmem_alloc(tmem_slot, 128); tmem_relinquish(); }
   for (int idx = tid; idx < hpc * kL; idx += kThreads) {
     const int hh = idx / kL, t = idx % kL;
@@ -60,14 +61,17 @@ ssd_outer_kernel(const bf16* __restrict__ arow, long long lda, const bf16* __res
     const int k0 = half * kOuterHalf;
     const int v = max(0, min(kOuterHalf, valid - k0));
     auto scale = [&](int row, int blk) { return s_scale[blk * kL + k0 + row]; };
-    load_tile<2, false>(sB, bop + (row0 + k0) * ldb + g * kN, ldb, kOuterHalf, v, NoScale(), tid, kThreads);  // async
-    cp_async_commit();
+    if (tid == 0) {  // B / C rows of this half by TMA (two 64-column atoms); rows past the sequence end read as zeros
+      mbar_arrive_expect_tx(ld_bar, kOuterHalf * 2 * 128);
+      for (int j2 = 0; j2 < 2; ++j2)
+        tma_load_3d(sB + j2 * kOuterHalf * 128, &tmBop, ld_bar, g * kN + j2 * 64, c * kL + k0, b);
+    }
     if (hpc == 2) load_tile<2, true>(sA, arow + (row0 + k0) * lda + h0 * kP, lda, kOuterHalf, v, scale, tid, kThreads);
     else load_tile<1, true>(sA, arow + (row0 + k0) * lda + h0 * kP, lda, kOuterHalf, v, scale, tid, kThreads);
-    cp_async_wait<0>();
     fence_proxy_async_smem();
     __syncthreads();
     if (tid == 0) {
+      mbar_wait(ld_bar, half & 1);
       tc_fence_after();
       constexpr uint32_t idesc = make_idesc_bf16(128, kN, MAJOR_MN, MAJOR_MN);
       const uint32_t a_addr = smem_u32(sA), b_addr = smem_u32(sB);
@@ -607,16 +611,17 @@ extern "C" int mb_ssd_chunk_state(const void* arow, long long lda, const void* b
   const int nc = cdiv(T, L);
   const int hpc = ((H / G) % 2 == 0) ? 2 : 1;
   dim3 grid(B * nc, H / hpc);
-  CUtensorMap tmOut;
-  if (make_tmap_f32_2d(&tmOut, out, (long long)B * nc * H * P, N, N)) return 1;
+  CUtensorMap tmOut, tmBop;
+  if (make_tmap_f32_2d(&tmOut, out, (long long)B * nc * H * P, N, N) ||
+      make_tmap_bf16_3d(&tmBop, bop, B, T, (long long)G * N, ldb, kOuterHalf, 64)) return 1;
   if (dstate) {
     static bool once = false;
     if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_outer_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kOuterSmem)); once = true; }
-    ssd_outer_kernel<true><<<grid, kThreads, kOuterSmem, stream>>>((const bf16*)arow, lda, (const bf16*)bop, ldb, dt, a, tmOut, T, H, G, nc, hpc);
+    ssd_outer_kernel<true><<<grid, kThreads, kOuterSmem, stream>>>((const bf16*)arow, lda, tmBop, dt, a, tmOut, T, H, G, nc, hpc);
   } else {
     static bool once = false;
     if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_outer_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kOuterSmem)); once = true; }
-    ssd_outer_kernel<false><<<grid, kThreads, kOuterSmem, stream>>>((const bf16*)arow, lda, (const bf16*)bop, ldb, dt, a, tmOut, T, H, G, nc, hpc);
+    ssd_outer_kernel<false><<<grid, kThreads, kOuterSmem, stream>>>((const bf16*)arow, lda, tmBop, dt, a, tmOut, T, H, G, nc, hpc);
   }
   return check_launch("ssd_chunk_state");
 }
