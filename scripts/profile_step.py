@@ -9,7 +9,7 @@ from model import LMHeadModel
 
 B = int(os.environ.get("B", 32)); T = int(os.environ.get("T", 1024))
 torch.manual_seed(0)
-model = LMHeadModel(preset(os.environ.get("PRESET", "280m")), "cuda").cuda()
+model = LMHeadModel(preset(os.environ.get("PRESET", "280m"), layer=os.environ.get("LAYER", "Mamba2")), "cuda").cuda()
 ddp = FusedDDP(model)
 opt = model.configure_optimizers(0.1, 6e-4, "cuda", False, fused_comm=ddp)
 x = torch.randint(0, 50304, (B, T), device="cuda"); y = torch.randint(0, 50304, (B, T), device="cuda")
