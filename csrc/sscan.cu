@@ -43,26 +43,58 @@ __device__ __forceinline__ float half_warp_sum(float v) {
   return v;
 }
 
+// Per-token inputs of one (batch, tile, 8-channel block), staged in shared memory so that the 64-step
+// recurrences below never wait on global memory inside the loop (dt = 0 / u = 0 pad the ragged end: the
+// state then just carries through).
+struct SScanTile {
+  float dt[kSTile][kSChan], u[kSTile][kSChan];
+  float B[kSTile][kSN], C[kSTile][kSN];
+};
+__device__ __forceinline__ void sscan_stage(const SScanArgs& a, SScanTile& s, int b, int t0, int nt, int d0,
+                                            bool want_u, bool want_b, bool want_c) {
+  for (int idx = threadIdx.x; idx < kSTile * kSChan; idx += blockDim.x) {
+    const int i = idx / kSChan, cch = idx % kSChan, dch = d0 + cch;
+    float dt = 0.f, uu = 0.f;
+    if (i < nt && dch < a.Dn) {
+      const size_t row = (size_t)b * a.T + t0 + i;
+      dt = __bfloat162float(a.delta[row * a.ldd + dch]) + (a.delta_bias ? a.delta_bias[dch] : 0.f);
+      if (a.softplus) dt = softplus_f(dt);
+      if (want_u) uu = __bfloat162float(a.u[row * a.ldu + dch]);
+    }
+    s.dt[i][cch] = dt; s.u[i][cch] = uu;
+  }
+  for (int idx = threadIdx.x; idx < kSTile * kSN; idx += blockDim.x) {
+    const int i = idx / kSN, nn = idx % kSN;
+    float bv = 0.f, cv = 0.f;
+    if (i < nt) {
+      const size_t row = (size_t)b * a.T + t0 + i;
+      if (want_b) bv = __bfloat162float(a.Bm[row * a.ldb + nn]);
+      if (want_c) cv = __bfloat162float(a.Cm[row * a.ldc + nn]);
+    }
+    s.B[i][nn] = bv; s.C[i][nn] = cv;
+  }
+}
+
 // pass 1: per (b, tile, d, n): P = prod_t exp(dt_t A), S = local end state from zero
 __global__ void __launch_bounds__(kSChan * kSN)
 sscan_local_kernel(SScanArgs a, float* __restrict__ P, float* __restrict__ S) {
-  const int n = threadIdx.x & (kSN - 1), dl = threadIdx.x >> 4;
-  const int d = blockIdx.x * kSChan + dl;
+  __shared__ SScanTile st;
   const int tile = blockIdx.y, b = blockIdx.z;
+  const int t0 = tile * kSTile, nt = min(t0 + kSTile, a.T) - t0;
+  const int d0 = blockIdx.x * kSChan;
+  sscan_stage(a, st, b, t0, nt, d0, true, true, false);
+  __syncthreads();
+  const int n = threadIdx.x & (kSN - 1), dl = threadIdx.x >> 4;
+  const int d = d0 + dl;
   if (d >= a.Dn) return;
   const float An = a.A[d * kSN + n];
-  const float bias = a.delta_bias ? a.delta_bias[d] : 0.f;
-  const int t0 = tile * kSTile, t1 = min(t0 + kSTile, a.T);
   float h = 0.f, lp = 0.f;
-  for (int t = t0; t < t1; ++t) {
-    const size_t row = (size_t)b * a.T + t;
-    float dt = __bfloat162float(a.delta[row * a.ldd + d]) + bias;
-    if (a.softplus) dt = softplus_f(dt);
-    const float uu = __bfloat162float(a.u[row * a.ldu + d]);
-    const float Bn = __bfloat162float(a.Bm[row * a.ldb + n]);
+#pragma unroll 8
+  for (int i = 0; i < kSTile; ++i) {
+    const float dt = st.dt[i][dl];
     const float la = dt * An;
     lp += la;
-    h = fast_exp(la) * h + dt * Bn * uu;
+    h = fast_exp(la) * h + dt * st.B[i][n] * st.u[i][dl];
   }
   const size_t o = (((size_t)b * a.ntiles + tile) * a.Dn + d) * kSN + n;
   P[o] = lp;  // log of the decay product (kept in log space: no underflow surprises)
@@ -86,29 +118,37 @@ __global__ void sscan_carry_fwd_kernel(const float* __restrict__ P, const float*
 // pass 2: output.  One half-warp per channel, lane = n.
 __global__ void __launch_bounds__(kSChan * kSN)
 sscan_fwd_kernel(SScanArgs a, const float* __restrict__ hin, bf16* __restrict__ y, long long ldy) {
-  const int n = threadIdx.x & (kSN - 1), dl = threadIdx.x >> 4;
-  const int d = blockIdx.x * kSChan + dl;
+  __shared__ SScanTile st;
+  __shared__ float s_g[kSTile][kSChan];   // silu(z) on the way in, y on the way out
   const int tile = blockIdx.y, b = blockIdx.z;
-  if (d >= a.Dn) return;
+  const int t0 = tile * kSTile, nt = min(t0 + kSTile, a.T) - t0;
+  const int d0 = blockIdx.x * kSChan;
+  sscan_stage(a, st, b, t0, nt, d0, true, true, true);
+  for (int idx = threadIdx.x; idx < kSTile * kSChan; idx += blockDim.x) {
+    const int i = idx / kSChan, cch = idx % kSChan, dch = d0 + cch;
+    float gz = 1.f;
+    if (a.z && i < nt && dch < a.Dn) gz = silu_f(__bfloat162float(a.z[((size_t)b * a.T + t0 + i) * a.ldz + dch]));
+    s_g[i][cch] = gz;
+  }
+  __syncthreads();
+  const int n = threadIdx.x & (kSN - 1), dl = threadIdx.x >> 4;
+  const int d_real = d0 + dl;
+  const bool active = d_real < a.Dn;
+  const int d = active ? d_real : 0;
   const float An = a.A[d * kSN + n];
-  const float bias = a.delta_bias ? a.delta_bias[d] : 0.f;
   const float Dd = a.D ? a.D[d] : 0.f;
-  const int t0 = tile * kSTile, t1 = min(t0 + kSTile, a.T);
-  float h = hin[(((size_t)b * a.ntiles + tile) * a.Dn + d) * kSN + n];
-  for (int t = t0; t < t1; ++t) {
-    const size_t row = (size_t)b * a.T + t;
-    float dt = __bfloat162float(a.delta[row * a.ldd + d]) + bias;
-    if (a.softplus) dt = softplus_f(dt);
-    const float uu = __bfloat162float(a.u[row * a.ldu + d]);
-    const float Bn = __bfloat162float(a.Bm[row * a.ldb + n]);
-    const float Cn = __bfloat162float(a.Cm[row * a.ldc + n]);
-    h = fast_exp(dt * An) * h + dt * Bn * uu;
-    float yy = half_warp_sum(Cn * h);
-    if (n == 0) {
-      yy += Dd * uu;
-      if (a.z) yy *= silu_f(__bfloat162float(a.z[row * a.ldz + d]));
-      y[row * ldy + d] = __float2bfloat16(yy);
-    }
+  float h = active ? hin[(((size_t)b * a.ntiles + tile) * a.Dn + d) * kSN + n] : 0.f;
+#pragma unroll 8
+  for (int i = 0; i < kSTile; ++i) {
+    const float dt = st.dt[i][dl], uu = st.u[i][dl];
+    h = fast_exp(dt * An) * h + dt * st.B[i][n] * uu;
+    const float yy = half_warp_sum(st.C[i][n] * h);
+    if (n == 0) s_g[i][dl] = (yy + Dd * uu) * s_g[i][dl];   // only this lane reads / writes the slot
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < nt * kSChan; idx += blockDim.x) {
+    const int i = idx / kSChan, cch = idx % kSChan, dch = d0 + cch;
+    if (dch < a.Dn) y[((size_t)b * a.T + t0 + i) * ldy + dch] = __float2bfloat16(s_g[i][cch]);
   }
 }
 
@@ -118,29 +158,33 @@ sscan_fwd_kernel(SScanArgs a, const float* __restrict__ hin, bf16* __restrict__ 
 __global__ void __launch_bounds__(kSChan * kSN)
 sscan_bwd_local_kernel(SScanArgs a, const bf16* __restrict__ dy, long long lddy, const float* __restrict__ hin,
                        float* __restrict__ Gl) {
-  const int n = threadIdx.x & (kSN - 1), dl = threadIdx.x >> 4;
-  const int d = blockIdx.x * kSChan + dl;
+  __shared__ SScanTile st;                 // u slot holds dyy = dy * silu(z)
   const int tile = blockIdx.y, b = blockIdx.z;
+  const int t0 = tile * kSTile, nt = min(t0 + kSTile, a.T) - t0;
+  const int d0 = blockIdx.x * kSChan;
+  sscan_stage(a, st, b, t0, nt, d0, false, false, true);
+  for (int idx = threadIdx.x; idx < kSTile * kSChan; idx += blockDim.x) {
+    const int i = idx / kSChan, cch = idx % kSChan, dch = d0 + cch;
+    float dyy = 0.f;
+    if (i < nt && dch < a.Dn) {
+      const size_t row = (size_t)b * a.T + t0 + i;
+      dyy = __bfloat162float(dy[row * lddy + dch]);
+      // y = (ssm + D u) * silu(z): the part flowing into the SSM output is dy * silu(z)
+      if (a.z) dyy *= silu_f(__bfloat162float(a.z[row * a.ldz + dch]));
+    }
+    st.u[i][cch] = dyy;
+  }
+  __syncthreads();
+  const int n = threadIdx.x & (kSN - 1), dl = threadIdx.x >> 4;
+  const int d = d0 + dl;
   if (d >= a.Dn) return;
   const float An = a.A[d * kSN + n];
-  const float bias = a.delta_bias ? a.delta_bias[d] : 0.f;
-  const float Dd = a.D ? a.D[d] : 0.f;
-  const int t0 = tile * kSTile, t1 = min(t0 + kSTile, a.T);
   // gradient w.r.t. the state *entering* the tile, from the tile's own outputs only
-  float g = 0.f;  // dL/dh_t accumulated right-to-left
-  for (int t = t1 - 1; t >= t0; --t) {
-    const size_t row = (size_t)b * a.T + t;
-    float dt = __bfloat162float(a.delta[row * a.ldd + d]) + bias;
-    if (a.softplus) dt = softplus_f(dt);
-    float dyy = __bfloat162float(dy[row * lddy + d]);
-    if (a.z) {
-      // y = (ssm + D u) * silu(z): the part flowing into the SSM output is dy * silu(z)
-      dyy *= silu_f(__bfloat162float(a.z[row * a.ldz + d]));
-    }
-    const float Cn = __bfloat162float(a.Cm[row * a.ldc + n]);
-    g = (g + Cn * dyy) * fast_exp(dt * An);  // after this line g = dL/dh_{t-1} contribution through h_t
-  }
-  (void)Dd;
+  float g = 0.f;  // dL/dh_t accumulated right-to-left (padding steps: dt = 0, dyy = 0 leave it unchanged)
+#pragma unroll 8
+  for (int i = kSTile - 1; i >= 0; --i)
+    g = (g + st.C[i][n] * st.u[i][dl]) * fast_exp(st.dt[i][dl] * An);  // after this line g = dL/dh_{t-1} through h_t
+  (void)hin;
   Gl[(((size_t)b * a.ntiles + tile) * a.Dn + d) * kSN + n] = g;
 }
 
