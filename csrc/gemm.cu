@@ -512,10 +512,27 @@ static int launch_gemm_mc(const CUtensorMap& ta, const CUtensorMap& tb, const CU
   return check_launch("gemm_bf16");
 }
 
+// The two modes that issue TMA loads with .multicast::cluster (MODE_MULTICAST, MODE_QUAD) are opt-in, and even
+// then only taken when both operands are ordinary allocations of the GPU the kernel runs on: TMA multicast
+// loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory hung
+// the GPU.  The default path (CTA pairs, or one CTA per tile for narrow N) has no multicast load in it.
+static thread_local bool g_operands_local = false;
+static bool operands_on_this_gpu(const void* A, const void* B) {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) return false;
+  const void* ptrs[2] = {A, B};
+  for (const void* p : ptrs) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    if (at.type != cudaMemoryTypeDevice || at.device != dev) return false;
+  }
+  return true;
+}
+
 static bool use_multicast() {
   static int v = -1;
-  if (v < 0) { const char* e = getenv("MAMBA_B200_GEMM_MULTICAST"); v = (e == nullptr || e[0] != '0') ? 1 : 0; }
-  return v == 1;
+  if (v < 0) { const char* e = getenv("MAMBA_B200_GEMM_MULTICAST"); v = (e != nullptr && e[0] == '1') ? 1 : 0; }  // default off
+  return v == 1 && g_operands_local;
 }
 
 static bool use_pair() {
@@ -527,7 +544,7 @@ static bool use_pair() {
 static bool use_quad() {
   static int v = -1;
   if (v < 0) { const char* e = getenv("MAMBA_B200_GEMM_QUAD"); v = (e != nullptr && e[0] == '1') ? 1 : 0; }
-  return v == 1;
+  return v == 1 && g_operands_local;
 }
 // quarter-height box of the K-major B tile (MODE_QUAD); set by mb_gemm_bf16 right before the dispatch
 static thread_local CUtensorMap g_tb_quarter;
@@ -593,6 +610,15 @@ extern "C" int mb_gemm_bf16(const void* A, long long lda, int a_major, const voi
   else { if (make_tmap_bf16_2d(&ta, A, K, M, lda, BK)) return 1; }
   if (b_major == 0) { if (make_tmap_bf16_2d(&tb, B, N, K, ldb, BN)) return 1; }
   else { if (make_tmap_bf16_2d(&tb, B, K, N, ldb, BK)) return 1; }
+  {  // multicast modes need both operands in this GPU's own memory; only look when one of them was asked for
+    static int any_mc = -1;
+    if (any_mc < 0) {
+      const char* e1 = getenv("MAMBA_B200_GEMM_MULTICAST");
+      const char* e2 = getenv("MAMBA_B200_GEMM_QUAD");
+      any_mc = ((e1 != nullptr && e1[0] == '1') || (e2 != nullptr && e2[0] == '1')) ? 1 : 0;
+    }
+    g_operands_local = any_mc == 1 && operands_on_this_gpu(A, B);
+  }
   // half-height box of the K-major B tile for the multicast path (MN-major boxes are per 64-wide atom already)
   if (b_major == 0) { if (make_tmap_bf16_2d(&tbh, B, N, K, ldb, BN / 2)) return 1; }
   else tbh = tb;
