@@ -173,7 +173,7 @@ def main():
     if fused and args.graphs and accum > 1:
         # one-time, untimed: capture forward + backward of a no-sync micro-step (same kernels, same math)
         from mamba_distributed_b200.parallel import MicroStepGraph
-        graph = MicroStepGraph(wrapped, 1.0 / accum, (B, T), device=device)
+        graph = MicroStepGraph.build_if_it_fits(wrapped, 1.0 / accum, (B, T), device=device)
         optimizer.zero_grad()
 
     def micro(x, y, last):

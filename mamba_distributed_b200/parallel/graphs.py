@@ -41,14 +41,35 @@ class MicroStepGraph:
                     self._micro()
             torch.cuda.current_stream(device).wait_stream(side)
             torch.cuda.synchronize(device)
+            torch.cuda.empty_cache()               # the warm-up's blocks belong to the side stream: give them back
+            reserved0 = torch.cuda.memory_reserved(device)
             self.graph = torch.cuda.CUDAGraph()
             n0 = _lib.kernel_launches()
             with torch.cuda.graph(self.graph):
                 self.loss = self._micro()
             self.kernels_per_replay = _lib.kernel_launches() - n0   # our kernels inside one replay
+            # the graph's private pool keeps one micro-step's peak working set reserved for as long as it lives
+            self.pool_bytes = max(0, torch.cuda.memory_reserved(device) - reserved0)
         finally:
             ddp.require_backward_grad_sync = prev
         self.replays = 0
+
+    def leaves_room_for_eager_step(self, margin: float = 1.1) -> bool:
+        """The final (eager) micro-step needs about the same working set again, from the ordinary pool."""
+        free, _ = torch.cuda.mem_get_info(self.x.device)
+        return free >= margin * self.pool_bytes
+
+    @classmethod
+    def build_if_it_fits(cls, *args, **kwargs):
+        """``MicroStepGraph(...)`` or ``None`` when two micro-step working sets do not fit in device memory
+        (e.g. 2.7B at T = 8192 on one 180 GB GPU): the caller then runs every micro-step eagerly."""
+        g = cls(*args, **kwargs)
+        if g.leaves_room_for_eager_step():
+            return g
+        del g.graph, g.loss
+        del g
+        torch.cuda.empty_cache()
+        return None
 
     def _micro(self):
         with torch.autocast("cuda", dtype=self.autocast_dtype):

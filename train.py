@@ -213,7 +213,8 @@ def main(argv=None):
             # first training step: capture forward + backward of a no-sync micro-step (its warm-up passes
             # leave gradients in the arena, which the zero_grad below clears)
             from mamba_distributed_b200.parallel import MicroStepGraph
-            micro_graph = MicroStepGraph(model, 1.0 / grad_accum_steps, (B, T), device=device)
+            micro_graph = MicroStepGraph.build_if_it_fits(model, 1.0 / grad_accum_steps, (B, T), device=device)
+            want_graph = micro_graph is not None
         optimizer.zero_grad()
         loss_accum = torch.zeros((), device=device)
         for micro_step in range(grad_accum_steps):
