@@ -273,12 +273,12 @@ def main():
 
     if rank == 0:
         out = {
-            "metric": f"train tokens/sec Mamba-2 {args.preset.upper()} DDP",
+            "metric": f"train tokens/sec {'Mamba-2' if args.layer == 'Mamba2' else 'Mamba-1'} {args.preset.upper()} DDP",
             "impl": args.impl,
             "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"model": f"Mamba-2 {args.preset} ({nparams/1e6:.1f}M params, {cfg.layer_type}, "
+            "config": {"model": f"{'Mamba-2' if args.layer == 'Mamba2' else 'Mamba-1'} {args.preset} ({nparams/1e6:.1f}M params, {cfg.layer_type}, "
                                 f"d_model={cfg.d_model}, n_layer={cfg.n_layer}, vocab={cfg.vocab_size}), random init",
                        "global_batch": tokens_per_step, "micro_batch": B, "seq_len": T,
                        "grad_accum": accum, "parallelism": f"dp{world}",
