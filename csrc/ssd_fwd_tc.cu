@@ -129,9 +129,6 @@ ssd_outer_kernel(const bf16* __restrict__ arow, long long lda, const __grid_cons
 // Accumulators are double-buffered in TMEM (CB 256 cols + 2 x (64 + 64)), per-head tiles in smem, so
 // head h+1 is being scaled while head h is multiplied and head h-1 is written out.
 // ------------------------------------------------------------------------------------------
-#ifndef MB_EXP_NOSTORE
-#define MB_EXP_NOSTORE 0
-#endif
 #ifndef MB_TBLK
 #define MB_TBLK 5
 #endif

@@ -1,5 +1,5 @@
 #!/bin/bash
-# usage: scan_exp.sh "<extra nvcc flags>"  -- timeline experiment, prints epilogue durations and total
+# usage: scan_exp.sh "<extra nvcc flags, e.g. -DMB_TBLK=4 -DMB_TBWD=1>"  -- clock64 timeline of one scan CTA: epilogue / scale durations
 cd "$(dirname "$0")/.."
 MB_NVCC_EXTRA="-DMB_SSD_TIMING $1" python -m mamba_distributed_b200.ops.build -f >/dev/null
 timeout 3000 /usr/local/graft/bin/gpurun --timeout 600 -- 'timeout 300 python scripts/ncu_targets.py ssd > gpurun_out/timeline.txt 2>&1' | tail -1
