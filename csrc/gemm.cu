@@ -45,6 +45,13 @@ __device__ __forceinline__ void decode_tile(int tile, int tiles_m, int tiles_n, 
 
 enum { EPI_BF16 = 0, EPI_F32 = 1, EPI_F32_ATOMIC = 2 };
 
+// Columns the MMAs of N tile `n_blk` have to cover: the tile width, or the remaining columns rounded up to 32 (each
+// CTA of a pair then holds a multiple of 16 B rows, i.e. whole 8-row swizzle groups).
+__device__ __forceinline__ int tile_n_eff(int Ng, int n_blk, int BN) {
+  const int rem = Ng - n_blk * BN;
+  return rem >= BN ? BN : ((rem + 31) & ~31);
+}
+
 enum { MODE_SINGLE = 0, MODE_MULTICAST = 1, MODE_PAIR = 2, MODE_QUAD = 3 };
 
 template <int BN, int MODE = MODE_SINGLE>
@@ -163,7 +170,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 tma_load_2d_pair_mc(b_dst + pair * (BK * 128), &tmB, &full_bar[stage],
                                     n_blk * BN + (qpos * (BN / 128) + pair) * 64, kb * BK, m2);
             } else if (B_MAJOR == MAJOR_K) {  // tmB here is the half-height (BN/2 rows) box
-              tma_load_2d_pair(b_dst, &tmB, &full_bar[stage], kb * BK, n_blk * BN + crank * (BN / 2));
+              // the MMA of a narrow last N tile (see n_eff in the MMA issuer) takes its second half of the B rows from
+              // the odd CTA, so that CTA fetches from n0 + n_eff / 2 instead of n0 + BN / 2
+              tma_load_2d_pair(b_dst, &tmB, &full_bar[stage], kb * BK, n_blk * BN + crank * (tile_n_eff(Ng, n_blk, BN) / 2));
             } else {
 #pragma unroll
               for (int j = 0; j < BN / 128; ++j)
@@ -209,7 +218,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   } else if (warp == 1) {
     // ================================ MMA issuer ========================================
     if (lane == 0 && (!PAIR || qpos == 0)) {
-      constexpr uint32_t idesc = make_idesc_bf16(PAIR ? 2 * BM : BM, BN, A_MAJOR, B_MAJOR);
+      constexpr uint32_t idesc_full = make_idesc_bf16(PAIR ? 2 * BM : BM, BN, A_MAJOR, B_MAJOR);
       // K-major: +32 B per UMMA_K inside the swizzle row; MN-major: +16 k-rows * 128 B
       constexpr uint32_t a_kstep = A_MAJOR == MAJOR_K ? 32 : 16 * 128;
       constexpr uint32_t b_kstep = B_MAJOR == MAJOR_K ? 32 : 16 * 128;
@@ -224,6 +233,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int kb1 = min(kb0 + kb_per_split, kblocks);
         const int acc = local & 1;
         const uint32_t acc_phase = (local >> 1) & 1;
+        // A ragged last N tile (in_proj: 3352 = 13 x 256 + 24) runs its MMAs at N = 32 instead of 256: the MMA time
+        // is proportional to N and the rest of the tile would only multiply zero-filled rows.
+        uint32_t idesc = idesc_full;
+        if (PAIR && !QUAD && B_MAJOR == MAJOR_K) {
+          int m_unused, n_blk_t, s_unused;
+          decode_tile(tile, tiles_m, tiles_n, m_unused, n_blk_t, s_unused);
+          idesc = make_idesc_bf16(2 * BM, (uint32_t)tile_n_eff(Ng, n_blk_t, BN), A_MAJOR, B_MAJOR);
+        }
 #ifdef MB_GEMM_TIMING
         const long long tt0 = clock64();
 #endif
