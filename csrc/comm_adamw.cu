@@ -137,6 +137,7 @@ comm_adamw_allgather_kernel(PeerTable peers, int world, int rank, unsigned long 
                             float* __restrict__ norm_acc, float* __restrict__ norm_out,
                             unsigned int* __restrict__ block_counter) {
   __shared__ float s_clip;
+  __shared__ bool s_skip;
   const int tid = threadIdx.x;
   // ---- global gradient norm: exchange per-rank partials ----
   if (blockIdx.x == 0 && tid < world) {
@@ -156,7 +157,9 @@ comm_adamw_allgather_kernel(PeerTable peers, int world, int rank, unsigned long 
     const float norm = sqrtf(total);
     float clip = 1.f;
     if (a.max_norm > 0.f) clip = fminf(1.f, a.max_norm / (norm + 1e-6f));
-    if (!isfinite(norm)) clip = 0.f;  // NaN/Inf guard: skip the update direction, keep state finite
+    // NaN/Inf guard: a non-finite global norm means some gradient is NaN/Inf; every rank sees the
+    // same total, so all of them skip this update (parameters, m and v stay as they are; 0 * NaN would not).
+    s_skip = !isfinite(norm);
     s_clip = clip;
     if (blockIdx.x == 0) *norm_out = norm;
   }
@@ -166,7 +169,7 @@ comm_adamw_allgather_kernel(PeerTable peers, int world, int rank, unsigned long 
   float* grad = peers.grad[rank];
   float* master = peers.master[rank];
 
-  for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+  for (int it = blockIdx.x; it < n_items && !s_skip; it += gridDim.x) {
     const long long arena_off = items[4 * it + 0];
     const long long local_off = items[4 * it + 1];
     const int count = (int)items[4 * it + 2];

@@ -86,6 +86,11 @@ class FusedAdamW:
         ddp = self.ddp
         g = ddp.flat_grad
         norm = torch.linalg.vector_norm(g)
+        if not bool(torch.isfinite(norm)):
+            # NaN/Inf guard: leave parameters and moments untouched (the fused kernel does the same on the device)
+            self.step_count -= 1
+            print(f"FusedAdamW: non-finite gradient norm ({float(norm)}), step skipped")
+            return norm
         if max_norm is not None:
             coef = torch.clamp(max_norm / (norm + 1e-6), max=1.0)
             g.mul_(coef)

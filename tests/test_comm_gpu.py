@@ -61,3 +61,36 @@ def test_fused_comm_multi_gpu(world):
                         os.path.join(ROOT, "tests", "_comm_worker.py")], env=env, capture_output=True, text=True,
                        timeout=600)
     assert r.returncode == 0 and "COMM_OK" in r.stdout, (r.stdout[-2000:], r.stderr[-4000:])
+
+
+@pytest.mark.gpu
+def test_fused_step_skips_update_on_non_finite_gradient():
+    """a NaN anywhere in the gradient must not reach the parameters or the Adam moments."""
+    from mamba_distributed_b200.config import MambaConfig
+    from mamba_distributed_b200.parallel import FusedDDP
+    from model import LMHeadModel
+    cfg = MambaConfig(d_model=256, n_layer=2, vocab_size=2048, ssm_cfg={"layer": "Mamba2"})
+    torch.manual_seed(0)
+    m = LMHeadModel(cfg, "cuda").cuda()
+    ddp = FusedDDP(m, comm="fused", bucket_cap_mb=0.5)
+    opt = m.configure_optimizers(0.1, 3e-3, "cuda", False, fused_comm=ddp)
+    x = torch.randint(0, 2048, (2, 256), device="cuda"); y = torch.randint(0, 2048, (2, 256), device="cuda")
+
+    def fwd_bwd(poison=False):
+        opt.zero_grad()
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            _, loss = ddp(x, y)
+        # the gradient has to be bad while backward runs: the per-bucket reduce + norm kernels read it from there
+        (loss * float("nan") if poison else loss).backward()
+
+    fwd_bwd(); opt.step(max_norm=1.0)            # one healthy step so that m / v are non-trivial
+    before = ddp.flat_param.clone()
+    fwd_bwd(poison=True)
+    norm = opt.step(max_norm=1.0)
+    torch.cuda.synchronize()
+    assert not torch.isfinite(torch.as_tensor(float(norm)))
+    assert torch.equal(ddp.flat_param, before)      # nothing moved
+    fwd_bwd(); norm2 = opt.step(max_norm=1.0)     # and training continues with finite state afterwards
+    torch.cuda.synchronize()
+    assert torch.isfinite(torch.as_tensor(float(norm2))) and torch.isfinite(ddp.flat_param).all()
+    assert not torch.equal(ddp.flat_param, before)

@@ -113,3 +113,25 @@ def test_single_process_wrapper_and_arena_views():
     assert ddp.flat_grad.abs().sum() == 0
     # state_dict is the module's, fp32, full shapes
     assert set(ddp.state_dict()) == set(model.state_dict())
+
+
+def test_flat_adamw_skips_non_finite_gradient(capsys):
+    """The PyTorch arm of FusedAdamW leaves parameters and moments alone when the gradient norm is NaN/Inf."""
+    import torch
+    from mamba_distributed_b200.config import MambaConfig
+    from mamba_distributed_b200.parallel import FusedDDP
+    from model import LMHeadModel
+    torch.manual_seed(0)
+    cfg = MambaConfig(d_model=32, n_layer=1, vocab_size=64, ssm_cfg={"layer": "Mamba2", "headdim": 8, "d_state": 16, "chunk_size": 8})
+    m = LMHeadModel(cfg, "cpu")
+    ddp = FusedDDP(m)
+    opt = m.configure_optimizers(0.1, 1e-2, "cpu", False, fused_comm=ddp)
+    x = torch.randint(0, 64, (2, 16)); y = torch.randint(0, 64, (2, 16))
+    opt.zero_grad(); _, loss = ddp(x, y); loss.backward(); opt.step(max_norm=1.0)
+    before, m0, steps = ddp.flat_param.clone(), opt.m.clone(), opt.step_count
+    opt.zero_grad(); _, loss = ddp(x, y); loss.backward()
+    ddp.flat_grad[3] = float("inf")
+    norm = opt.step(max_norm=1.0)
+    assert not torch.isfinite(norm)
+    assert torch.equal(ddp.flat_param, before) and torch.equal(opt.m, m0) and opt.step_count == steps
+    assert "step skipped" in capsys.readouterr().out
