@@ -64,9 +64,13 @@ def test_train_and_eval_cli_tiny(tmp_path):
     r = _run([os.path.join(ROOT, "train.py"), "--device", "cpu", "--synthetic", "--d_model", "32",
               "--n_layer", "1", "--vocab_size", "50304", "--B", "2", "--T", "32",
               "--total_batch_size", "128", "--max_steps", "3", "--val_every", "2", "--val_steps", "1",
-              "--sample_every", "2", "--ckpt_every", "2", "--warmup_steps", "2"], cwd)
+              "--sample_every", "2", "--ckpt_every", "2", "--warmup_steps", "2", "--timers",
+              "--metrics_jsonl", "metrics.jsonl"], cwd)
     assert r.returncode == 0, r.stderr[-3000:]
     out = r.stdout
+    import json
+    recs = [json.loads(l) for l in open(os.path.join(cwd, "metrics.jsonl"))]
+    assert [x["step"] for x in recs] == [0, 1, 2] and all(x["tok_per_sec"] > 0 and "fwd" in x["phases_ms"] for x in recs)
     assert "=> calculated gradient accumulation steps: 2" in out
     assert "step     0 | loss:" in out and "tok/sec:" in out and "rank 0 sample 0:" in out
     lines = open(os.path.join(cwd, "log", "log.txt")).read().split("\n")

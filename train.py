@@ -24,6 +24,8 @@ process-group init, every rank truncating the log file.
 from __future__ import annotations
 
 import argparse
+import math
+import json
 import os
 import time
 
@@ -68,6 +70,8 @@ def parse_args(argv=None):
     p.add_argument("--device", default=None)
     p.add_argument("--seed", type=int, default=1337)
     p.add_argument("--timers", action="store_true", help="print per-phase device timings")
+    p.add_argument("--metrics_jsonl", default=None,
+                   help="append one JSON object per step (loss, lr, norm, dt, tok/s, phase timings, exposed comm ms)")
     p.add_argument("--cuda_graphs", type=int, default=1,
                    help="replay the non-final micro-steps of a step from one captured CUDA graph (GPU + fused kernels only)")
     return p.parse_args(argv)
@@ -249,8 +253,20 @@ def main(argv=None):
                   f"dt: {dt*1000:.2f}ms | tok/sec: {tokens_per_sec:.2f}")
             with open(log_file, "a") as f:
                 f.write(f"{step} train {loss_accum.item():.6f}\n")
+            phases = timer.flush() if args.timers else {}
             if args.timers:
-                print("  phases(ms): " + ", ".join(f"{k}={v:.1f}" for k, v in timer.flush().items()))
+                print("  phases(ms): " + ", ".join(f"{k}={v:.1f}" for k, v in phases.items()))
+            if not math.isfinite(float(norm)):
+                print(f"step {step:5d} | non-finite gradient norm: optimizer step skipped")
+            if args.metrics_jsonl:
+                rec = {"step": step, "loss": loss_accum.item(), "lr": lr, "norm": float(norm), "dt_ms": dt * 1000,
+                       "tok_per_sec": tokens_per_sec, "phases_ms": phases}
+                symm = getattr(model, "symm", None)
+                t_comm = symm.last_timings() if symm is not None else None
+                if t_comm is not None:
+                    rec["exposed_grad_reduce_scatter_ms"], rec["clip_adamw_allgather_ms"] = float(t_comm[0]), float(t_comm[1])
+                with open(args.metrics_jsonl, "a") as f:
+                    f.write(json.dumps(rec) + "\n")
 
     if ddp:
         dist.destroy_process_group()
