@@ -21,7 +21,6 @@ from enum import Enum
 
 import torch
 import torch.distributed as dist
-import torch.nn.functional as F
 
 from mamba_distributed_b200.config import MambaConfig
 from mamba_distributed_b200.utils import hellaswag as hs

@@ -6,7 +6,6 @@ it is here so every field of ``MambaConfig`` is honoured.  Parameter names follo
 code (PyTorch SDPA), not a hand-written kernel: it is outside the benchmarked surface."""
 from __future__ import annotations
 
-import math
 
 import torch
 import torch.nn as nn

@@ -15,7 +15,6 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from .. import ops
-from ..ops import ref
 from .norm import RMSNormGated
 
 

@@ -7,7 +7,6 @@ jsonl files, which cannot be downloaded here (eval.py:16-20 needs the network)."
 from __future__ import annotations
 
 import json
-import os
 import random
 
 import torch
