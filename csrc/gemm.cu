@@ -52,25 +52,20 @@ __device__ __forceinline__ int tile_n_eff(int Ng, int n_blk, int BN) {
   return rem >= BN ? BN : ((rem + 31) & ~31);
 }
 
-enum { MODE_SINGLE = 0, MODE_MULTICAST = 1, MODE_PAIR = 2, MODE_QUAD = 3 };
+enum { MODE_SINGLE = 0, MODE_PAIR = 1 };
 
 template <int BN, int MODE = MODE_SINGLE>
 struct GemmCfg {
   // MODE_PAIR: each CTA of the pair keeps only its half of the B tile, which buys two more stages
-  static constexpr int STAGES = MODE >= MODE_PAIR ? 6 : (BN == 256 ? 4 : 6);
+  static constexpr int STAGES = MODE == MODE_PAIR ? 6 : (BN == 256 ? 4 : 6);
   static constexpr int A_BYTES = BM * BK * 2;
-  static constexpr int B_BYTES = (MODE >= MODE_PAIR ? BN / 2 : BN) * BK * 2;
+  static constexpr int B_BYTES = (MODE == MODE_PAIR ? BN / 2 : BN) * BK * 2;
   static constexpr int STAGING = 4 * 2 * 4096;  // 4 epilogue warps x 2 buffers x [32 rows][128 B]
   static constexpr int SMEM = STAGES * (A_BYTES + B_BYTES) + STAGING + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
-// MC = true: launched as clusters of 2 CTAs that work on two vertically adjacent output tiles
-// (same N block).  Each CTA TMA-loads its own A tile and HALF of the shared B tile, multicast to
-// both CTAs, which cuts L2->SM operand traffic per tile from 48 KB to 32 KB per k-block (the
-// mainloop is L2-bandwidth bound otherwise: ncu showed 64 % tensor-pipe activity at 148 x 48 KB
-// per 512 clk).  Stage release needs both CTAs' MMA commits (multicast commit, count 2).
-//
-// MODE_PAIR: the two CTAs of a cluster form one `cta_group::2` MMA: a 256 x BN tile whose A rows and TMEM
+// MODE_PAIR: launched as clusters of 2 CTAs that work on two vertically adjacent output tiles (same N block)
+// and form one `cta_group::2` MMA: a 256 x BN tile whose A rows and TMEM
 // accumulator rows are split across the two SMs and whose B tile is split in halves of BN/2 rows, one per
 // SM.  Only the even CTA issues tcgen05.mma / tcgen05.commit; both run a TMA producer (whose transaction
 // bytes are all counted on the even CTA's full barrier) and an epilogue over their own TMEM.  Per k-block
@@ -83,13 +78,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                  long long ldd, int splitk, int kb_per_split, float alpha) {
   using Cfg = GemmCfg<BN, MODE>;
   constexpr int STAGES = Cfg::STAGES;
-  constexpr bool MC = MODE != MODE_SINGLE;   // launched as clusters that share an N block
-  constexpr bool PAIR = MODE >= MODE_PAIR;   // cta_group::2 MMA
-  // MODE_QUAD: clusters of 4 = two CTA pairs on vertically adjacent 256-row tiles of the same N block.  The two
-  // CTAs that hold the same half of the B tile (one per pair) each fetch half of it and multicast it to both:
-  // 24 KB instead of 32 KB per k-block per SM out of L2 (the mainloop was waiting on the TMA full barriers).
-  constexpr bool QUAD = MODE == MODE_QUAD;
-  constexpr int CL = QUAD ? 4 : (MC ? 2 : 1);
+  constexpr bool PAIR = MODE == MODE_PAIR;   // cluster of 2 CTAs, cta_group::2 MMA
+  constexpr int CL = PAIR ? 2 : 1;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
@@ -104,22 +94,20 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tiles_m_real = (Mg + BM - 1) / BM, tiles_n = (Ng + BN - 1) / BN;
-  // with MC the scheduler hands out PAIRS of M blocks to a cluster; CTA `crank` takes block 2*pm + crank
+  // with PAIR the scheduler hands out pairs of M blocks to a cluster; CTA `crank` takes block 2*pm + crank
   const int tiles_m = (tiles_m_real + CL - 1) / CL;
   const int num_tiles = tiles_m * tiles_n * splitk;
   const int kblocks = (Kg + BK - 1) / BK;
-  const int crank = MC ? (int)cluster_ctarank() : 0;
+  const int crank = PAIR ? (int)cluster_ctarank() : 0;
   const int worker = (int)blockIdx.x / CL;
   const int nworkers = (int)gridDim.x / CL;
-  const int pair = crank >> 1, qpos = crank & 1;          // which pair of the cluster, position inside the pair
-  const uint16_t pair_mask = (uint16_t)(0b11 << (2 * pair));
 
   if (warp == 0 && lane == 0) {
     prefetch_tensormap(&tmA);
     prefetch_tensormap(&tmB);
     if (TMA_STORE) prefetch_tensormap(&tmD);
-    // multicast: a stage is free once BOTH CTAs' MMAs released it; pair: one (multicast) commit per CTA
-    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], ((MC && !PAIR) || QUAD) ? 2 : 1); }
+    // pair: the issuing CTA's commit arrives once on the empty barrier of both CTAs
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
     // pair: the issuing CTA waits for the epilogue warps of both CTAs before it reuses an accumulator
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], PAIR ? 8 : 4); }
     fence_mbar_init();
@@ -130,7 +118,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
   tc_fence_before();
   __syncthreads();
-  if (MC) cluster_sync_all();  // the peer's barriers exist before anything is multicast into them
+  if (PAIR) cluster_sync_all();  // the peer's barriers exist before anything signals them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -142,7 +130,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       for (int tile = worker; tile < num_tiles; tile += nworkers) {
         int m_blk, n_blk, split;
         decode_tile(tile, tiles_m, tiles_n, m_blk, n_blk, split);
-        if (MC) m_blk = CL * m_blk + crank;
+        if (PAIR) m_blk = CL * m_blk + crank;
         const int kb0 = split * kb_per_split;
         const int kb1 = min(kb0 + kb_per_split, kblocks);
         for (int kb = kb0; kb < kb1; ++kb) {
@@ -151,7 +139,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           uint8_t* b_dst = sB + stage * Cfg::B_BYTES;
           if (PAIR) {
             // both CTAs' loads complete on the even CTA's barrier, which expects the bytes of both
-            if (qpos == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * (Cfg::A_BYTES + Cfg::B_BYTES));
+            if (crank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * (Cfg::A_BYTES + Cfg::B_BYTES));
             if (A_MAJOR == MAJOR_K) {
               tma_load_2d_pair(a_dst, &tmA, &full_bar[stage], kb * BK, m_blk * BM);
             } else {
@@ -159,17 +147,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               for (int j = 0; j < BM / 64; ++j)
                 tma_load_2d_pair(a_dst + j * (BK * 128), &tmA, &full_bar[stage], m_blk * BM + j * 64, kb * BK);
             }
-            if (QUAD) {
-              // half `qpos` of the B tile is shared with the CTA at the same position of the other pair: each of the
-              // two fetches one quarter of the tile (64 rows / one 64-column atom) and multicasts it to both
-              const uint16_t m2 = (uint16_t)((1u << qpos) | (1u << (qpos + 2)));
-              if (B_MAJOR == MAJOR_K)   // tmB here is the quarter-height (BN/4 rows) box
-                tma_load_2d_pair_mc(b_dst + pair * (BN / 4) * 128, &tmB, &full_bar[stage], kb * BK,
-                                    n_blk * BN + qpos * (BN / 2) + pair * (BN / 4), m2);
-              else
-                tma_load_2d_pair_mc(b_dst + pair * (BK * 128), &tmB, &full_bar[stage],
-                                    n_blk * BN + (qpos * (BN / 128) + pair) * 64, kb * BK, m2);
-            } else if (B_MAJOR == MAJOR_K) {  // tmB here is the half-height (BN/2 rows) box
+            if (B_MAJOR == MAJOR_K) {  // tmB here is the half-height (BN/2 rows) box
               // the MMA of a narrow last N tile (see n_eff in the MMA issuer) takes its second half of the B rows from
               // the odd CTA, so that CTA fetches from n0 + n_eff / 2 instead of n0 + BN / 2
               tma_load_2d_pair(b_dst, &tmB, &full_bar[stage], kb * BK, n_blk * BN + crank * (tile_n_eff(Ng, n_blk, BN) / 2));
@@ -190,26 +168,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             for (int j = 0; j < BM / 64; ++j)
               tma_load_2d(a_dst + j * (BK * 128), &tmA, &full_bar[stage], m_blk * BM + j * 64, kb * BK);
           }
-          if (!MC) {
-            if (B_MAJOR == MAJOR_K) {
-              tma_load_2d(b_dst, &tmB, &full_bar[stage], kb * BK, n_blk * BN);
-            } else {
-#pragma unroll
-              for (int j = 0; j < BN / 64; ++j)
-                tma_load_2d(b_dst + j * (BK * 128), &tmB, &full_bar[stage], n_blk * BN + j * 64, kb * BK);
-            }
+          if (B_MAJOR == MAJOR_K) {
+            tma_load_2d(b_dst, &tmB, &full_bar[stage], kb * BK, n_blk * BN);
           } else {
-            // this CTA fetches half of the B tile and multicasts it into both CTAs' stage
-            if (B_MAJOR == MAJOR_K) {
-              tma_load_2d_mc(b_dst + crank * (BN / 2) * 128, &tmB, &full_bar[stage], kb * BK,
-                             n_blk * BN + crank * (BN / 2), 0b11);
-            } else {
 #pragma unroll
-              for (int j = 0; j < BN / 128; ++j) {
-                const int atom = crank * (BN / 128) + j;
-                tma_load_2d_mc(b_dst + atom * (BK * 128), &tmB, &full_bar[stage], n_blk * BN + atom * 64, kb * BK, 0b11);
-              }
-            }
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_2d(b_dst + j * (BK * 128), &tmB, &full_bar[stage], n_blk * BN + j * 64, kb * BK);
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -217,7 +181,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ========================================
-    if (lane == 0 && (!PAIR || qpos == 0)) {
+    if (lane == 0 && (!PAIR || crank == 0)) {
       constexpr uint32_t idesc_full = make_idesc_bf16(PAIR ? 2 * BM : BM, BN, A_MAJOR, B_MAJOR);
       // K-major: +32 B per UMMA_K inside the swizzle row; MN-major: +16 k-rows * 128 B
       constexpr uint32_t a_kstep = A_MAJOR == MAJOR_K ? 32 : 16 * 128;
@@ -236,7 +200,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // A ragged last N tile (in_proj: 3352 = 13 x 256 + 24) runs its MMAs at N = 32 instead of 256: the MMA time
         // is proportional to N and the rest of the tile would only multiply zero-filled rows.
         uint32_t idesc = idesc_full;
-        if (PAIR && !QUAD && B_MAJOR == MAJOR_K) {
+        if (PAIR && B_MAJOR == MAJOR_K) {
           int m_unused, n_blk_t, s_unused;
           decode_tile(tile, tiles_m, tiles_n, m_unused, n_blk_t, s_unused);
           idesc = make_idesc_bf16(2 * BM, (uint32_t)tile_n_eff(Ng, n_blk_t, BN), A_MAJOR, B_MAJOR);
@@ -269,16 +233,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             if (PAIR) mma_bf16_ss_pair(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
             else mma_bf16_ss(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
-          // frees this smem stage when the MMAs above retire (in BOTH CTAs with MC: the peer's
-          // producer multicasts into our stage too; with PAIR the MMA itself read both CTAs' stage)
-          if (QUAD) mma_commit_pair_mc(&empty_bar[stage], 0b1111);   // the other pair's producers write into our stage too
-          else if (PAIR) mma_commit_pair_mc(&empty_bar[stage], 0b11);
-          else if (MC) mma_commit_mc(&empty_bar[stage], 0b11);
+          // frees this smem stage when the MMAs above retire (with PAIR in both CTAs: the MMA read both stages)
+          if (PAIR) mma_commit_pair_mc(&empty_bar[stage], 0b11);
           else mma_commit(&empty_bar[stage]);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
         // accumulator complete -> epilogue (of both CTAs with PAIR)
-        if (PAIR) mma_commit_pair_mc(&tfull_bar[acc], pair_mask); else mma_commit(&tfull_bar[acc]);
+        if (PAIR) mma_commit_pair_mc(&tfull_bar[acc], 0b11); else mma_commit(&tfull_bar[acc]);
 #ifdef MB_GEMM_TIMING
         if (blockIdx.x == 4 && local < 30)
           printf("G tile %d start %lld wait_acc %lld wait_full %lld issue_total %lld\n", local, tt0, tt1 - tt0, twait_full, clock64() - tt0);
@@ -293,7 +254,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int tile = worker; tile < num_tiles; tile += nworkers, ++local) {
       int m_blk, n_blk, split_unused;
       decode_tile(tile, tiles_m, tiles_n, m_blk, n_blk, split_unused);
-      if (MC) m_blk = CL * m_blk + crank;
+      if (PAIR) m_blk = CL * m_blk + crank;
       const int acc = local & 1;
       const uint32_t acc_phase = (local >> 1) & 1;
       mbar_wait(&tfull_bar[acc], acc_phase);
@@ -399,7 +360,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       tc_fence_before();
       __syncwarp();
       if (lane == 0) {
-        if (PAIR && qpos != 0) mbar_arrive_cluster(&tempty_bar[acc], 2 * pair);  // the issuing (even) CTA owns the wait
+        if (PAIR && crank != 0) mbar_arrive_cluster(&tempty_bar[acc], 0);  // the issuing (even) CTA owns the wait
         else mbar_arrive(&tempty_bar[acc]);
       }
     }
@@ -407,7 +368,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
   tc_fence_before();
   __syncthreads();
-  if (MC) cluster_sync_all();  // no CTA leaves while its peer may still signal / write into it
+  if (PAIR) cluster_sync_all();  // no CTA leaves while its peer may still signal / read from it
   if (warp == 1) { if (PAIR) tmem_dealloc2(tmem_base, 2 * BN); else tmem_dealloc(tmem_base, 2 * BN); }
 }
 
@@ -487,11 +448,10 @@ int make_tmap_bf16_3d(CUtensorMap* map, const void* ptr, long long d2, long long
 }
 
 template <int BN, uint32_t AM, uint32_t BMJ, int EPI, bool TS, int MODE>
-static int launch_gemm_mc(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, void* D,
-                          const float* bias, int M, int N, int K, long long ldd, int splitk, int kb_per_split,
-                          float alpha, cudaStream_t stream) {
-  constexpr bool MC = MODE != MODE_SINGLE;
-  constexpr int CL = MODE == MODE_QUAD ? 4 : (MC ? 2 : 1);
+static int launch_gemm_mode(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, void* D,
+                            const float* bias, int M, int N, int K, long long ldd, int splitk, int kb_per_split,
+                            float alpha, cudaStream_t stream) {
+  constexpr int CL = MODE == MODE_PAIR ? 2 : 1;
   auto kern = gemm_bf16_kernel<BN, AM, BMJ, EPI, TS, MODE>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -500,7 +460,7 @@ static int launch_gemm_mc(const CUtensorMap& ta, const CUtensorMap& tb, const CU
   }
   const int tiles_m = (cdiv(M, BM) + CL - 1) / CL;
   const int tiles = tiles_m * cdiv(N, BN) * splitk;       // groups of CL vertically adjacent tiles
-  int grid = CL * (tiles < num_sms() / CL ? tiles : num_sms() / CL);
+  const int grid = CL * (tiles < num_sms() / CL ? tiles : num_sms() / CL);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(kGemmThreads);
@@ -513,70 +473,27 @@ static int launch_gemm_mc(const CUtensorMap& ta, const CUtensorMap& tb, const CU
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  if (CL == 4) {
-    // clusters of 4 do not tile every GPC exactly: size the persistent grid by what can be co-resident
-    static int max_clusters = 0;
-    if (max_clusters == 0) {
-      cfg.gridDim = dim3(num_sms() / CL * CL);
-      MB_CUDA(cudaOccupancyMaxActiveClusters(&max_clusters, kern, &cfg));
-      if (max_clusters < 1) max_clusters = 1;
-      if (getenv("MAMBA_B200_GEMM_DEBUG")) fprintf(stderr, "gemm: %d clusters of 4 can be co-resident\n", max_clusters);
-    }
-    grid = CL * (tiles < max_clusters ? tiles : max_clusters);
-    cfg.gridDim = dim3(grid);
-  }
   MB_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha));
   return check_launch("gemm_bf16");
 }
 
-// The two modes that issue TMA loads with .multicast::cluster (MODE_MULTICAST, MODE_QUAD) are opt-in, and even
-// then only taken when both operands are ordinary allocations of the GPU the kernel runs on: TMA multicast
-// loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory hung
-// the GPU.  The default path (CTA pairs, or one CTA per tile for narrow N) has no multicast load in it.
-static thread_local bool g_operands_local = false;
-static bool operands_on_this_gpu(const void* A, const void* B) {
-  int dev = -1;
-  if (cudaGetDevice(&dev) != cudaSuccess) return false;
-  const void* ptrs[2] = {A, B};
-  for (const void* p : ptrs) {
-    cudaPointerAttributes at;
-    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
-    if (at.type != cudaMemoryTypeDevice || at.device != dev) return false;
-  }
-  return true;
-}
-
-static bool use_multicast() {
-  static int v = -1;
-  if (v < 0) { const char* e = getenv("MAMBA_B200_GEMM_MULTICAST"); v = (e != nullptr && e[0] == '1') ? 1 : 0; }  // default off
-  return v == 1 && g_operands_local;
-}
-
+// No TMA load in this file is a multicast load: the operands may be any device-accessible pointer the caller
+// passes through the C ABI, and TMA multicast loads here read only this GPU's memory, since on B200 a TMA
+// multicast load from another GPU's memory hung the GPU.  CTA pairs share the B tile through the cta_group::2
+// MMA (each CTA loads its own half) instead.
 static bool use_pair() {
   static int v = -1;
   if (v < 0) { const char* e = getenv("MAMBA_B200_GEMM_PAIR"); v = (e == nullptr || e[0] != '0') ? 1 : 0; }  // default on
   return v == 1;
 }
 
-static bool use_quad() {
-  static int v = -1;
-  if (v < 0) { const char* e = getenv("MAMBA_B200_GEMM_QUAD"); v = (e != nullptr && e[0] == '1') ? 1 : 0; }
-  return v == 1 && g_operands_local;
-}
-// quarter-height box of the K-major B tile (MODE_QUAD); set by mb_gemm_bf16 right before the dispatch
-static thread_local CUtensorMap g_tb_quarter;
-
 template <int BN, uint32_t AM, uint32_t BMJ, int EPI, bool TS>
 static int launch_gemm_ts(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tb_half, const CUtensorMap& td,
                           void* D, const float* bias, int M, int N, int K, long long ldd, int splitk, int kb_per_split,
                           float alpha, cudaStream_t stream) {
-  if (BN == 256 && use_quad() && cdiv(M, BM) >= 4 && num_sms() % 4 == 0)
-    return launch_gemm_mc<256, AM, BMJ, EPI, TS, MODE_QUAD>(ta, g_tb_quarter, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha, stream);
   if (BN == 256 && use_pair() && cdiv(M, BM) >= 2)
-    return launch_gemm_mc<256, AM, BMJ, EPI, TS, MODE_PAIR>(ta, tb_half, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha, stream);
-  if (use_multicast() && cdiv(M, BM) >= 2)
-    return launch_gemm_mc<BN, AM, BMJ, EPI, TS, MODE_MULTICAST>(ta, tb_half, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha, stream);
-  return launch_gemm_mc<BN, AM, BMJ, EPI, TS, MODE_SINGLE>(ta, tb, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha, stream);
+    return launch_gemm_mode<256, AM, BMJ, EPI, TS, MODE_PAIR>(ta, tb_half, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha, stream);
+  return launch_gemm_mode<BN, AM, BMJ, EPI, TS, MODE_SINGLE>(ta, tb, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha, stream);
 }
 
 template <int BN, uint32_t AM, uint32_t BMJ, int EPI>
@@ -627,29 +544,17 @@ extern "C" int mb_gemm_bf16(const void* A, long long lda, int a_major, const voi
   else { if (make_tmap_bf16_2d(&ta, A, K, M, lda, BK)) return 1; }
   if (b_major == 0) { if (make_tmap_bf16_2d(&tb, B, N, K, ldb, BN)) return 1; }
   else { if (make_tmap_bf16_2d(&tb, B, K, N, ldb, BK)) return 1; }
-  {  // multicast modes need both operands in this GPU's own memory; only look when one of them was asked for
-    static int any_mc = -1;
-    if (any_mc < 0) {
-      const char* e1 = getenv("MAMBA_B200_GEMM_MULTICAST");
-      const char* e2 = getenv("MAMBA_B200_GEMM_QUAD");
-      any_mc = ((e1 != nullptr && e1[0] == '1') || (e2 != nullptr && e2[0] == '1')) ? 1 : 0;
-    }
-    g_operands_local = any_mc == 1 && operands_on_this_gpu(A, B);
-  }
-  // half-height box of the K-major B tile for the multicast path (MN-major boxes are per 64-wide atom already)
+  // half-height box of the K-major B tile for the CTA-pair path (MN-major boxes are per 64-wide atom already)
   if (b_major == 0) { if (make_tmap_bf16_2d(&tbh, B, N, K, ldb, BN / 2)) return 1; }
   else tbh = tb;
-  if (b_major == 0) { if (make_tmap_bf16_2d(&g_tb_quarter, B, N, K, ldb, BN / 4)) return 1; }
-  else g_tb_quarter = tb;
   // split-K only where the epilogue is additive.  The persistent grid runs whole waves of work units
   // (tile pairs x splits when two CTAs share a tile column), so pick the split count that minimises
   // waves x (k-blocks per split + the cost of one more additive epilogue), not just "enough units".
   const int kblocks = cdiv(K, BK);
   int splitk = 1;
   if (d_mode == 2) {
-    const bool paired = cdiv(M, BM) >= 2 && (use_multicast() || (BN == 256 && use_pair()));
-    const bool quad = BN == 256 && use_quad() && cdiv(M, BM) >= 4 && num_sms() % 4 == 0;
-    const int cl = quad ? 4 : (paired ? 2 : 1);
+    const bool paired = cdiv(M, BM) >= 2 && BN == 256 && use_pair();
+    const int cl = paired ? 2 : 1;
     const long long units = (long long)((cdiv(M, BM) + cl - 1) / cl) * cdiv(N, BN);
     const int workers = num_sms() / cl;
     int max_split = kblocks / 8;  // keep >= 8 k-blocks (512 deep) per split
