@@ -48,8 +48,9 @@ def parse_args():
     p.add_argument("--layer", default="Mamba2")
     p.add_argument("--comm", default="auto")
     p.add_argument("--no_e2e", action="store_true")
-    p.add_argument("--graphs", type=int, default=1,
-                   help="1: replay the non-final (no-sync) micro-steps from a CUDA graph (ours only); 0: all eager")
+    p.add_argument("--graphs", type=int, default=2,
+                   help="2: replay every micro-step from a CUDA graph, the final one with its reduce-scatter kernels; "
+                        "1: only the non-final (no-sync) micro-steps; 0: all eager (ours only)")
     return p.parse_args()
 
 
@@ -169,11 +170,15 @@ def main():
     host = [torch.randint(0, V, (2, B, T), generator=gen, dtype=torch.long).pin_memory() for _ in range(accum)]
     dev_batches = [h.to(device) for h in host]
 
-    graph = None
-    if fused and args.graphs and accum > 1:
-        # one-time, untimed: capture forward + backward of a no-sync micro-step (same kernels, same math)
+    graph = graph_last = None
+    if fused and args.graphs:
+        # one-time, untimed: capture forward + backward of a no-sync micro-step and of the final, synchronising
+        # one (same kernels, same math; the final graph contains the per-bucket reduce-scatter launches)
         from mamba_distributed_b200.parallel import MicroStepGraph
-        graph = MicroStepGraph.build_if_it_fits(wrapped, 1.0 / accum, (B, T), device=device)
+        if args.graphs >= 2 and wrapped.symm is not None:
+            graph, graph_last = MicroStepGraph.build_pair(wrapped, 1.0 / accum, (B, T), accum, device=device)
+        elif accum > 1:
+            graph = MicroStepGraph.build_if_it_fits(wrapped, 1.0 / accum, (B, T), device=device)
         optimizer.zero_grad()
 
     def micro(x, y, last):
@@ -181,26 +186,32 @@ def main():
             wrapped.require_backward_grad_sync = last
         if graph is not None and not last:
             return graph(x, y).clone()
+        if graph_last is not None and last:
+            return graph_last(x, y).clone()
         with torch.autocast("cuda", dtype=torch.bfloat16):
             _, loss = wrapped(x, y)
         (loss / accum).backward()
         return loss.detach()
 
-    def opt_step(step_idx):
+    def opt_step(step_idx, loss_acc):
+        """Loss mean over ranks + clip + AdamW, as /root/reference/train.py:221-227; returns (mean loss, norm)."""
         lr = 6e-4 * min(1.0, (step_idx + 1) / 715)
         for g in optimizer.param_groups:
             g["lr"] = lr
         if fused:
-            return optimizer.step(max_norm=1.0)
+            norm = optimizer.step(max_norm=1.0, loss=loss_acc if ddp else None)
+            return (optimizer.last_loss if ddp else loss_acc), norm
+        if ddp:
+            dist.all_reduce(loss_acc, op=dist.ReduceOp.AVG)
         norm = torch.nn.utils.clip_grad_norm_(wrapped.parameters(), 1.0)
         optimizer.step()
-        return norm
+        return loss_acc, norm
 
     def train_step(step_idx, from_host):
         optimizer.zero_grad()
         loss_acc = torch.zeros((), device=device)
         for m in range(accum):
-            if from_host and graph is not None and m != accum - 1:
+            if from_host and (graph if m != accum - 1 else graph_last) is not None:
                 x, y = host[m][0], host[m][1]   # pinned host -> the graph's static input buffers, one copy
             elif from_host:
                 xy = host[m].to(device, non_blocking=True)
@@ -208,7 +219,7 @@ def main():
             else:
                 x, y = dev_batches[m][0], dev_batches[m][1]
             loss_acc += micro(x, y, m == accum - 1).float() / accum
-        norm = opt_step(step_idx)
+        loss_acc, norm = opt_step(step_idx, loss_acc)
         return loss_acc, norm
 
     def barrier():
@@ -227,7 +238,8 @@ def main():
     if rank == 0:
         sampler.start()
     launches0 = _lib.kernel_launches()
-    replays0 = graph.replays if graph is not None else 0
+    graphs = [g for g in (graph, graph_last) if g is not None]
+    replays0 = [g.replays for g in graphs]
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -236,8 +248,8 @@ def main():
     e1.record()
     barrier()
     launches = _lib.kernel_launches() - launches0   # launched through the library's entry points ...
-    if graph is not None:                            # ... plus the same kernels replayed from the captured graph
-        launches += (graph.replays - replays0) * graph.kernels_per_replay
+    for g, r0 in zip(graphs, replays0):              # ... plus the same kernels replayed from the captured graphs
+        launches += (g.replays - r0) * g.kernels_per_replay
     comm_t = None
     if fused and getattr(wrapped, "symm", None) is not None:
         t_ = wrapped.symm.last_timings()  # last timed step: device ms, this rank
@@ -246,7 +258,20 @@ def main():
             if ddp:
                 dist.all_reduce(ct, op=dist.ReduceOp.MAX)
             comm_t = {"exposed_grad_reduce_scatter_ms": float(ct[0]), "clip_adamw_allgather_ms": float(ct[1]),
-                      "note": "device time on the comm stream after the end of backward; max over ranks"}
+                      "note": "GPU wall-clock stamps: end of backward -> last reduce-scatter done -> optimizer + "
+                              "all-gather done; max over ranks (the first includes waiting for the slowest rank)",
+                      "algorithms": wrapped.symm.describe()}
+            if world > 1:
+                # roofline of the fused path (BASELINE.json): bytes that must cross NVLink at the measured 770 GB/s
+                # per direction per GPU, or the optimizer's HBM traffic at the measured copy rate, whichever is slower
+                nv, hbm = 770e9, 6.5e12
+                s_, e_, _ = wrapped.buckets[-1]
+                rs_ms = (e_ - s_) * 4 * (world - 1) / world / nv * 1e3          # only the last bucket is exposed
+                ag_ms = max(wrapped.total * 2 * (world - 1) / world / nv, wrapped.total / world * 30 / hbm) * 1e3
+                comm_t["roofline"] = {"exposed_rs_ms": rs_ms, "adamw_allgather_ms": ag_ms,
+                                      "fraction_rs": rs_ms / max(float(ct[0]), 1e-9),
+                                      "fraction_adamw_allgather": ag_ms / max(float(ct[1]), 1e-9),
+                                      "nvlink_gbs_per_direction": 770, "hbm_gbs": 6500}
     ms = torch.tensor([e0.elapsed_time(e1)], device=device)
     if ddp:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
@@ -285,7 +310,9 @@ def main():
                        "optimizer": "AdamW(0.9,0.95) wd0.1 clip1.0, fp32 master + bf16 compute",
                        "l2": "per-step working set (activations, 1.1 GB grads, weights) >> 126 MB L2; no flush needed",
                        "comm": getattr(wrapped, "comm", "nccl-ddp"),
-                       "cuda_graph": ("non-final micro-steps replayed from one captured graph (forward+backward)"
+                       "cuda_graph": ("every micro-step replayed from a captured graph (forward+backward; the final one "
+                                      "with its per-bucket reduce-scatter kernels)" if graph_last is not None else
+                                      "non-final micro-steps replayed from one captured graph (forward+backward)"
                                       if graph is not None else "off")},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "comm": comm_t,
             "loss_first": loss0, "loss_last": float(loss),

@@ -9,9 +9,9 @@
 
 Additions: ``data_root`` is a parameter (the reference hard-codes ``edu_fineweb10B``), the
 batch is staged in pinned host memory so the H2D copy can be asynchronous, and
-``state_dict``/``load_state_dict`` allow exact resume.  ``data_root="synthetic"`` (or a
-missing directory together with ``synthetic_ok``) generates shards of the same shape, since
-the dataset cannot be downloaded here."""
+``state_dict``/``load_state_dict`` allow exact resume.  ``data_root="synthetic"`` (explicit; a
+missing directory is an error as in the reference unless ``synthetic_ok`` is passed) generates
+shards of the same shape, since the dataset cannot be downloaded here."""
 from __future__ import annotations
 
 import os
@@ -28,7 +28,7 @@ def load_tokens(filename):
 
 class DataLoaderLite:
     def __init__(self, B, T, process_rank, num_processes, split, master_process=False,
-                 data_root="edu_fineweb10B", synthetic_ok=True, pin=None):
+                 data_root="edu_fineweb10B", synthetic_ok=False, pin=None):
         self.B, self.T = B, T
         self.process_rank, self.num_processes = process_rank, num_processes
         assert split in {"train", "val"}
@@ -52,7 +52,8 @@ class DataLoaderLite:
         tag = os.path.join(root, f"n{max(need, 1 << 20)}")
         done = os.path.join(tag, ".done")
         if not os.path.exists(done):
-            # every rank may race here; writes are idempotent (same seed, atomic rename by np.save)
+            # every rank may race here: each writes the (identical, seeded) shards under temporary names and
+            # renames them into place, so a reader never sees a partial file
             write_synthetic_shards(tag, n_train=2, n_val=1, tokens_per_shard=max(need, 1 << 20))
             open(done, "w").close()
         if master_process:
@@ -113,9 +114,15 @@ class DataLoaderLite:
 
     # -- resume support (not in the reference) --------------------------------
     def state_dict(self):
-        return {"current_shard": self.current_shard, "current_position": self.current_position}
+        """Rank-independent: the shard and the position of rank 0's window (all ranks advance in lockstep, each
+        reading ``B*T*rank`` further on), so the state saved by rank 0 restores every rank."""
+        return {"current_shard": self.current_shard,
+                "base_position": self.current_position - self.B * self.T * self.process_rank}
 
     def load_state_dict(self, sd):
         self.current_shard = sd["current_shard"]
         self.tokens = load_tokens(self.shards[self.current_shard])
-        self.current_position = sd["current_position"]
+        if "base_position" in sd:
+            self.current_position = sd["base_position"] + self.B * self.T * self.process_rank
+        else:  # files written before the state became rank-independent (single-process runs)
+            self.current_position = sd["current_position"]

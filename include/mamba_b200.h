@@ -143,20 +143,38 @@ int mb_sscan_update(float* state, const void* x, long long ldx, const void* delt
                     const float* D, const void* z, long long ldz, const float* delta_bias, void* y,
                     long long ldy, int B, int Dn, int N, int softplus, cudaStream_t stream);
 
-/* ---- K19-K21: gradient reduce-scatter + global-norm clip + sharded AdamW + bf16 parameter
- * all-gather over NVLink peer memory (replaces DDP's NCCL all-reduce, clip_grad_norm_ and
- * torch.optim.AdamW of /root/reference/train.py:86,219-227).  *_ptrs are HOST arrays of `world`
- * device addresses of the peer-mapped gradient / bf16-parameter / control arenas. */
+/* ---- K19-K21: gradient reduce-scatter + global-norm clip + loss mean + sharded AdamW + bf16
+ * parameter all-gather over NVLink peer / NVLS multicast memory (replaces DDP's NCCL all-reduce,
+ * the scalar loss all-reduce, clip_grad_norm_ and torch.optim.AdamW of
+ * /root/reference/train.py:86,219-227).  *_ptrs are HOST arrays of `world` device addresses of
+ * the peer-mapped gradient / bf16-parameter / control / fp32-master arenas; mc_* are the
+ * multicast addresses of the same arenas (0 when the system has no multicast object: the P2P
+ * forms are used).  The step sequence number lives in the control block, so no launch argument
+ * changes from step to step.
+ *   algo (reduce-scatter, chosen per bucket): 0 P2P pull, 1 NVLS multimem.ld_reduce,
+ *   2 one-shot single-CTA pull for buckets under 256 KiB. */
 long long mb_comm_ctrl_words(void);
-int mb_comm_reduce_scatter(const long long* grad_ptrs, const long long* bf16_ptrs,
-                           const long long* ctrl_ptrs, int world, int rank, int bucket, long long start,
-                           long long shard_len, long long seq, float* norm_acc, int num_blocks,
-                           cudaStream_t stream);
+int mb_comm_set_timeout_ms(long long ms); /* wall-clock budget of every cross-GPU wait (default 60 s) */
+int mb_comm_reduce_scatter(const long long* grad_ptrs, const long long* ctrl_ptrs, long long mc_grad,
+                           int world, int rank, int bucket, long long start, long long shard_len,
+                           float* norm_acc, int algo, int num_blocks, cudaStream_t stream);
 int mb_comm_adamw_allgather(const long long* grad_ptrs, const long long* bf16_ptrs,
-                            const long long* ctrl_ptrs, const long long* master_ptrs, int world, int rank,
-                            long long seq, const long long* items, int n_items, float* m_state,
-                            float* v_state, const float* hyper, float* norm_acc, float* norm_out,
+                            const long long* ctrl_ptrs, const long long* master_ptrs, long long mc_bf16,
+                            long long mc_master, int world, int rank, const long long* items,
+                            int n_items, float* m_state, float* v_state, const float* hyper,
+                            float* norm_acc, float* norm_out, const float* loss_in, float* loss_out,
                             unsigned int* block_counter, int num_blocks, cudaStream_t stream);
+/* Stand-alone pieces of the same control-block protocol (not on the step path):
+ *   barrier over all ranks; mean of one fp32 scalar over ranks (validation loss,
+ *   /root/reference/train.py:147); pull of every peer's owned fp32 master shard of one bucket
+ *   (checkpointing a ZeRO-1 sharded model, /root/reference/train.py:152-163). */
+int mb_comm_barrier(const long long* ctrl_ptrs, int world, int rank, cudaStream_t stream);
+int mb_comm_scalar_mean(const long long* ctrl_ptrs, int world, int rank, const float* in, float* out,
+                        cudaStream_t stream);
+int mb_comm_gather_master(const long long* master_ptrs, const long long* ctrl_ptrs, int world, int rank,
+                          long long start, long long shard_len, int num_blocks, cudaStream_t stream);
+/* GPU wall clock (ns) written to *out when the stream gets there; usable inside graph capture. */
+int mb_timestamp(unsigned long long* out, cudaStream_t stream);
 
 #ifdef __cplusplus
 }

@@ -21,9 +21,14 @@ Gradient synchronisation has two implementations:
     from gradient-ready hooks so it overlaps the rest of backward; result is the mean.  This is
     the CPU/gloo path (BASELINE.json config 1) and the "NCCL baseline" on GPU.
   * ``comm="fused"`` — GPU only: the grad arena lives in symmetric (peer-mapped) memory and the
-    reduction is done by our own kernel (``csrc/comm_adamw.cu``) with P2P loads over NVLink,
-    fused with the 1/world scale, the grad-norm partial and — in ``FusedAdamW.step`` — clipping,
-    the sharded AdamW update and the bf16 parameter all-gather.  No NCCL call on that path.
+    reduction is done by our own kernel (``csrc/comm_adamw.cu``) with NVLS ``multimem`` loads through the
+    NVSwitch or P2P loads over NVLink, chosen per bucket size, fused with the 1/world scale, the grad-norm
+    partial and — in ``FusedAdamW.step`` — clipping, the loss mean, the sharded AdamW update and the bf16
+    parameter all-gather.  No NCCL call on that path; the validation-loss mean, the checkpoint gather of the
+    sharded fp32 masters and the barrier around it use the same control block.
+
+Collective calls (every rank must make them, in the same order): construction, ``sync_master`` /
+``state_dict``, ``all_reduce_mean``, ``barrier``, ``close``, and ``FusedAdamW.step`` / ``state_dict``.
 """
 from __future__ import annotations
 
@@ -132,9 +137,13 @@ class FusedDDP(nn.Module):
         for i, p in enumerate(self.params):
             p.register_post_accumulate_grad_hook(self._make_hook(i))
         self.grad_sync_pending = False  # fused path: reduction deferred into optimizer.step
+        self.graph_synced = False       # fused path: this step's reduce-scatters ran inside a replayed graph
         self.master_stale = False       # fused path, world > 1: fp32 masters are current only on their owner
-        module.register_state_dict_pre_hook(lambda *a, **k: self.sync_master())
+        self._in_collective_state_dict = False
+        module.register_state_dict_pre_hook(lambda *a, **k: self._state_dict_guard())
         module.register_load_state_dict_post_hook(lambda *a, **k: self.refresh_bf16())
+        names = {id(p): n for n, p in module.named_parameters()}
+        self.param_names = [names[id(p)] for p in self.params]
 
     # ------------------------------------------------------------------ API
     def forward(self, *args, **kwargs):
@@ -148,14 +157,57 @@ class FusedDDP(nn.Module):
 
     def sync_master(self):
         """Make every rank's fp32 master arena complete (owners hold the current values of their
-        shards after a fused step).  Not on the hot path: checkpointing / fp32 evaluation only."""
-        if not self.master_stale:
+        shards after a fused step): each rank pulls the other owners' shards over NVLink with our own
+        kernel, bracketed by control-block barriers.  COLLECTIVE — every rank must call it (a rank-0-only
+        call would wait for peers that never come).  Not on the hot path: checkpointing / fp32 evaluation."""
+        if not self.master_stale:   # same value on every rank: set by the fused step, cleared here
             return
-        for (s, e, _) in self.buckets:
-            sl = (e - s) // self.world
-            mine = self.flat_param[s + self.rank * sl: s + (self.rank + 1) * sl]
-            dist.all_gather_into_tensor(self.flat_param[s:e], mine.clone(), group=self.process_group)
+        self.symm.gather_master(self.buckets)
         self.master_stale = False
+
+    def _state_dict_guard(self):
+        # module.state_dict() on ONE rank cannot complete the masters (it needs every rank): fail loudly
+        # instead of deadlocking the peers (round-1 bug: rank 0 alone entered a collective at checkpoint time)
+        if self.master_stale and not self._in_collective_state_dict:
+            raise RuntimeError("fp32 masters are sharded after a fused step: call FusedDDP.state_dict() / "
+                               "FusedDDP.sync_master() on EVERY rank before reading module.state_dict()")
+
+    def all_reduce_mean(self, value: torch.Tensor) -> torch.Tensor:
+        """Mean over ranks of a scalar tensor (the validation loss of /root/reference/train.py:147) without NCCL
+        on the fused path.  COLLECTIVE."""
+        if self.world == 1:
+            return value
+        if self.symm is not None:
+            return self.symm.scalar_mean(value).to(value.dtype)
+        out = value.detach().clone()
+        dist.all_reduce(out, op=dist.ReduceOp.SUM, group=self.process_group)
+        return out / self.world
+
+    def barrier(self):
+        """All ranks reach this point before any proceeds (device-side on the fused path: the host does not
+        block, the next kernels on the current stream wait).  Used after rank-0-only work such as writing a
+        checkpoint, so that no peer spins on this rank's gradient flags for the duration of a file write."""
+        if self.world == 1:
+            return
+        if self.symm is not None:
+            torch.cuda.current_stream(self.device).synchronize()  # host-side work (the file write) is ordered too
+            self.symm.barrier()
+        else:
+            dist.barrier(group=self.process_group)
+
+    def close(self):
+        """Release the symmetric / multicast mappings (call before ``destroy_process_group``).  COLLECTIVE."""
+        if self.symm is not None:
+            self.sync_master()
+            with torch.no_grad():   # parameters survive as ordinary tensors
+                for p in self.params:
+                    p.data = p.data.clone()
+                    p.grad = None
+                    if hasattr(p, "_bf16"):
+                        del p._bf16
+            self.flat_grad = self.flat_bf16 = self.flat_param = None
+            self.symm.close()
+            self.symm = None
 
     def zero_grad(self, set_to_none=False):
         self.flat_grad.zero_()
@@ -164,8 +216,13 @@ class FusedDDP(nn.Module):
                 p.grad = self.flat_grad[off:off + p.numel()].view(p.shape)
 
     def state_dict(self, *args, **kwargs):
+        """COLLECTIVE on the fused path (gathers the sharded fp32 masters first)."""
         self.sync_master()
-        return self.module.state_dict(*args, **kwargs)
+        self._in_collective_state_dict = True
+        try:
+            return self.module.state_dict(*args, **kwargs)
+        finally:
+            self._in_collective_state_dict = False
 
     def load_state_dict(self, sd, *args, **kwargs):
         out = self.module.load_state_dict(sd, *args, **kwargs)

@@ -25,6 +25,7 @@ class FusedAdamW:
         self.betas, self.eps = betas, eps
         self.param_groups = [dict(g, lr=lr) for g in param_groups]
         self.step_count = 0
+        self.last_loss = None
         # per-element weight decay expressed as merged arena segments
         group_of = {}
         for gi, g in enumerate(self.param_groups):
@@ -62,28 +63,61 @@ class FusedAdamW:
         self.ddp.zero_grad()
 
     def state_dict(self):
+        """World-size independent optimizer state, laid out like ``torch.optim.AdamW``'s: per parameter
+        (by name) ``exp_avg`` / ``exp_avg_sq`` in the parameter's own shape, plus the step count and the
+        group learning rates.  On the fused path the moments are sharded over ranks (ZeRO-1): this is a
+        COLLECTIVE that assembles them on rank 0 — the other ranks get the scalars only.  A checkpoint
+        written at 8 GPUs resumes at 8, 2 or 1."""
+        ddp = self.ddp
+        sd = {"format": "per-param", "step": self.step_count, "lrs": [g["lr"] for g in self.param_groups],
+              "betas": tuple(self.betas), "eps": self.eps}
         if self.impl is not None:
-            sd = self.impl.state_dict()
-            sd["step"] = self.step_count
-            return sd
-        return {"step": self.step_count, "m": self.m.cpu(), "v": self.v.cpu(),
-                "lrs": [g["lr"] for g in self.param_groups]}
+            full = self.impl.full_state()
+        else:
+            full = (self.m.cpu(), self.v.cpu())
+        if full is not None:
+            state = {}
+            for name, p, off in zip(ddp.param_names, ddp.params, ddp.offsets):
+                n = p.numel()
+                state[name] = {"exp_avg": full[0][off:off + n].view(p.shape).clone(),
+                               "exp_avg_sq": full[1][off:off + n].view(p.shape).clone()}
+            sd["state"] = state
+        return sd
 
     def load_state_dict(self, sd):
+        """Every rank loads the same (full) state and keeps its own shards."""
+        ddp = self.ddp
+        assert sd.get("format") == "per-param" and "state" in sd, \
+            "optimizer state must come from FusedAdamW.state_dict() as gathered on rank 0"
+        self.step_count = int(sd["step"])
+        for g, lr in zip(self.param_groups, sd.get("lrs", [])):
+            g["lr"] = lr
+        m_full = torch.zeros(ddp.total, dtype=torch.float32)
+        v_full = torch.zeros(ddp.total, dtype=torch.float32)
+        for name, p, off in zip(ddp.param_names, ddp.params, ddp.offsets):
+            st = sd["state"][name]
+            n = p.numel()
+            m_full[off:off + n] = st["exp_avg"].reshape(-1).float()
+            v_full[off:off + n] = st["exp_avg_sq"].reshape(-1).float()
         if self.impl is not None:
-            self.step_count = sd["step"]
-            return self.impl.load_state_dict(sd)
-        self.step_count = sd["step"]
-        self.m.copy_(sd["m"])
-        self.v.copy_(sd["v"])
+            self.impl.load_full_state(m_full, v_full)
+        else:
+            self.m.copy_(m_full)
+            self.v.copy_(v_full)
 
     # -------------------------------------------------------------- step
     @torch.no_grad()
-    def step(self, max_norm=None):
+    def step(self, max_norm=None, loss=None):
+        """``loss``: optional scalar tensor (this rank's accumulated loss); its mean over ranks — the
+        ``dist.all_reduce(loss_accum, AVG)`` of /root/reference/train.py:221 — is left in ``self.last_loss``.
+        On the fused path it rides in the control-block exchange of the optimizer kernel (K21)."""
         self.step_count += 1
         if self.impl is not None:
-            return self.impl.step(self, max_norm)
+            norm = self.impl.step(self, max_norm, loss)
+            self.last_loss = self.ddp.symm.loss_out[0] if loss is not None else None
+            return norm
         ddp = self.ddp
+        self.last_loss = ddp.all_reduce_mean(loss.detach()) if loss is not None else None
         g = ddp.flat_grad
         norm = torch.linalg.vector_norm(g)
         if not bool(torch.isfinite(norm)):

@@ -19,13 +19,21 @@ def checkpoint_path(log_dir: str, step: int) -> str:
     return os.path.join(log_dir, f"model_{step:05d}.pt")
 
 
-def save_checkpoint(path, model, step, val_loss, optimizer=None, loader=None, extra=None):
+def save_checkpoint(path, model, step, val_loss, optimizer=None, loader=None, extra=None,
+                    model_state=None, optimizer_state=None):
+    """Writes the file on the calling rank only and enters no collective: with a sharded model / optimizer
+    (``FusedDDP`` + ``FusedAdamW`` at world > 1) pass ``model_state`` / ``optimizer_state`` gathered beforehand by
+    ``FusedDDP.state_dict()`` / ``FusedAdamW.state_dict()``, which every rank has to call (train.py does)."""
+    if model_state is None:
+        model_state = model.state_dict()
     sd = {k: v.detach().to("cpu", torch.float32) if v.is_floating_point() else v.detach().cpu()
-          for k, v in model.state_dict().items()}
+          for k, v in model_state.items()}
     ckpt = {"model": sd, "config": model.config, "step": step, "val_loss": val_loss,
             "config_dict": model.config.to_dict()}
-    if optimizer is not None:
-        ckpt["optimizer"] = optimizer.state_dict()
+    if optimizer_state is None and optimizer is not None:
+        optimizer_state = optimizer.state_dict()
+    if optimizer_state is not None:
+        ckpt["optimizer"] = optimizer_state
         ckpt["rng"] = {"cpu": torch.get_rng_state(),
                        "cuda": torch.cuda.get_rng_state_all() if torch.cuda.is_available() else None}
     if loader is not None and hasattr(loader, "state_dict"):

@@ -30,6 +30,9 @@ def write_synthetic_shards(root, n_train=2, n_val=1, tokens_per_shard=1 << 20, v
             else:
                 toks = rng.integers(0, vocab_size, size=tokens_per_shard)
             p = os.path.join(root, f"synthetic_{split}_{i:06d}.npy")
-            np.save(p, toks.astype(np.uint16))
+            # the temporary name must not contain "train" / "val": the loader lists shards by that substring
+            tmp = os.path.join(root, f".partial_{os.getpid()}_{len(paths):06d}.npy")
+            np.save(tmp, toks.astype(np.uint16))
+            os.replace(tmp, p)   # atomic: concurrent ranks write identical bytes, readers never see a partial file
             paths.append(p)
     return paths

@@ -15,16 +15,22 @@ from mamba_distributed_b200.parallel import FusedDDP
 from model import LMHeadModel
 
 
-def run(comm, rank, world, straggle=False):
+def run(comm, rank, world, straggle=False, graphs=False):
     torch.manual_seed(1337)
     cfg = MambaConfig(d_model=256, n_layer=2, vocab_size=2048, ssm_cfg={"layer": "Mamba2"})
     model = LMHeadModel(cfg, "cuda").cuda()
     ddp = FusedDDP(model, comm=comm, bucket_cap_mb=0.5)
     opt = model.configure_optimizers(0.1, 3e-3, "cuda", False, fused_comm=ddp)
+    g0 = g1 = None
+    if graphs:
+        from mamba_distributed_b200.parallel import MicroStepGraph
+        g0, g1 = MicroStepGraph.build_pair(ddp, 0.5, (2, 256), 2)
+        assert g0 is not None and g1 is not None
     g = torch.Generator().manual_seed(7)
-    norms, losses, snaps = [], [], []
+    norms, losses, mean_losses = [], [], []
     for step in range(3):
         opt.zero_grad()
+        lacc = torch.zeros((), device="cuda")
         for micro in range(2):
             x = torch.randint(0, 2048, (2 * world, 256), generator=g)
             y = torch.randint(0, 2048, (2 * world, 256), generator=g)
@@ -32,9 +38,14 @@ def run(comm, rank, world, straggle=False):
             ddp.require_backward_grad_sync = micro == 1
             if straggle and rank == 1 and micro == 1:
                 torch.cuda._sleep(200_000_000)  # ~0.1 s: rank 1 arrives late at every bucket
-            with torch.autocast("cuda", dtype=torch.bfloat16):
-                _, loss = ddp(xs, ys)
-            (loss / 2).backward()
+            gr = g1 if micro == 1 else g0
+            if gr is not None:
+                loss = gr(xs, ys).clone()
+            else:
+                with torch.autocast("cuda", dtype=torch.bfloat16):
+                    _, loss = ddp(xs, ys)
+                (loss / 2).backward()
+            lacc += loss.detach().float() / 2
             losses.append(loss.item())
         if comm == "fused" and step == 0 and os.environ.get("COMM_DEBUG"):
             torch.cuda.synchronize(); ddp.symm.comm_stream.synchronize()
@@ -42,7 +53,13 @@ def run(comm, rank, world, straggle=False):
             gl = [torch.zeros_like(loc) for _ in range(world)]
             dist.all_gather(gl, loc)
             print(f"[rank {rank}] local |g|={loc.norm().item():.4f} peers |g|={[g_.norm().item() for g_ in gl]}", flush=True)
-        norms.append(float(opt.step(max_norm=1.0)))
+        norms.append(float(opt.step(max_norm=1.0, loss=lacc)))
+        # K21: the loss mean that rode in the optimizer kernel's exchange == NCCL's all-reduce of the same scalar
+        ref_mean = lacc.clone()
+        dist.all_reduce(ref_mean, op=dist.ReduceOp.SUM)
+        ref_mean /= world
+        assert abs(float(opt.last_loss) - float(ref_mean)) <= 1e-5 * abs(float(ref_mean)), (float(opt.last_loss), float(ref_mean))
+        mean_losses.append(float(opt.last_loss))
     torch.cuda.synchronize()
     ddp.sync_master()
     return ddp, norms, losses
@@ -92,6 +109,16 @@ def main():
     ref, norms_ref, _ = run("allreduce", rank, world)
     fused, norms_f, _ = run("fused", rank, world, straggle=True)
     assert fused.comm == "fused" and fused.symm is not None
+    # stand-alone collectives on the control block: scalar mean (validation loss) and barrier
+    v = fused.all_reduce_mean(torch.tensor(float(rank + 1), device="cuda"))
+    assert abs(float(v) - (world + 1) / 2) < 1e-6, float(v)
+    fused.barrier()
+    # the same three steps with both micro-steps replayed from graphs (reduce-scatters captured in the second)
+    fused_g, norms_g, _ = run("fused", rank, world, straggle=True, graphs=True)
+    for a, b in zip(norms_g, norms_f):
+        assert abs(a - b) <= 2e-2 * abs(b) + 1e-3, (norms_g, norms_f)
+    errg = ((fused_g.flat_param - fused.flat_param).norm() / fused.flat_param.norm()).item()
+    assert errg < 5e-3, errg
     # tensors that kernels read in fp32 (norms, conv, A_log, dt_bias, D, embedding) must be current on
     # EVERY rank right after the fused step, without any explicit synchronisation
     for n, p_ in fused.module.named_parameters():
@@ -116,9 +143,12 @@ def main():
         assert torch.equal(mx, mn)
     assert torch.equal(fused.flat_bf16, fused.flat_param.bfloat16())
     t = fused.symm.last_timings()
+    desc = fused.symm.describe()
     if rank == 0:
-        print(f"COMM_OK world={world} norms={norms_f} exposed_rs_ms={t[0]:.3f} adamw_ag_ms={t[1]:.3f}")
+        print(f"COMM_OK world={world} norms={norms_f} exposed_rs_ms={t[0]:.3f} adamw_ag_ms={t[1]:.3f} algos={desc}")
     dist.barrier()
+    fused_g.close()
+    fused.close()
     dist.destroy_process_group()
 
 

@@ -51,11 +51,13 @@ def test_fused_step_world1_matches_clip_plus_torch_adamw():
 
 @pytest.mark.gpu
 @pytest.mark.multigpu
-@pytest.mark.parametrize("world", [2])
-def test_fused_comm_multi_gpu(world):
+@pytest.mark.parametrize("world,nvls", [(2, "1"), (2, "force"), (4, "1"), (4, "0"), (8, "1")])
+def test_fused_comm_multi_gpu(world, nvls):
+    """nvls "1": the default choice (NVLS multimem above world 2 when a multicast object exists, P2P otherwise);
+    "force": multimem kernels also at world 2; "0": the P2P kernels at any world."""
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
-    env = dict(os.environ, PYTHONPATH=ROOT)
+    env = dict(os.environ, PYTHONPATH=ROOT, MAMBA_B200_NVLS=nvls)
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
                         "--master-addr", "127.0.0.1", "--master-port", "29631",
                         os.path.join(ROOT, "tests", "_comm_worker.py")], env=env, capture_output=True, text=True,

@@ -46,3 +46,54 @@ def test_micro_step_graph_matches_eager():
     # and the optimizer step works on top of the replayed gradients
     norm = opt.step(max_norm=1.0)
     assert torch.isfinite(torch.as_tensor(float(norm)))
+
+
+def test_sync_micro_step_graph_world1_matches_eager_step():
+    """The final micro-step captured together with its reduce-scatter launches (``build_pair``): a full optimizer
+    step from two graphs must give the same norm, loss and parameters as the eager step."""
+    from mamba_distributed_b200.config import MambaConfig
+    from mamba_distributed_b200.parallel import FusedDDP, MicroStepGraph
+    from model import LMHeadModel
+    cfg = MambaConfig(d_model=256, n_layer=3, vocab_size=1024, ssm_cfg={"layer": "Mamba2"})
+    B, T, accum = 4, 512, 3
+    g = torch.Generator().manual_seed(11)
+    xs = torch.randint(0, 1024, (2, accum, B, T), generator=g).cuda()
+    ys = torch.randint(0, 1024, (2, accum, B, T), generator=g).cuda()
+
+    def run(use_graphs):
+        torch.manual_seed(0)
+        model = LMHeadModel(cfg, "cuda")
+        ddp = FusedDDP(model, bucket_cap_mb=0.5)
+        assert len(ddp.buckets) > 2
+        opt = model.configure_optimizers(0.1, 1e-3, "cuda", False, fused_comm=ddp)
+        g0 = g1 = None
+        if use_graphs:
+            g0, g1 = MicroStepGraph.build_pair(ddp, 1.0 / accum, (B, T), accum)
+            assert g0 is not None and g1 is not None and g1.kernels_per_replay > g0.kernels_per_replay
+        norms, losses = [], []
+        for step in range(2):
+            opt.zero_grad()
+            for i in range(accum):
+                last = i == accum - 1
+                ddp.require_backward_grad_sync = last
+                gr = g1 if last else g0
+                if gr is not None:
+                    losses.append(float(gr(xs[step, i], ys[step, i])))
+                else:
+                    with torch.autocast("cuda", dtype=torch.bfloat16):
+                        _, loss = ddp(xs[step, i], ys[step, i])
+                    (loss / accum).backward()
+                    losses.append(float(loss))
+            norms.append(float(opt.step(max_norm=1.0)))
+        torch.cuda.synchronize()
+        t = ddp.symm.last_timings()
+        assert t is not None and t[0] >= 0 and t[1] > 0
+        return norms, losses, ddp.flat_param.clone()
+
+    n_e, l_e, p_e = run(False)
+    n_g, l_g, p_g = run(True)
+    for a, b in zip(n_e, n_g):
+        assert abs(a - b) <= 2e-2 * abs(a), (n_e, n_g)
+    for a, b in zip(l_e, l_g):
+        assert abs(a - b) < 5e-3, (l_e, l_g)
+    assert float((p_e - p_g).norm() / p_e.norm()) < 5e-3

@@ -72,8 +72,9 @@ def parse_args(argv=None):
     p.add_argument("--timers", action="store_true", help="print per-phase device timings")
     p.add_argument("--metrics_jsonl", default=None,
                    help="append one JSON object per step (loss, lr, norm, dt, tok/s, phase timings, exposed comm ms)")
-    p.add_argument("--cuda_graphs", type=int, default=1,
-                   help="replay the non-final micro-steps of a step from one captured CUDA graph (GPU + fused kernels only)")
+    p.add_argument("--cuda_graphs", type=int, default=2,
+                   help="2: replay every micro-step from a captured CUDA graph (the final one with its reduce-scatter "
+                        "kernels); 1: only the non-final micro-steps; 0: eager (GPU + fused kernels only)")
     return p.parse_args(argv)
 
 
@@ -131,7 +132,8 @@ def main(argv=None):
     if args.resume:
         resume = load_checkpoint(args.resume, map_location="cpu")
         model.load_state_dict(resume["model"])
-        start_step = int(resume["step"]) + 1
+        # the checkpoint of step S is written before step S trains: resume AT S (same LR, same batch)
+        start_step = int(resume["step"])
     model = FusedDDP(model, device_ids=[ddp_local_rank] if use_cuda else None, comm=args.comm)
     raw_model = model.module
 
@@ -161,8 +163,8 @@ def main(argv=None):
         return torch.autocast(device_type=device_type, dtype=torch.bfloat16)
 
     from mamba_distributed_b200.ops import native_enabled
-    want_graph = bool(args.cuda_graphs) and use_cuda and grad_accum_steps > 1 and native_enabled()
-    micro_graph = None
+    want_graph = bool(args.cuda_graphs) and use_cuda and native_enabled()
+    micro_graph = last_graph = None
 
     for step in range(start_step, max_steps):
         t0 = time.time()
@@ -180,14 +182,22 @@ def main(argv=None):
                         logits, loss = model(x, y)
                     val_loss_accum += loss.detach().float() / args.val_steps
             if ddp:
-                dist.all_reduce(val_loss_accum, op=dist.ReduceOp.AVG)
+                val_loss_accum = model.all_reduce_mean(val_loss_accum)   # own kernel on the fused path, no NCCL
+            ckpt_now = step > 0 and (step % args.ckpt_every == 0 or last_step) and not (resume is not None and step == start_step)
+            if ckpt_now:
+                # collectives, entered by EVERY rank: the fp32 masters and the Adam moments are sharded over ranks
+                model_state = model.state_dict()
+                optimizer_state = optimizer.state_dict()
             if master_process:
                 print(f"validation loss: {val_loss_accum.item():.4f}")
                 with open(log_file, "a") as f:
                     f.write(f"{step} val {val_loss_accum.item():.4f}\n")
-                if step > 0 and (step % args.ckpt_every == 0 or last_step):
-                    save_checkpoint(checkpoint_path(log_dir, step), raw_model, step,
-                                    val_loss_accum.item(), optimizer=optimizer, loader=train_loader)
+                if ckpt_now:   # rank 0 only serialises; no collective inside (reference: train.py:152-163)
+                    save_checkpoint(checkpoint_path(log_dir, step), raw_model, step, val_loss_accum.item(),
+                                    loader=train_loader, model_state=model_state, optimizer_state=optimizer_state)
+            if ckpt_now:
+                del model_state, optimizer_state
+                model.barrier()   # peers do not run ahead into a step while rank 0 is still writing the file
 
         # ---- sampling (train.py:166-199) ---------------------------------------------------
         if (step > 0 and step % args.sample_every == 0) or last_step:
@@ -217,17 +227,22 @@ def main(argv=None):
             # first training step: capture forward + backward of a no-sync micro-step (its warm-up passes
             # leave gradients in the arena, which the zero_grad below clears)
             from mamba_distributed_b200.parallel import MicroStepGraph
-            micro_graph = MicroStepGraph.build_if_it_fits(model, 1.0 / grad_accum_steps, (B, T), device=device)
-            want_graph = micro_graph is not None
+            if args.cuda_graphs >= 2 and model.symm is not None:
+                micro_graph, last_graph = MicroStepGraph.build_pair(model, 1.0 / grad_accum_steps, (B, T),
+                                                                    grad_accum_steps, device=device)
+            elif grad_accum_steps > 1:
+                micro_graph = MicroStepGraph.build_if_it_fits(model, 1.0 / grad_accum_steps, (B, T), device=device)
+            want_graph = False
         optimizer.zero_grad()
         loss_accum = torch.zeros((), device=device)
         for micro_step in range(grad_accum_steps):
             with timer("data"):
                 x, y = train_loader.next_batch_device(device)
             model.require_backward_grad_sync = micro_step == grad_accum_steps - 1
-            if micro_graph is not None and micro_step != grad_accum_steps - 1:
+            g = micro_graph if micro_step != grad_accum_steps - 1 else last_graph
+            if g is not None:
                 with timer("fwd+bwd (graph)"):
-                    loss_accum += micro_graph(x, y).float() / grad_accum_steps
+                    loss_accum += g(x, y).float() / grad_accum_steps
                 continue
             with timer("fwd"):
                 with autocast():
@@ -236,13 +251,15 @@ def main(argv=None):
                 loss_accum += loss.detach().float()
             with timer("bwd"):
                 loss.backward()
-        if ddp:
-            dist.all_reduce(loss_accum, op=dist.ReduceOp.AVG)
         lr = get_lr(step)
         for param_group in optimizer.param_groups:
             param_group["lr"] = lr
         with timer("sync+clip+adamw"):
-            norm = optimizer.step(max_norm=args.grad_clip)
+            # the loss mean over ranks (reference: dist.all_reduce(loss_accum, AVG), train.py:221) rides in the
+            # optimizer kernel's control-block exchange on the fused path
+            norm = optimizer.step(max_norm=args.grad_clip, loss=loss_accum if ddp else None)
+            if ddp:
+                loss_accum = optimizer.last_loss
         if device_type == "cuda":
             torch.cuda.synchronize()
         dt = time.time() - t0
@@ -268,6 +285,7 @@ def main(argv=None):
                 with open(args.metrics_jsonl, "a") as f:
                     f.write(json.dumps(rec) + "\n")
 
+    model.close()   # releases the symmetric / multicast mappings (collective)
     if ddp:
         dist.destroy_process_group()
 
