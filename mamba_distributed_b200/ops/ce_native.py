@@ -11,7 +11,7 @@ from __future__ import annotations
 import torch
 
 from ._lib import call
-from .native import bf16_weight, gemm_nn, gemm_nt, gemm_tn_acc, grad_buffer, notify_grad_ready
+from .native import bf16_weight, gemm_nn, gemm_nt, gemm_tn_acc, grad_buffer
 
 SLAB_ROWS = 4096   # upper bound when the device is unknown; see slab_rows()
 
@@ -69,13 +69,12 @@ class LinearCrossEntropyFn(torch.autograd.Function):
     def backward(ctx, g):
         dh, dW, weight = ctx.saved_tensors
         assert ctx.reduction in ("mean", "sum"), "per-token losses are differentiable only via the PyTorch path"
-        dh = dh * g.to(dh.dtype)
+        # scale in fp32 (a bf16-rounded 1/grad_accum would skew the backbone gradient against dW for accumulation
+        # counts that are not powers of two); g stays on the device: float(g) would synchronise the host with the
+        # GPU at the start of every backward (and cannot be captured in a CUDA graph)
+        dh = (dh.float() * g.float()).to(dh.dtype)
         if weight.requires_grad:
-            # g stays on the device: float(g) would synchronise the host with the GPU at the start of every
-            # backward (and cannot be captured in a CUDA graph)
             grad_buffer(weight).addcmul_(dW, g.to(dW.dtype))
-            if not getattr(weight, "_tied_embedding", False):
-                notify_grad_ready(weight)
         return dh, None, None, None
 
 

@@ -83,7 +83,7 @@ def selective_state_update(state, x, dt, A, B, C, D=None, z=None, dt_bias=None, 
 def linear(x, weight, bias=None):
     """K16: ``x @ weight.T (+ bias)``; tcgen05 GEMM on the native path."""
     if use_native(x):
-        return _native().linear(x, weight, bias, notify=not getattr(weight, "_tied_embedding", False))
+        return _native().linear(x, weight, bias)
     return F.linear(x, weight, bias)
 
 

@@ -15,16 +15,10 @@ Data-flow conventions (B200-first):
 """
 from __future__ import annotations
 
-import os
-
 import torch
 
-from . import _lib, ref
+from . import _lib
 from ._lib import call
-
-_SSD_IMPL = os.environ.get("MAMBA_B200_SSD", "native")     # "native" | "torch"
-_GEMM_IMPL = os.environ.get("MAMBA_B200_GEMM", "native")   # "native" | "cublas" (comparison arm)
-_CE_IMPL = os.environ.get("MAMBA_B200_CE", "native")       # "native" | "chunked"
 
 _scratch = {}
 
@@ -73,13 +67,6 @@ def inplace_grad(p):
     return g if (g.dtype == torch.float32 and g.is_contiguous()) else None
 
 
-def notify_grad_ready(p: torch.Tensor):
-    """Nothing to do: autograd runs the parameter's post-accumulate-grad hooks right after the
-    node that called us returns (even though we return ``None`` for the weight), which is when the
-    wgrad kernel has been enqueued.  ``FusedDDP`` listens there."""
-    return None
-
-
 # ------------------------------------------------------------------------------------------
 # GEMM wrappers (K16)
 # ------------------------------------------------------------------------------------------
@@ -98,11 +85,6 @@ def gemm_nt(x, w, out=None, bias=None, out_dtype=torch.bfloat16):
     N = w.shape[0]
     if out is None:
         out = torch.empty(M, N, dtype=out_dtype, device=x.device)
-    if _GEMM_IMPL == "cublas":
-        torch.matmul(x, w.t(), out=out) if out.dtype == x.dtype else out.copy_(torch.matmul(x, w.t()))
-        if bias is not None:
-            out.add_(bias.to(out.dtype))
-        return out
     call("mb_gemm_bf16", x, x.stride(0), 0, w, w.stride(0), 0, out, out.stride(0),
          0 if out.dtype == torch.bfloat16 else 1, bias, M, N, K, 1.0)
     return out
@@ -115,9 +97,6 @@ def gemm_nn(dy, w, out=None):
     K = w.shape[1]
     if out is None:
         out = torch.empty(M, K, dtype=torch.bfloat16, device=dy.device)
-    if _GEMM_IMPL == "cublas":
-        torch.matmul(dy, w, out=out)
-        return out
     call("mb_gemm_bf16", dy, dy.stride(0), 0, w, w.stride(0), 1, out, out.stride(0), 0, None, M, K, N, 1.0)
     return out
 
@@ -128,9 +107,6 @@ def gemm_tn_acc(dy, x, grad, alpha=1.0):
     M, N = dy.shape
     K = x.shape[1]
     assert grad.dtype == torch.float32 and grad.shape == (N, K) and grad.stride(1) == 1
-    if _GEMM_IMPL == "cublas":
-        grad.add_(torch.matmul(dy.t(), x).float(), alpha=alpha)
-        return grad
     call("mb_gemm_bf16", dy, dy.stride(0), 1, x, x.stride(0), 1, grad, grad.stride(0), 2, None, N, K, M, alpha)
     return grad
 
@@ -139,7 +115,7 @@ class LinearFn(torch.autograd.Function):
     """y = x W^T (+ b).  dW is accumulated in place into ``weight.grad`` (see module docstring)."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, notify):
+    def forward(ctx, x, weight, bias):
         x2 = _rows(x)
         if x2.dtype != torch.bfloat16:
             x2 = x2.to(torch.bfloat16)
@@ -148,7 +124,6 @@ class LinearFn(torch.autograd.Function):
         w = bf16_weight(weight)
         y = gemm_nt(x2, w, bias=bias.float() if bias is not None else None)
         ctx.save_for_backward(x2, weight, bias, w)
-        ctx.notify = notify
         ctx.xshape = x.shape
         ctx.xdtype = x.dtype
         return y.view(*x.shape[:-1], w.shape[0])
@@ -164,19 +139,17 @@ class LinearFn(torch.autograd.Function):
             dx = gemm_nn(dy2, w).view(ctx.xshape).to(ctx.xdtype)
         if weight.requires_grad:
             gemm_tn_acc(dy2, x2, grad_buffer(weight))
-            if ctx.notify:
-                notify_grad_ready(weight)
         db = dy2.float().sum(0) if bias is not None and ctx.needs_input_grad[2] else None
-        return dx, None, db, None
+        return dx, None, db
 
 
-def linear(x, weight, bias=None, notify=True):
+def linear(x, weight, bias=None):
     N, K = weight.shape
     if K % 8 != 0 or N % 8 != 0:
         # TMA needs 16-byte row strides; shapes this small are never on the hot path
         return torch.nn.functional.linear(x, weight.to(x.dtype) if x.dtype != weight.dtype else weight,
                                           bias if bias is None else bias.to(x.dtype))
-    return LinearFn.apply(x, weight, bias, notify)
+    return LinearFn.apply(x, weight, bias)
 
 
 # ------------------------------------------------------------------------------------------
@@ -388,7 +361,6 @@ class EmbeddingFn(torch.autograd.Function):
             V, D = weight.shape
             g = grad_buffer(weight)
             call("mb_embedding_bwd", ids, dout.contiguous().float(), g, ids.numel(), D, V)
-            notify_grad_ready(weight)
         return None, None
 
 
@@ -401,15 +373,15 @@ def embedding(ids, weight):
 # K7-K12: SSD.  (kernels live in ops/ssd_native.py; "torch" = oracle math on the GPU)
 # ------------------------------------------------------------------------------------------
 def ssd_combined(x, dt, A, B, C, chunk_size, D, z, dt_bias, dt_softplus):
-    if _SSD_IMPL == "native":
-        from . import ssd_native
-        return ssd_native.ssd_combined(x, dt, A, B, C, chunk_size, D, z, dt_bias, dt_softplus)
-    return ref.ssd_chunked_ref(x, dt, A, B, C, chunk_size, D, z, dt_bias, dt_softplus)
+    from . import ssd_native
+    return ssd_native.ssd_combined(x, dt, A, B, C, chunk_size, D, z, dt_bias, dt_softplus)
 
 
 def selective_scan(u, delta, A, B, C, D, z, delta_bias, delta_softplus):
-    from . import sscan_native
-    return sscan_native.selective_scan(u, delta, A, B, C, D, z, delta_bias, delta_softplus)
+    """K4/K5: the Mamba-1 selective scan kernels (``csrc/sscan.cu``).  A missing extension is an error here like
+    everywhere else in this module — no quiet detour through the PyTorch oracle."""
+    from . import sscan_kernels
+    return sscan_kernels.selective_scan(u, delta, A, B, C, D, z, delta_bias, delta_softplus)
 
 
 # ------------------------------------------------------------------------------------------
@@ -459,7 +431,6 @@ class Mamba2MixerFn(torch.autograd.Function):
         # out_proj
         dyn = gemm_nn(dout2, w_out)
         gemm_tn_acc(dout2, yn, grad_buffer(out_w))
-        notify_grad_ready(out_w)
         # gated norm: dy (SSD output grad) and dz (written into the z columns of d(zxbcdt))
         dzxbcdt = torch.empty_like(zxbcdt)
         dy = torch.empty_like(y)
@@ -483,7 +454,6 @@ class Mamba2MixerFn(torch.autograd.Function):
         # in_proj
         du = gemm_nn(dzxbcdt, w_in).view(Bsz, T, dm)
         gemm_tn_acc(dzxbcdt, u2, grad_buffer(in_w))
-        notify_grad_ready(in_w)
         small = red_out is not None
         return (du.to(ctx.udtype), None,
                 None if g_cw is not None else dcw.view(conv_w.shape).to(conv_w.dtype),

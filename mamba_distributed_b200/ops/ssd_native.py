@@ -2,14 +2,13 @@
 
 ``ssd_fwd`` / ``ssd_bwd`` are the pieces the fused mixer node (``native.Mamba2MixerFn``) calls
 with the in-place column-slice conventions; ``ssd_combined`` is the standalone autograd op.
-``MAMBA_B200_SSD=torch`` swaps the kernels for the oracle math running as PyTorch ops on the
-GPU (debug / comparison arm only)."""
+Geometries the tensor-core kernels are not specialised for (anything but chunk 256 / headdim 64 /
+d_state 128, which every benchmark config uses) run the oracle math as PyTorch ops on the GPU."""
 from __future__ import annotations
 
 import torch
 
 from . import ref
-from .native import _SSD_IMPL
 
 
 def _views(xBC, zxbcdt, Bsz, T, cfg):
@@ -47,8 +46,6 @@ def _torch_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D
 def _use_torch(cfg):
     """The tensor-core kernels are specialised for chunk 256 / headdim 64 / d_state 128 (every
     benchmark config); other geometries run the oracle math on the GPU."""
-    if _SSD_IMPL == "torch":
-        return True
     from . import ssd_kernels
     return not ssd_kernels.supported(cfg)
 
