@@ -124,7 +124,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   if (warp == 0) {
     // ================================ TMA producer =====================================
-    if (lane == 0) {
+    // all 32 lanes run the loops and the waits; one elected lane issues the TMA loads of a stage (see
+    // "warp-uniform single-lane issue" in ptx.cuh)
+    {
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = worker; tile < num_tiles; tile += nworkers) {
@@ -134,54 +136,56 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int kb0 = split * kb_per_split;
         const int kb1 = min(kb0 + kb_per_split, kblocks);
         for (int kb = kb0; kb < kb1; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_wait_warp(&empty_bar[stage], phase ^ 1);
           uint8_t* a_dst = sA + stage * Cfg::A_BYTES;
           uint8_t* b_dst = sB + stage * Cfg::B_BYTES;
-          if (PAIR) {
-            // both CTAs' loads complete on the even CTA's barrier, which expects the bytes of both
-            if (crank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * (Cfg::A_BYTES + Cfg::B_BYTES));
-            if (A_MAJOR == MAJOR_K) {
-              tma_load_2d_pair(a_dst, &tmA, &full_bar[stage], kb * BK, m_blk * BM);
+          if (elect_one()) {
+            if (PAIR) {
+              // both CTAs' loads complete on the even CTA's barrier, which expects the bytes of both
+              if (crank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * (Cfg::A_BYTES + Cfg::B_BYTES));
+              if (A_MAJOR == MAJOR_K) {
+                tma_load_2d_pair(a_dst, &tmA, &full_bar[stage], kb * BK, m_blk * BM);
+              } else {
+#pragma unroll
+                for (int j = 0; j < BM / 64; ++j)
+                  tma_load_2d_pair(a_dst + j * (BK * 128), &tmA, &full_bar[stage], m_blk * BM + j * 64, kb * BK);
+              }
+              if (B_MAJOR == MAJOR_K) {  // tmB here is the half-height (BN/2 rows) box
+                // the MMA of a narrow last N tile (see n_eff in the MMA issuer) takes its second half of the B rows
+                // from the odd CTA, so that CTA fetches from n0 + n_eff / 2 instead of n0 + BN / 2
+                tma_load_2d_pair(b_dst, &tmB, &full_bar[stage], kb * BK, n_blk * BN + crank * (tile_n_eff(Ng, n_blk, BN) / 2));
+              } else {
+#pragma unroll
+                for (int j = 0; j < BN / 128; ++j)
+                  tma_load_2d_pair(b_dst + j * (BK * 128), &tmB, &full_bar[stage],
+                                   n_blk * BN + (crank * (BN / 128) + j) * 64, kb * BK);
+              }
             } else {
+              mbar_arrive_expect_tx(&full_bar[stage], Cfg::A_BYTES + Cfg::B_BYTES);
+              if (A_MAJOR == MAJOR_K) {
+                tma_load_2d(a_dst, &tmA, &full_bar[stage], kb * BK, m_blk * BM);
+              } else {
 #pragma unroll
-              for (int j = 0; j < BM / 64; ++j)
-                tma_load_2d_pair(a_dst + j * (BK * 128), &tmA, &full_bar[stage], m_blk * BM + j * 64, kb * BK);
+                for (int j = 0; j < BM / 64; ++j)
+                  tma_load_2d(a_dst + j * (BK * 128), &tmA, &full_bar[stage], m_blk * BM + j * 64, kb * BK);
+              }
+              if (B_MAJOR == MAJOR_K) {
+                tma_load_2d(b_dst, &tmB, &full_bar[stage], kb * BK, n_blk * BN);
+              } else {
+#pragma unroll
+                for (int j = 0; j < BN / 64; ++j)
+                  tma_load_2d(b_dst + j * (BK * 128), &tmB, &full_bar[stage], n_blk * BN + j * 64, kb * BK);
+              }
             }
-            if (B_MAJOR == MAJOR_K) {  // tmB here is the half-height (BN/2 rows) box
-              // the MMA of a narrow last N tile (see n_eff in the MMA issuer) takes its second half of the B rows from
-              // the odd CTA, so that CTA fetches from n0 + n_eff / 2 instead of n0 + BN / 2
-              tma_load_2d_pair(b_dst, &tmB, &full_bar[stage], kb * BK, n_blk * BN + crank * (tile_n_eff(Ng, n_blk, BN) / 2));
-            } else {
-#pragma unroll
-              for (int j = 0; j < BN / 128; ++j)
-                tma_load_2d_pair(b_dst + j * (BK * 128), &tmB, &full_bar[stage],
-                                 n_blk * BN + (crank * (BN / 128) + j) * 64, kb * BK);
-            }
-            if (++stage == STAGES) { stage = 0; phase ^= 1; }
-            continue;
           }
-          mbar_arrive_expect_tx(&full_bar[stage], Cfg::A_BYTES + Cfg::B_BYTES);
-          if (A_MAJOR == MAJOR_K) {
-            tma_load_2d(a_dst, &tmA, &full_bar[stage], kb * BK, m_blk * BM);
-          } else {
-#pragma unroll
-            for (int j = 0; j < BM / 64; ++j)
-              tma_load_2d(a_dst + j * (BK * 128), &tmA, &full_bar[stage], m_blk * BM + j * 64, kb * BK);
-          }
-          if (B_MAJOR == MAJOR_K) {
-            tma_load_2d(b_dst, &tmB, &full_bar[stage], kb * BK, n_blk * BN);
-          } else {
-#pragma unroll
-            for (int j = 0; j < BN / 64; ++j)
-              tma_load_2d(b_dst + j * (BK * 128), &tmB, &full_bar[stage], n_blk * BN + j * 64, kb * BK);
-          }
+          __syncwarp();
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ========================================
-    if (lane == 0 && (!PAIR || crank == 0)) {
+    if (!PAIR || crank == 0) {   // whole warp; the MMAs / commits of a k-block are issued by one elected lane
       constexpr uint32_t idesc_full = make_idesc_bf16(PAIR ? 2 * BM : BM, BN, A_MAJOR, B_MAJOR);
       // K-major: +32 B per UMMA_K inside the swizzle row; MN-major: +16 k-rows * 128 B
       constexpr uint32_t a_kstep = A_MAJOR == MAJOR_K ? 32 : 16 * 128;
@@ -208,7 +212,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #ifdef MB_GEMM_TIMING
         const long long tt0 = clock64();
 #endif
-        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        mbar_wait_warp(&tempty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
 #ifdef MB_GEMM_TIMING
         const long long tt1 = clock64();
@@ -219,29 +223,33 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #ifdef MB_GEMM_TIMING
           const long long tf0 = clock64();
 #endif
-          mbar_wait(&full_bar[stage], phase);
+          mbar_wait_warp(&full_bar[stage], phase);
           tc_fence_after();
 #ifdef MB_GEMM_TIMING
           twait_full += clock64() - tf0;
 #endif
           const uint32_t a_addr = smem_u32(sA + stage * Cfg::A_BYTES);
           const uint32_t b_addr = smem_u32(sB + stage * Cfg::B_BYTES);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k) {
-            const uint64_t da = make_smem_desc(a_addr + k * a_kstep, a_lbo, 1024);
-            const uint64_t db = make_smem_desc(b_addr + k * b_kstep, b_lbo, 1024);
-            if (PAIR) mma_bf16_ss_pair(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-            else mma_bf16_ss(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < BK / 16; ++k) {
+              const uint64_t da = make_smem_desc(a_addr + k * a_kstep, a_lbo, 1024);
+              const uint64_t db = make_smem_desc(b_addr + k * b_kstep, b_lbo, 1024);
+              if (PAIR) mma_bf16_ss_pair(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+              else mma_bf16_ss(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            }
+            // frees this smem stage when the MMAs above retire (with PAIR in both CTAs: the MMA read both stages)
+            if (PAIR) mma_commit_pair_mc(&empty_bar[stage], 0b11);
+            else mma_commit(&empty_bar[stage]);
           }
-          // frees this smem stage when the MMAs above retire (with PAIR in both CTAs: the MMA read both stages)
-          if (PAIR) mma_commit_pair_mc(&empty_bar[stage], 0b11);
-          else mma_commit(&empty_bar[stage]);
+          __syncwarp();
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
         // accumulator complete -> epilogue (of both CTAs with PAIR)
-        if (PAIR) mma_commit_pair_mc(&tfull_bar[acc], 0b11); else mma_commit(&tfull_bar[acc]);
+        if (elect_one()) { if (PAIR) mma_commit_pair_mc(&tfull_bar[acc], 0b11); else mma_commit(&tfull_bar[acc]); }
+        __syncwarp();
 #ifdef MB_GEMM_TIMING
-        if (blockIdx.x == 4 && local < 30)
+        if (blockIdx.x == 4 && local < 30 && lane == 0)
           printf("G tile %d start %lld wait_acc %lld wait_full %lld issue_total %lld\n", local, tt0, tt1 - tt0, twait_full, clock64() - tt0);
 #endif
       }
@@ -273,7 +281,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           if (col0 >= Ng) break;  // warp-uniform
           uint8_t* buf = my_stage + (st_iter & 1) * 4096;
           if (st_iter >= 2) {  // the store issued two slabs ago must have finished reading this buffer
-            if (lane == 0) tma_store_wait_read<1>();
+            if (elect_one()) tma_store_wait_read<1>();
             __syncwarp();
           }
 #pragma unroll
@@ -301,7 +309,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
           fence_proxy_async_smem();
           __syncwarp();
-          if (lane == 0) {
+          if (elect_one()) {   // always the same lane (elect.sync is deterministic): bulk groups are per thread
             tma_store_2d(&tmD, buf, col0, m_blk * BM + lane_grp * 32);
             tma_store_commit();
           }
@@ -364,7 +372,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         else mbar_arrive(&tempty_bar[acc]);
       }
     }
-    if (TMA_STORE && lane == 0) tma_store_wait<0>();
+    if (TMA_STORE && elect_one()) tma_store_wait<0>();
   }
   tc_fence_before();
   __syncthreads();

@@ -58,6 +58,21 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// Same wait for a warp whose 32 lanes all wait together (the single-lane-issue warps below): the loop condition
+// is a vote, so every lane leaves in the same iteration and the warp stays converged — which is what lets ptxas
+// keep the following descriptor / address arithmetic in uniform registers.
+__device__ __forceinline__ void mbar_wait_warp(uint64_t* bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!__any_sync(0xffffffffu, mbar_try_wait(bar, parity))) {
+    if (++spins > (1u << 24)) {
+      if ((threadIdx.x & 31) == 0)
+        printf("mbar_wait timeout: block (%d,%d,%d) thread %d parity %u\n", blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x, parity);
+      __trap();
+    }
+  }
+  __syncwarp();
+}
+
 // ------------------------------------------------------------------ proxies / fences
 __device__ __forceinline__ void fence_proxy_async_smem() {
   // generic-proxy smem writes -> visible to the async proxy (TMA, tcgen05.mma operand reads)
@@ -199,6 +214,24 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint64_t* bar, uint32_t rank
       "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}"
       ::"r"(smem_u32(bar)), "r"(rank) : "memory");
 }
+
+// ------------------------------------------------------------------ warp-uniform single-lane issue
+// How the MMA-issuing and TMA-producing warps are written (all tcgen05 kernels of this library):
+//
+//     for (...) {                       // executed by all 32 lanes, converged
+//       mbar_wait_warp(...);            // vote-terminated spin: the warp stays converged
+//       if (elect_one()) { mma...; commit; }   // one lane, chosen by elect.sync
+//       __syncwarp();
+//     }
+//
+// Why: UTCHMMA / UTMALDG / UTCBAR take their descriptors, coordinates and addresses from UNIFORM registers.
+// With the whole role inside `if (lane == 0)` ptxas cannot use the uniform datapath (the warp is diverged): it
+// computes the operands in ordinary registers and moves each over with an ELECT + R2UR.BROADCAST retry loop —
+// ~20 serialised instructions, ~100 cycles, per MMA, more than the 32-64 cycles the tensor core needs for one
+// N <= 256 MMA.  A single issuing thread was the bottleneck of every tcgen05 kernel here (SSD scan: ~120 cycles
+// per N = 64 MMA measured).  With converged loops and an elect.sync branch ptxas knows exactly one lane is active,
+// keeps the descriptor arithmetic in uniform registers (ULOP3 / UIADD3) and emits the MMAs of a k-block
+// back to back.
 
 // ------------------------------------------------------------------ TMEM -> registers
 // 32 lanes x 32-bit, x32 columns: thread t of the warp receives lane (lane_base + t), columns

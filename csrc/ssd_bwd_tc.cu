@@ -43,7 +43,7 @@ ssd_dcb_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__
   const int cj0 = blk == 2 ? 128 : 0;
   const int valid = min(kL, T - c * kL);
 
-  if (tid == 0) {
+  if (warp == 0 && elect_one()) {
     mbar_init(bar, 1); mbar_init(&tile_bar[0], 1); mbar_init(&tile_bar[1], 1); mbar_init(ld_bar, 1);
     fence_mbar_init();
     // C / B tiles for the CB block: two 64-column boxes each, straight away (they borrow the per-head buffers)
@@ -66,16 +66,19 @@ ssd_dcb_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__
   {
     uint8_t* sCt = smem;
     uint8_t* sBt = smem + 2 * 128 * 128;
-    if (tid == 0) {
-      mbar_wait(ld_bar, 0);
+    if (warp == 0) {  // converged warp, one elected lane issues (ptx.cuh: warp-uniform single-lane issue)
+      mbar_wait_warp(ld_bar, 0);
       tc_fence_after();
       constexpr uint32_t idesc = make_idesc_bf16(128, 128, MAJOR_K, MAJOR_K);
       const uint32_t a_addr = smem_u32(sCt), b_addr = smem_u32(sBt);
+      if (elect_one()) {
 #pragma unroll
-      for (int k = 0; k < kN / 16; ++k)
-        mma_bf16_ss(tCB, desc_kmajor(a_addr, 128, k >> 2, k & 3), desc_kmajor(b_addr, 128, k >> 2, k & 3), idesc,
-                    k > 0 ? 1u : 0u);
-      mma_commit(bar);
+        for (int k = 0; k < kN / 16; ++k)
+          mma_bf16_ss(tCB, desc_kmajor(a_addr, 128, k >> 2, k & 3), desc_kmajor(b_addr, 128, k >> 2, k & 3), idesc,
+                      k > 0 ? 1u : 0u);
+        mma_commit(bar);
+      }
+      __syncwarp();
     }
     mbar_wait(bar, phase);
     phase ^= 1;
@@ -99,7 +102,7 @@ ssd_dcb_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__
     const uint32_t ad = smem_u32(s_ad + bsel * 2 * kL);
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(ad + tid * 4), "l"(av + sb + tid) : "memory");
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(ad + (kL + tid) * 4), "l"(dtv + sb + tid) : "memory");
-    if (tid == 0) {  // dY rows / X rows of this head by TMA: one 128 x 64 box each, 128B-swizzled
+    if (warp == 0 && elect_one()) {  // dY rows / X rows of this head by TMA: one 128 x 64 box each, 128B-swizzled
       uint8_t* t0 = smem + bsel * 2 * 128 * 128;
       mbar_arrive_expect_tx(&tile_bar[bsel], 2 * 128 * 128);
       tma_load_3d(t0, &tmDY, &tile_bar[bsel], h * kP, c * kL + ri0, b);
@@ -118,15 +121,18 @@ ssd_dcb_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__
     else cp_async_wait<0>();
     fence_proxy_async_smem();
     __syncthreads();
-    if (tid == 0) {
-      mbar_wait(&tile_bar[hh & 1], (hh >> 1) & 1);
+    if (warp == 0) {
+      mbar_wait_warp(&tile_bar[hh & 1], (hh >> 1) & 1);
       tc_fence_after();
       constexpr uint32_t idesc = make_idesc_bf16(128, 128, MAJOR_K, MAJOR_K);
       const uint32_t a_addr = smem_u32(sDY), b_addr = smem_u32(sX);
+      if (elect_one()) {
 #pragma unroll
-      for (int ks = 0; ks < 4; ++ks)
-        mma_bf16_ss(tmem, desc_kmajor(a_addr, 128, 0, ks), desc_kmajor(b_addr, 128, 0, ks), idesc, ks > 0 ? 1u : 0u);
-      mma_commit(bar);
+        for (int ks = 0; ks < 4; ++ks)
+          mma_bf16_ss(tmem, desc_kmajor(a_addr, 128, 0, ks), desc_kmajor(b_addr, 128, 0, ks), idesc, ks > 0 ? 1u : 0u);
+        mma_commit(bar);
+      }
+      __syncwarp();
     }
     {  // per (lane group, column) decay factors for the blocks strictly below the diagonal, where
        // exp(a_i - a_j) = exp(a_i - a_ref) exp(a_ref - a_j) with both factors <= 1 (a_ref = first row of the group)
@@ -251,7 +257,7 @@ ssd_dbdc_kernel(const __grid_constant__ CUtensorMap tmG,    // dCB   [B*nc*G*256
   const size_t row_base = (size_t)b * T + (size_t)c * kL;
   const int g_row0 = (bc * G + g) * kL;   // first row of this (b, c, g) block in the dCB matrix
 
-  if (tid == 0) {
+  if (warp == 0 && elect_one()) {
     for (int i = 0; i < kDbdcStages; ++i) { mbar_init(&bars[i], 1); mbar_init(&full[i], 1); }
     fence_mbar_init();
   }
@@ -275,7 +281,7 @@ ssd_dbdc_kernel(const __grid_constant__ CUtensorMap tmG,    // dCB   [B*nc*G*256
     uint8_t* sB = sA + 128 * 128;
     uint64_t* fb = &full[s % kDbdcStages];
     if (s < n_part1) {
-      if (tid == 0) {
+      if (warp == 0 && elect_one()) {
         const int kk = k_begin + s * 64;
         mbar_arrive_expect_tx(fb, 2 * 128 * 128);
         for (int j2 = 0; j2 < 2; ++j2) {
@@ -290,7 +296,7 @@ ssd_dbdc_kernel(const __grid_constant__ CUtensorMap tmG,    // dCB   [B*nc*G*256
     } else {
       const int h = g * hpg + (s - n_part1);
       const size_t sbase = ((size_t)bc * H + h) * kL;
-      if (tid == 0) {
+      if (warp == 0 && elect_one()) {
         mbar_arrive_expect_tx(fb, 2 * 128 * 128);
         for (int j2 = 0; j2 < 2; ++j2) {
           tma_load_3d(sA + j2 * 64 * 128, &tmAct, fb, h * kP, c * kL + m0 + j2 * 64, b);   // [128 rows][64] K-major
@@ -349,16 +355,19 @@ ssd_dbdc_kernel(const __grid_constant__ CUtensorMap tmG,    // dCB   [B*nc*G*256
     }
     fence_proxy_async_smem();
     __syncthreads();
-    if (tid == 0) {
+    if (warp == 0) {
       tc_fence_after();
       const uint32_t a_addr = smem_u32(sA), b_addr = smem_u32(sB);
       const uint32_t idesc = make_idesc_bf16(128, kN, a_mn ? MAJOR_MN : MAJOR_K, MAJOR_MN);
+      if (elect_one()) {
 #pragma unroll
-      for (int ks = 0; ks < 4; ++ks) {
-        const uint64_t da = a_mn ? desc_mnmajor(a_addr, 64, ks) : desc_kmajor(a_addr, 128, 0, ks);
-        mma_bf16_ss(tmem, da, desc_mnmajor(b_addr, 64, ks), idesc, (s > 0 || ks > 0) ? 1u : 0u);
+        for (int ks = 0; ks < 4; ++ks) {
+          const uint64_t da = a_mn ? desc_mnmajor(a_addr, 64, ks) : desc_kmajor(a_addr, 128, 0, ks);
+          mma_bf16_ss(tmem, da, desc_mnmajor(b_addr, 64, ks), idesc, (s > 0 || ks > 0) ? 1u : 0u);
+        }
+        mma_commit(&bars[buf]);
       }
-      mma_commit(&bars[buf]);
+      __syncwarp();
     }
   }
   {

@@ -61,7 +61,7 @@ ssd_outer_kernel(const bf16* __restrict__ arow, long long lda, const __grid_cons
     const int k0 = half * kOuterHalf;
     const int v = max(0, min(kOuterHalf, valid - k0));
     auto scale = [&](int row, int blk) { return s_scale[blk * kL + k0 + row]; };
-    if (tid == 0) {  // B / C rows of this half by TMA (two 64-column atoms); rows past the sequence end read as zeros
+    if (warp == 0 && elect_one()) {  // B / C rows of this half by TMA (two 64-column atoms); rows past the sequence end read as zeros
       mbar_arrive_expect_tx(ld_bar, kOuterHalf * 2 * 128);
       for (int j2 = 0; j2 < 2; ++j2)
         tma_load_3d(sB + j2 * kOuterHalf * 128, &tmBop, ld_bar, g * kN + j2 * 64, c * kL + k0, b);
@@ -70,16 +70,19 @@ ssd_outer_kernel(const bf16* __restrict__ arow, long long lda, const __grid_cons
     else load_tile<1, true>(sA, arow + (row0 + k0) * lda + h0 * kP, lda, kOuterHalf, v, scale, tid, kThreads);
     fence_proxy_async_smem();
     __syncthreads();
-    if (tid == 0) {
-      mbar_wait(ld_bar, half & 1);
+    if (warp == 0) {  // converged warp, one elected lane issues (ptx.cuh: warp-uniform single-lane issue)
+      mbar_wait_warp(ld_bar, half & 1);
       tc_fence_after();
       constexpr uint32_t idesc = make_idesc_bf16(128, kN, MAJOR_MN, MAJOR_MN);
       const uint32_t a_addr = smem_u32(sA), b_addr = smem_u32(sB);
+      if (elect_one()) {
 #pragma unroll
-      for (int k = 0; k < kOuterHalf / 16; ++k)
-        mma_bf16_ss(tmem, desc_mnmajor(a_addr, kOuterHalf, k), desc_mnmajor(b_addr, kOuterHalf, k), idesc,
-                    (half > 0 || k > 0) ? 1u : 0u);
-      mma_commit(bar);
+        for (int k = 0; k < kOuterHalf / 16; ++k)
+          mma_bf16_ss(tmem, desc_mnmajor(a_addr, kOuterHalf, k), desc_mnmajor(b_addr, kOuterHalf, k), idesc,
+                      (half > 0 || k > 0) ? 1u : 0u);
+        mma_commit(bar);
+      }
+      __syncwarp();
     }
     mbar_wait(bar, half & 1);  // operands consumed: smem may be refilled / accumulator readable
     tc_fence_after();
@@ -103,12 +106,12 @@ ssd_outer_kernel(const bf16* __restrict__ arow, long long lda, const __grid_cons
             make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
       fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0) {
+      if (elect_one()) {   // the same lane every time (elect.sync is deterministic for a given mask)
         tma_store_2d(&tmOut, stg, col, (bc * H + h0) * kP + lg * 32);
         tma_store_commit();
       }
     }
-    if (lane == 0) tma_store_wait_read<0>();
+    if (elect_one()) tma_store_wait_read<0>();
   }
   tc_fence_before();
   __syncthreads();
@@ -211,7 +214,7 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
   // The producer lane initialises the barriers and, without waiting for anyone, starts the TMA loads of the
   // row / column operands and of the tiles of heads 0 and 1: they fly while the other warps allocate TMEM
   // and fetch a | dt (everything else waits for the __syncthreads below before touching a barrier).
-  if (warp == kScanWarpsScale + kScanWarpsEpi + 1 && lane == 0) {
+  if (warp == kScanWarpsScale + kScanWarpsEpi + 1 && elect_one()) {
     mbar_init(cb_bar, 1);
     mbar_init(ld_bar, 1);
     for (int i = 0; i < kScanWarpsEpi; ++i) mbar_init(&x_full[i], 1);
@@ -247,16 +250,19 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   const uint32_t tCB = tmem;
-  if (warp == kScanWarpsScale + kScanWarpsEpi && lane == 0) {
-    mbar_wait(ld_bar, 0);
+  if (warp == kScanWarpsScale + kScanWarpsEpi) {
+    mbar_wait_warp(ld_bar, 0);
     tc_fence_after();
     const uint32_t idesc = make_idesc_bf16(128, ncols, MAJOR_K, MAJOR_K);
     const uint32_t a_addr = smem_u32(sR), b_addr = smem_u32(sC);
+    if (elect_one()) {
 #pragma unroll
-    for (int k = 0; k < kN / 16; ++k)
-      mma_bf16_ss(tCB, desc_kmajor(a_addr, 128, k >> 2, k & 3), desc_kmajor(b_addr, ncols, k >> 2, k & 3), idesc,
-                  k > 0 ? 1u : 0u);
-    mma_commit(cb_bar);
+      for (int k = 0; k < kN / 16; ++k)
+        mma_bf16_ss(tCB, desc_kmajor(a_addr, 128, k >> 2, k & 3), desc_kmajor(b_addr, ncols, k >> 2, k & 3), idesc,
+                    k > 0 ? 1u : 0u);
+      mma_commit(cb_bar);
+    }
+    __syncwarp();
   }
   mbar_wait(cb_bar, 0);  // CB complete: the column operand is dead, its smem becomes the G ring
   tc_fence_after();
@@ -398,7 +404,7 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
     for (int hh = 0; hh < hgs; ++hh) {
       const int h = h_first + hh;
       const int acc = hh & 1;
-      if (BWD && lane == 0) {  // backward also needs x[rows, h, cols]: TMA it into the staging tile while waiting
+      if (BWD && elect_one()) {  // backward also needs x[rows, h, cols]: TMA it into the staging tile while waiting
         tma_store_wait_read<0>();
         mbar_arrive_expect_tx(&x_full[ew], 2048);
         tma_load_3d(stg, &tmOut2, &x_full[ew], h * kP + pc0, trow, b);
@@ -490,14 +496,14 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
       // lays its 32 x 32 tile out in shared memory (64B-swizzled rows) and one lane issues a TMA store;
       // the tensor map is [B][T][H*P], so rows past the end of the sequence are dropped by the hardware.
       auto stage_and_store = [&](const uint4* pk, const CUtensorMap* map) {
-        if (lane == 0) tma_store_wait_read<0>();  // the previous store has finished reading the staging tile
+        if (elect_one()) tma_store_wait_read<0>();  // the previous store has finished reading the staging tile
         __syncwarp();
 #pragma unroll
         for (int q = 0; q < 4; ++q)
           *reinterpret_cast<uint4*>(stg + lane * 64 + ((q ^ ((lane >> 1) & 3)) << 4)) = pk[q];
         fence_proxy_async_smem();
         __syncwarp();
-        if (lane == 0) {
+        if (elect_one()) {
           tma_store_3d(map, stg, h * kP + pc0, trow, b);
           tma_store_commit();
         }
@@ -514,48 +520,56 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
       }
       TMARK("epi", hh, "epi_done");
     }
-    if (lane == 0) tma_store_wait_read<0>();  // staging must outlive the last store's read
+    if (elect_one()) tma_store_wait_read<0>();  // staging must outlive the last store's read
   } else if (warp == kScanWarpsScale + kScanWarpsEpi) {
-    if (lane == 0) {
     // =================================== MMA issuer ===================================
+    // all 32 lanes run the loops and the waits (converged), one elected lane issues each group of MMAs: the
+    // descriptors then live in uniform registers and the 8 MMAs of a group go out back to back
+    {
     const uint32_t r_addr = smem_u32(sR);
     constexpr uint32_t idesc_off = make_idesc_bf16(128, kP, MAJOR_K, MAJOR_K);
     constexpr uint32_t idesc_diag = make_idesc_bf16(128, kP, MAJOR_K, MAJOR_MN);
     int unit = 0;
     for (int hh = 0; hh < hgs; ++hh) {
       const int acc = hh & 1;
-      if (hh >= 2) mbar_wait(&acc_empty[acc], ((hh >> 1) - 1) & 1);
-      mbar_wait(&tiles_full[acc], (hh >> 1) & 1);
+      if (hh >= 2) mbar_wait_warp(&acc_empty[acc], ((hh >> 1) - 1) & 1);
+      mbar_wait_warp(&tiles_full[acc], (hh >> 1) & 1);
       tc_fence_after();
       TMARK("mma", hh, "ready");
       const uint32_t tOff = tmem + 256 + acc * 128, tDiag = tOff + 64;
       const uint32_t s_addr = smem_u32(sS0 + acc * kP * 2 * 128), v_addr = smem_u32(sV0 + acc * kL * 128);
+      if (elect_one()) {
 #pragma unroll
-      for (int k = 0; k < kN / 16; ++k)  // (C | B)[128 x 128] . (S_prev | dS)[64 x 128]^T
-        mma_bf16_ss(tOff, desc_kmajor(r_addr, 128, k >> 2, k & 3), desc_kmajor(s_addr, kP, k >> 2, k & 3), idesc_off,
-                    k > 0 ? 1u : 0u);
+        for (int k = 0; k < kN / 16; ++k)  // (C | B)[128 x 128] . (S_prev | dS)[64 x 128]^T
+          mma_bf16_ss(tOff, desc_kmajor(r_addr, 128, k >> 2, k & 3), desc_kmajor(s_addr, kP, k >> 2, k & 3), idesc_off,
+                      k > 0 ? 1u : 0u);
+      }
+      __syncwarp();
       for (int half = 0; half < nhalves; ++half, ++unit) {
         const int slot = unit & 1;
-        mbar_wait(&g_full[slot], (unit >> 1) & 1);
+        mbar_wait_warp(&g_full[slot], (unit >> 1) & 1);
         tc_fence_after();
         TMARK("mma", hh, "g_full");
         const uint32_t g_addr = smem_u32(sG + slot * 32768);
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < 8; ++k)  // G half-tile [128 x 128] . V[128 x 64]
-          mma_bf16_ss(tDiag, desc_kmajor(g_addr, 128, k >> 2, k & 3), desc_mnmajor(v_addr, ncols, half * 8 + k),
-                      idesc_diag, (half > 0 || k > 0) ? 1u : 0u);
-        mma_commit(&g_empty[slot]);
+          for (int k = 0; k < 8; ++k)  // G half-tile [128 x 128] . V[128 x 64]
+            mma_bf16_ss(tDiag, desc_kmajor(g_addr, 128, k >> 2, k & 3), desc_mnmajor(v_addr, ncols, half * 8 + k),
+                        idesc_diag, (half > 0 || k > 0) ? 1u : 0u);
+          mma_commit(&g_empty[slot]);
+        }
+        __syncwarp();
       }
-      mma_commit(&acc_full[acc]);
+      if (elect_one()) mma_commit(&acc_full[acc]);
+      __syncwarp();
     }
     }
   } else {
     // =================================== TMA producer ===================================
-    if (lane == 0) {
-      for (int hh = 2; hh < hgs; ++hh) {
-        mbar_wait(&tiles_empty[hh & 1], ((hh >> 1) - 1) & 1);
-        issue_head(hh);
-      }
+    for (int hh = 2; hh < hgs; ++hh) {
+      mbar_wait_warp(&tiles_empty[hh & 1], ((hh >> 1) - 1) & 1);
+      if (elect_one()) issue_head(hh);
+      __syncwarp();
     }
   }
   tc_fence_before();
