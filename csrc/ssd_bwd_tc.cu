@@ -34,8 +34,11 @@ ssd_dcb_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 4);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int blk = blockIdx.x % 3;
-  const int bc = blockIdx.x / 3;
+  // block 1 (rows 128.., columns 0..127) lies entirely below the diagonal and costs ~1.6x a diagonal block: all of
+  // them are launched first so that the second, partial wave of CTAs consists of short ones only
+  const int nbc = (int)gridDim.x / 3;
+  const int blk = (int)blockIdx.x < nbc ? 1 : (((int)blockIdx.x - nbc) & 1) * 2;
+  const int bc = (int)blockIdx.x < nbc ? (int)blockIdx.x : ((int)blockIdx.x - nbc) >> 1;
   const int b = bc / nc, c = bc % nc;
   const int g = blockIdx.y;
   const int hpg = H / G;

@@ -119,6 +119,154 @@ ssd_outer_kernel(const bf16* __restrict__ arow, long long lda, const __grid_cons
 }
 
 // ------------------------------------------------------------------------------------------
+// K9 + K10 in one kernel: chunk states AND the inter-chunk recurrence.
+//
+// One CTA owns a (batch, head pair) and walks the chunks of the sequence in order (backward: in reverse order),
+// so the recurrence  S_c = exp(a_last_c) S_{c-1} + X_c^T (w_c o B_c)  is carried in registers (64 fp32 per thread
+// in the TMEM lane layout of the accumulator) and only what the scan kernels consume ever reaches HBM: the bf16
+// state ENTERING each chunk (forward) / the bf16 gradient of each chunk's own state (backward).  The separate
+// state-passing kernels and their fp32 [B, nc, H, P, N] round trip (write 100 MB, read 100 MB per layer and
+// direction at B = 32, T = 1024) disappear.  Also native here: an initial state / its gradient and the final state
+// (mamba_chunk_scan_combined's initial_states / return_final_states).
+//   forward : sprev[c] = S_{c-1} ;  S_c = d_c S_{c-1} + states_c                         (S_{-1} = init or 0)
+//   backward: ds[c]    = g_c     ;  da_last[c] += d_c <g_c, sprev[c]> ;  g_{c-1} = d_c g_c + dstates_c   (g_{nc-1} = dfinal or 0)
+// Parallelism is B x H/2 CTAs: used when that fills the GPU, otherwise the per-chunk kernels above run.
+// ------------------------------------------------------------------------------------------
+template <bool DSTATE>
+__global__ void __launch_bounds__(kThreads, 2)
+ssd_states_seq_kernel(const bf16* __restrict__ arow, long long lda, const __grid_constant__ CUtensorMap tmBop,
+                      const float* __restrict__ dtv, const float* __restrict__ av,
+                      const __grid_constant__ CUtensorMap tmOut,          // bf16 [B*nc*H*P][N], box {64, 32}
+                      const bf16* __restrict__ sprev, float* __restrict__ da_last,   // backward only
+                      const float* __restrict__ init, float* __restrict__ last_out,  // fp32 [B, H, P, N] or null
+                      int T, int H, int G, int nc) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align1024(smem_raw);
+  uint8_t* sA = smem;                                // [128 k-rows][2 atoms]  MN-major A
+  uint8_t* sB = smem + kOuterHalf * 2 * 128;         // [128 k-rows][2 atoms]  MN-major B
+  float* s_scale = reinterpret_cast<float*>(smem + 2 * kOuterHalf * 2 * 128);  // [2][256]
+  uint64_t* bar = reinterpret_cast<uint64_t*>(s_scale + 2 * kL);
+  uint64_t* ld_bar = bar + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 2);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b = blockIdx.x;
+  const int h0 = blockIdx.y * 2;
+  const int g = h0 / (H / G);
+  const int lg = warp & 3, colhalf = warp >> 2;
+  const int row = lg * 32 + lane;              // accumulator row = (head of the pair, p)
+  const int hh = row >> 6, pp = row & 63;
+
+  if (tid == 0) { mbar_init(bar, 1); mbar_init(ld_bar, 1); fence_mbar_init(); }
+  if (warp == 0) { tmem_alloc(tmem_slot, 128); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  float run[64];   // this thread's 64 columns (colhalf * 64 ..) of the carried state / gradient
+  {
+    const float* src = init != nullptr ? init + (((size_t)b * H + h0 + hh) * kP + pp) * kN + colhalf * 64 : nullptr;
+#pragma unroll
+    for (int q = 0; q < 16; ++q) {
+      const float4 v = src != nullptr ? *reinterpret_cast<const float4*>(src + 4 * q) : make_float4(0.f, 0.f, 0.f, 0.f);
+      run[4 * q] = v.x; run[4 * q + 1] = v.y; run[4 * q + 2] = v.z; run[4 * q + 3] = v.w;
+    }
+  }
+  uint32_t mma_phase = 0, ld_phase = 0;
+  for (int ci = 0; ci < nc; ++ci) {
+    const int c = DSTATE ? nc - 1 - ci : ci;
+    const int bc = b * nc + c;
+    const int valid = min(kL, T - c * kL);
+    for (int idx = tid; idx < 2 * kL; idx += kThreads) {
+      const int h2 = idx / kL, t = idx % kL;
+      const size_t base = ((size_t)bc * H + h0 + h2) * kL;
+      const float a = av[base + t];
+      s_scale[h2 * kL + t] = DSTATE ? fast_exp(a) : fast_exp(av[base + kL - 1] - a) * dtv[base + t];
+    }
+    const float decay = fast_exp(av[((size_t)bc * H + h0 + hh) * kL + kL - 1]);
+    __syncthreads();   // scale vector visible; the previous chunk's TMA stores have finished reading the operand buffers
+    const size_t row0 = (size_t)b * T + (size_t)c * kL;
+    for (int half = 0; half < kL / kOuterHalf; ++half) {
+      const int k0 = half * kOuterHalf;
+      const int v = max(0, min(kOuterHalf, valid - k0));
+      auto scale = [&](int r_, int blk) { return s_scale[blk * kL + k0 + r_]; };
+      if (warp == 0 && elect_one()) {
+        mbar_arrive_expect_tx(ld_bar, kOuterHalf * 2 * 128);
+        for (int j2 = 0; j2 < 2; ++j2)
+          tma_load_3d(sB + j2 * kOuterHalf * 128, &tmBop, ld_bar, g * kN + j2 * 64, c * kL + k0, b);
+      }
+      load_tile<2, true>(sA, arow + (row0 + k0) * lda + h0 * kP, lda, kOuterHalf, v, scale, tid, kThreads);
+      fence_proxy_async_smem();
+      __syncthreads();
+      if (warp == 0) {
+        mbar_wait_warp(ld_bar, ld_phase);
+        tc_fence_after();
+        constexpr uint32_t idesc = make_idesc_bf16(128, kN, MAJOR_MN, MAJOR_MN);
+        const uint32_t a_addr = smem_u32(sA), b_addr = smem_u32(sB);
+        if (elect_one()) {
+#pragma unroll
+          for (int k = 0; k < kOuterHalf / 16; ++k)
+            mma_bf16_ss(tmem, desc_mnmajor(a_addr, kOuterHalf, k), desc_mnmajor(b_addr, kOuterHalf, k), idesc,
+                        (half > 0 || k > 0) ? 1u : 0u);
+          mma_commit(bar);
+        }
+        __syncwarp();
+      }
+      ld_phase ^= 1;
+      mbar_wait(bar, mma_phase);  // operands consumed: smem may be refilled / accumulator readable
+      mma_phase ^= 1;
+      tc_fence_after();
+    }
+    // ---- epilogue of the chunk: emit the carried value (bf16), then advance the recurrence ----
+    uint8_t* stg = smem + warp * 4096;   // [32 rows][128 B] staging in the idle operand buffers (128B swizzle)
+    float part = 0.f;
+    if (DSTATE) {  // <g_c, S_{c-1}> for d a_last: this thread's 64 columns of its row, 128 contiguous bytes
+      const bf16* sp = sprev + (((size_t)bc * H + h0 + hh) * kP + pp) * kN + colhalf * 64;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        float f[8];
+        unpack8(ld8(sp + 8 * q), f);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) part += run[8 * q + e] * f[e];
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 8; ++q)
+      *reinterpret_cast<bf16x8*>(stg + lane * 128 + ((q ^ (lane & 7)) << 4)) = pack8(run + 8 * q);
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (elect_one()) {
+      tma_store_2d(&tmOut, stg, colhalf * 64, (bc * H + h0) * kP + lg * 32);
+      tma_store_commit();
+    }
+#pragma unroll
+    for (int ch = 0; ch < 2; ++ch) {
+      uint32_t v[32];
+      tmem_ld32(tmem + ((uint32_t)(lg * 32) << 16) + colhalf * 64 + ch * 32, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) run[ch * 32 + j] = fmaf(decay, run[ch * 32 + j], __uint_as_float(v[j]));
+    }
+    if (DSTATE) {
+      part = warp_sum(part);   // all 32 rows of a warp belong to one head
+      if (lane == 0) atomicAdd(da_last + (size_t)bc * H + h0 + hh, decay * part);
+    }
+    if (elect_one()) tma_store_wait_read<0>();   // staging (= operand buffer) free before the next chunk's loads
+    tc_fence_before();
+  }
+  if (last_out != nullptr) {   // forward: final state; backward: gradient of the initial state
+    float* dst = last_out + (((size_t)b * H + h0 + hh) * kP + pp) * kN + colhalf * 64;
+#pragma unroll
+    for (int q = 0; q < 16; ++q)
+      *reinterpret_cast<float4*>(dst + 4 * q) = make_float4(run[4 * q], run[4 * q + 1], run[4 * q + 2], run[4 * q + 3]);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 128);
+}
+
+// ------------------------------------------------------------------------------------------
 // scan kernel (FWD: y ; BWD: dx, ddt partials) — warp-specialised, software-pipelined over heads
 //
 //   warps 0-7   "scale"     read the CB tile from TMEM, apply decay / mask / dt, write the bf16
@@ -187,8 +335,13 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14 + kScanWarpsEpi);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int rh = blockIdx.x & 1;
-  const int bc = blockIdx.x >> 1;
+  // Long CTAs first: the row half with two column halves of work (forward: the lower rows; backward: the upper
+  // ones) takes ~1.6x as long as the other, so launching all of them before the short ones leaves only short
+  // CTAs in the ragged last wave.
+  const int half_ctas = (int)gridDim.x >> 1;
+  const int first = (int)blockIdx.x < half_ctas ? 1 : 0;
+  const int rh = BWD ? 1 - first : first;
+  const int bc = (int)blockIdx.x - (first ? 0 : half_ctas);
   const int b = bc / nc, c = bc % nc;
   const int h_first = blockIdx.y * hgs;
   const int g = h_first / (H / G);
@@ -635,6 +788,43 @@ extern "C" int mb_ssd_chunk_state(const void* arow, long long lda, const void* b
     ssd_outer_kernel<false><<<grid, kThreads, kOuterSmem, stream>>>((const bf16*)arow, lda, tmBop, dt, a, tmOut, T, H, G, nc, hpc);
   }
   return check_launch("ssd_chunk_state");
+}
+
+// Whether the sequential chunk-state + state-passing kernel is the better choice for this shape: it needs an even
+// number of heads per group and enough (batch, head pair) CTAs to occupy the GPU (two per SM).
+extern "C" int mb_ssd_states_seq_ok(int B, int H, int G) {
+  return ((H / G) % 2 == 0 && (long long)B * (H / 2) >= (long long)num_sms() * 3 / 2) ? 1 : 0;
+}
+
+// Forward (dstate = 0): sprev[b,c] = state entering chunk c (bf16), optional init / final fp32 [B,H,P,N].
+// Backward (dstate = 1): arow = dy, bop = Cm; out = ds[b,c] (bf16 gradient of chunk c's own state),
+//   da_last[b,c,h] += exp(a_last) <ds, sprev> (pre-zeroed by the caller), `init` = gradient of the final state
+//   (or null), `last_out` = gradient of the initial state (or null).
+extern "C" int mb_ssd_states_seq(const void* arow, long long lda, const void* bop, long long ldb, const float* dt,
+                                 const float* a, void* out_bf16, const void* sprev_bf16, float* da_last,
+                                 const float* init, float* last_out, int dstate, int B, int T, int H, int G, int P,
+                                 int N, int L, cudaStream_t stream) {
+  SSD_SHAPE_CHECK("ssd_states_seq");
+  MB_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "ssd_states_seq: row strides must be multiples of 8");
+  MB_REQUIRE((H / G) % 2 == 0, "ssd_states_seq: needs an even number of heads per group");
+  MB_REQUIRE(!dstate || (sprev_bf16 != nullptr && da_last != nullptr), "ssd_states_seq: backward needs sprev and da_last");
+  const int nc = cdiv(T, L);
+  dim3 grid(B, H / 2);
+  CUtensorMap tmOut, tmBop;
+  if (make_tmap_bf16_2d(&tmOut, out_bf16, (long long)B * nc * H * P, N, N, 32) ||
+      make_tmap_bf16_3d(&tmBop, bop, B, T, (long long)G * N, ldb, kOuterHalf, 64)) return 1;
+  if (dstate) {
+    static bool once = false;
+    if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_states_seq_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kOuterSmem)); once = true; }
+    ssd_states_seq_kernel<true><<<grid, kThreads, kOuterSmem, stream>>>((const bf16*)arow, lda, tmBop, dt, a, tmOut, (const bf16*)sprev_bf16,
+                                                                        da_last, init, last_out, T, H, G, nc);
+  } else {
+    static bool once = false;
+    if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_states_seq_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kOuterSmem)); once = true; }
+    ssd_states_seq_kernel<false><<<grid, kThreads, kOuterSmem, stream>>>((const bf16*)arow, lda, tmBop, dt, a, tmOut, nullptr, nullptr,
+                                                                         init, last_out, T, H, G, nc);
+  }
+  return check_launch("ssd_states_seq");
 }
 
 // y[t,h,:] = exp(a_t) C_t S_prev^T + sum_{s<=t} (C_t.B_s) exp(a_t - a_s) dt_s x_s + D_h x_t ;  y_off = first term only

@@ -16,7 +16,7 @@ namespace mb {
 __global__ void ssd_prep_kernel(const bf16* __restrict__ dt_raw, long long ld_dt,
                                 const float* __restrict__ dt_bias, const float* __restrict__ A_log,
                                 float* __restrict__ dt_out, float* __restrict__ a_out, int T, int H, int L,
-                                int nc) {
+                                int nc, float dt_min, float dt_max) {
   extern __shared__ float sm[];  // [H][L] dA, then scanned in place
   const int b = blockIdx.x / nc, c = blockIdx.x % nc;
   const int t = threadIdx.x;
@@ -27,7 +27,7 @@ __global__ void ssd_prep_kernel(const bf16* __restrict__ dt_raw, long long ld_dt
   float* a_o = a_out + ((size_t)(b * nc + c) * H) * L;
   for (int h = 0; h < H; ++h) {
     float dt = 0.f;
-    if (valid) dt = softplus_f(__bfloat162float(src[h]) + dt_bias[h]);
+    if (valid) dt = fminf(fmaxf(softplus_f(__bfloat162float(src[h]) + dt_bias[h]), dt_min), dt_max);  // dt_limit
     dt_o[(size_t)h * L + t] = dt;
     sm[h * L + t] = dt * (-fast_exp(A_log[h]));
   }
@@ -129,7 +129,7 @@ __global__ void ssd_bwd_finalize_kernel(const bf16* __restrict__ dy, long long l
                                         const float* __restrict__ dt_bias, const float* __restrict__ A_log,
                                         bf16* __restrict__ draw_out,
                                         long long ld_draw, float* __restrict__ dA_log, float* __restrict__ ddt_bias,
-                                        int T, int H, int P, int L, int nc) {
+                                        int T, int H, int P, int L, int nc, float dt_min, float dt_max) {
   __shared__ float wsum[8];
   __shared__ float red3[2][8];
   __shared__ float s_rowpart[256];
@@ -196,7 +196,8 @@ __global__ void ssd_bwd_finalize_kernel(const bf16* __restrict__ dy, long long l
     float draw = 0.f;
     if (valid) {
       const float raw = __bfloat162float(dt_raw[row * ld_dt + h]) + dt_bias[h];
-      draw = ddt * sigmoid_f(raw);
+      const float sp = softplus_f(raw);
+      draw = (sp >= dt_min && sp <= dt_max) ? ddt * sigmoid_f(raw) : 0.f;   // no gradient through a clamped dt
       draw_out[row * ld_draw + h] = __float2bfloat16(draw);
     }
     float r0 = warp_sum(dtv * ddA), r1 = warp_sum(draw);
@@ -262,13 +263,15 @@ ssd_state_update_kernel(float* __restrict__ state, const bf16* __restrict__ x, l
 using namespace mb;
 
 extern "C" int mb_ssd_prep(const void* dt_raw, long long ld_dt, const float* dt_bias, const float* A_log,
-                           float* dt_out, float* a_out, int B, int T, int H, int L, cudaStream_t stream) {
+                           float* dt_out, float* a_out, int B, int T, int H, int L, float dt_min, float dt_max,
+                           cudaStream_t stream) {
   MB_REQUIRE(L == 64 || L == 128 || L == 256, "ssd_prep: chunk size %d not in {64,128,256}", L);
   const int nc = cdiv(T, L);
   const size_t smem = (size_t)H * L * sizeof(float);
   MB_REQUIRE(smem <= 200 * 1024, "ssd_prep: H*L too large for shared memory");
   if (smem > 48 * 1024) MB_CUDA(cudaFuncSetAttribute(ssd_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  ssd_prep_kernel<<<B * nc, L, smem, stream>>>((const bf16*)dt_raw, ld_dt, dt_bias, A_log, dt_out, a_out, T, H, L, nc);
+  ssd_prep_kernel<<<B * nc, L, smem, stream>>>((const bf16*)dt_raw, ld_dt, dt_bias, A_log, dt_out, a_out, T, H, L, nc,
+                                               dt_min, dt_max);
   return check_launch("ssd_prep");
 }
 
@@ -297,14 +300,16 @@ extern "C" int mb_ssd_bwd_finalize(const void* dy, long long lddy, const void* y
                                    const float* ddt2, const float* rowsum_m, const float* da_last,
                                    const float* dt_bias,
                                    const float* A_log, void* draw_out, long long ld_draw, float* dA_log,
-                                   float* ddt_bias, int B, int T, int H, int P, int L, cudaStream_t stream) {
+                                   float* ddt_bias, int B, int T, int H, int P, int L, float dt_min, float dt_max,
+                                   cudaStream_t stream) {
   MB_REQUIRE(L == 64 || L == 128 || L == 256, "ssd_bwd_finalize: chunk size %d not in {64,128,256}", L);
   MB_REQUIRE(P == 8 || P == 16 || P == 32 || P == 64 || P == 128 || P == 256,
              "ssd_bwd_finalize: headdim %d must be a power of two in [8, 256] (lanes of one row reduce by shuffles)", P);
   const int nc = cdiv(T, L);
   ssd_bwd_finalize_kernel<<<dim3(B * nc, H), L, 0, stream>>>((const bf16*)dy, lddy, (const bf16*)y_off, ldy,
                                                     (const bf16*)dt_raw, ld_dt, dt, ddt1, ddt2, rowsum_m, da_last, dt_bias,
-                                                    A_log, (bf16*)draw_out, ld_draw, dA_log, ddt_bias, T, H, P, L, nc);
+                                                    A_log, (bf16*)draw_out, ld_draw, dA_log, ddt_bias, T, H, P, L, nc,
+                                                    dt_min, dt_max);
   return check_launch("ssd_bwd_finalize");
 }
 

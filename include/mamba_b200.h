@@ -86,10 +86,22 @@ int mb_gemm_bf16(const void* A, long long lda, int a_major, const void* B, long 
  * Layouts: dt, a = cumsum(dt*A) per chunk: fp32 [B, nc, H, L]; states: fp32 [B, nc, H, P, N];
  * bf16 state operand copies: [B, nc, H, P, N]; x | B | C are column slices of the conv output. */
 int mb_ssd_prep(const void* dt_raw, long long ld_dt, const float* dt_bias, const float* A_log,
-                float* dt_out, float* a_out, int B, int T, int H, int L, cudaStream_t stream);
+                float* dt_out, float* a_out, int B, int T, int H, int L, float dt_min, float dt_max,
+                cudaStream_t stream);
 int mb_ssd_chunk_state(const void* arow, long long lda, const void* bop, long long ldb, const float* dt,
                        const float* a, float* out, int dstate, int B, int T, int H, int G, int P, int N,
                        int L, cudaStream_t stream);
+/* K9 + K10 fused: chunk states and the inter-chunk recurrence in one kernel (one CTA per batch x head pair walks
+ * the chunks in order and carries the state in registers), with native initial / final states and their
+ * gradients (mamba_chunk_scan_combined's initial_states / return_final_states).  dstate = 0: out = bf16 state
+ * entering each chunk; dstate = 1: arow = dy, bop = Cm, out = bf16 gradient of each chunk's own state,
+ * da_last += exp(a_last) <ds, sprev> (pre-zeroed), init = gradient of the final state, last_out = gradient of the
+ * initial state.  mb_ssd_states_seq_ok says whether the shape has enough (batch, head pair) parallelism for it. */
+int mb_ssd_states_seq_ok(int B, int H, int G);
+int mb_ssd_states_seq(const void* arow, long long lda, const void* bop, long long ldb, const float* dt,
+                      const float* a, void* out_bf16, const void* sprev_bf16, float* da_last, const float* init,
+                      float* last_out, int dstate, int B, int T, int H, int G, int P, int N, int L,
+                      cudaStream_t stream);
 int mb_ssd_state_passing_fwd(const float* states, const float* a, void* sprev_bf16, float* final_state,
                              int B, int nc, int H, int PN, int L, cudaStream_t stream);
 int mb_ssd_state_passing_bwd(const float* dstates_direct, const void* sprev_bf16, const float* a,
@@ -115,7 +127,7 @@ int mb_ssd_bwd_finalize(const void* dy, long long lddy, const void* y_off, long 
                         const float* ddt2, const float* rowsum_m, const float* da_last,
                         const float* dt_bias, const float* A_log,
                         void* draw_out, long long ld_draw, float* dA_log, float* ddt_bias, int B, int T, int H,
-                        int P, int L, cudaStream_t stream);
+                        int P, int L, float dt_min, float dt_max, cudaStream_t stream);
 
 /* ---- K4 / K5 / K23: Mamba-1 selective scan fwd / bwd / single-token update (mamba_ssm
  * csrc/selective_scan + Triton selective_state_update), channel-last, d_state = 16.

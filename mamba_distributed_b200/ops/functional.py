@@ -39,9 +39,9 @@ def causal_conv1d(x, weight, bias=None, activation="silu"):
 def ssd_combined(x, dt, A, B, C, chunk_size=256, D=None, z=None, dt_bias=None, dt_softplus=True,
                  dt_limit=(0.0, float("inf")), initial_states=None, return_final_states=False):
     """K7-K12: Mamba-2 chunked scan."""
-    if use_native(x) and initial_states is None and not return_final_states \
-            and dt_limit == (0.0, float("inf")):
-        return _native().ssd_combined(x, dt, A, B, C, chunk_size, D, z, dt_bias, dt_softplus)
+    if use_native(x) and dt_softplus and D is not None and dt_bias is not None:
+        return _native().ssd_combined(x, dt, A, B, C, chunk_size, D, z, dt_bias, dt_softplus, tuple(dt_limit),
+                                      initial_states, return_final_states)
     return ref.ssd_chunked_ref(x, dt, A, B, C, chunk_size, D, z, dt_bias, dt_softplus, dt_limit,
                                initial_states, return_final_states)
 

@@ -372,9 +372,11 @@ def embedding(ids, weight):
 # ------------------------------------------------------------------------------------------
 # K7-K12: SSD.  (kernels live in ops/ssd_native.py; "torch" = oracle math on the GPU)
 # ------------------------------------------------------------------------------------------
-def ssd_combined(x, dt, A, B, C, chunk_size, D, z, dt_bias, dt_softplus):
+def ssd_combined(x, dt, A, B, C, chunk_size, D, z, dt_bias, dt_softplus, dt_limit=(0.0, float("inf")),
+                 initial_states=None, return_final_states=False):
     from . import ssd_native
-    return ssd_native.ssd_combined(x, dt, A, B, C, chunk_size, D, z, dt_bias, dt_softplus)
+    return ssd_native.ssd_combined(x, dt, A, B, C, chunk_size, D, z, dt_bias, dt_softplus, dt_limit,
+                                   initial_states, return_final_states)
 
 
 def selective_scan(u, delta, A, B, C, D, z, delta_bias, delta_softplus):
@@ -464,7 +466,8 @@ class Mamba2MixerFn(torch.autograd.Function):
 
 def mamba2_mixer(mod, u):
     cfg = dict(d_inner=mod.d_inner, nheads=mod.nheads, headdim=mod.headdim, ngroups=mod.ngroups,
-               d_state=mod.d_state, chunk_size=mod.chunk_size, eps=mod.norm.eps)
+               d_state=mod.d_state, chunk_size=mod.chunk_size, eps=mod.norm.eps,
+               dt_limit=tuple(float(v) for v in mod.dt_limit))
     return Mamba2MixerFn.apply(u, mod.in_proj.weight, mod.conv1d.weight, mod.conv1d.bias, mod.dt_bias,
                                mod.A_log, mod.D, mod.norm.weight, mod.out_proj.weight, cfg)
 

@@ -1,8 +1,11 @@
 """Orchestration of the sm_100a SSD kernels (csrc/ssd_simt.cu, ssd_fwd_tc.cu, ssd_bwd_tc.cu).
 
-Forward : prep (softplus + chunk cumsum) -> chunk states (tcgen05) -> state passing -> fused
-          CB + chunk scan (tcgen05).   Saves dt, a, S_prev(bf16) — nothing is recomputed.
-Backward: dstates (tcgen05) -> reverse state passing -> dx + d(dt) partials (tcgen05) -> dCB
+Forward : prep (softplus + dt_limit clamp + chunk cumsum) -> chunk states + inter-chunk recurrence in ONE
+          kernel (tcgen05; one CTA per batch x head pair walks the chunks, the carried state stays in registers)
+          -> fused CB + chunk scan (tcgen05).   Saves dt, a, S_prev(bf16) — nothing is recomputed.
+          Shapes with too little (batch, head pair) parallelism (e.g. 2.7B at B = 2) use the per-chunk
+          chunk-state kernel + the stand-alone state-passing kernel instead.
+Backward: dstates + reverse recurrence (same fused kernel) -> dx + d(dt) partials (tcgen05) -> dCB
           (tcgen05) -> dB, dC (tcgen05, K-concatenated over heads) -> finalize (d dt_raw, dA_log,
           d dt_bias, dD).
 Everything reads x | B | C as column slices of the conv output and writes dx | dB | dC into the
@@ -11,9 +14,25 @@ from __future__ import annotations
 
 import torch
 
+from . import _lib
 from ._lib import call
 
 L_TC, P_TC, N_TC = 256, 64, 128
+INF = float("inf")
+
+
+FORCE_SEQ_STATES = None   # tests set True / False to pin one of the two state paths
+
+
+def _seq_states(Bsz, H, G, need_boundary_states):
+    """True: the fused chunk-state + state-passing kernel runs (always when an initial / final state is involved)."""
+    even = (H // G) % 2 == 0
+    if FORCE_SEQ_STATES is not None and not need_boundary_states:
+        return bool(FORCE_SEQ_STATES) and even
+    if need_boundary_states:
+        assert even, "initial / final SSD states need an even number of heads per group in the native path"
+        return True
+    return even and bool(_lib.load().mb_ssd_states_seq_ok(Bsz, H, G))
 
 
 def supported(cfg) -> bool:
@@ -29,7 +48,9 @@ def _slices(xBC, zxbcdt, cfg):
     return x, Bm, Cm, dt_raw
 
 
-def ssd_fwd(xBC, zxbcdt, Bsz, T, cfg, dt_bias, A_log, D):
+def ssd_fwd(xBC, zxbcdt, Bsz, T, cfg, dt_bias, A_log, D, initial_states=None, return_final_states=False,
+            dt_limit=(0.0, INF)):
+    """Returns ``(y, saved)`` or, with ``return_final_states``, ``(y, final_states fp32 [B,H,P,N], saved)``."""
     d_in, H, P, G, N, L = (cfg["d_inner"], cfg["nheads"], cfg["headdim"], cfg["ngroups"], cfg["d_state"],
                            cfg["chunk_size"])
     dev = xBC.device
@@ -40,18 +61,29 @@ def ssd_fwd(xBC, zxbcdt, Bsz, T, cfg, dt_bias, A_log, D):
     dt_bias, A_log, D = dt_bias.float().contiguous(), A_log.float().contiguous(), D.float().contiguous()
     dt = torch.empty(Bsz, nc, H, L, dtype=torch.float32, device=dev)
     a = torch.empty_like(dt)
-    call("mb_ssd_prep", dt_raw, zxbcdt.stride(0), dt_bias, A_log, dt, a, Bsz, T, H, L)
-    states = torch.empty(Bsz, nc, H, P, N, dtype=torch.float32, device=dev)
-    call("mb_ssd_chunk_state", x, ld, Bm, ld, dt, a, states, 0, Bsz, T, H, G, P, N, L)
+    call("mb_ssd_prep", dt_raw, zxbcdt.stride(0), dt_bias, A_log, dt, a, Bsz, T, H, L, float(dt_limit[0]),
+         min(float(dt_limit[1]), 3.0e38))
     sprev = torch.empty(Bsz, nc, H, P, N, dtype=torch.bfloat16, device=dev)
-    call("mb_ssd_state_passing_fwd", states, a, sprev, None, Bsz, nc, H, P * N, L)
+    final = torch.empty(Bsz, H, P, N, dtype=torch.float32, device=dev) if return_final_states else None
+    if _seq_states(Bsz, H, G, initial_states is not None or return_final_states):
+        init = initial_states.float().contiguous() if initial_states is not None else None
+        call("mb_ssd_states_seq", x, ld, Bm, ld, dt, a, sprev, None, None, init, final, 0, Bsz, T, H, G, P, N, L)
+    else:
+        states = torch.empty(Bsz, nc, H, P, N, dtype=torch.float32, device=dev)
+        call("mb_ssd_chunk_state", x, ld, Bm, ld, dt, a, states, 0, Bsz, T, H, G, P, N, L)
+        call("mb_ssd_state_passing_fwd", states, a, sprev, None, Bsz, nc, H, P * N, L)
     y = torch.empty(M, d_in, dtype=torch.bfloat16, device=dev)
     y_ssm = torch.empty(M, d_in, dtype=torch.bfloat16, device=dev)  # inter-chunk part exp(a) C S_prev^T, needed by backward (d a_t)
     call("mb_ssd_chunk_scan_fwd", Cm, Bm, ld, x, ld, sprev, dt, a, D, y, y_ssm, y.stride(0), Bsz, T, H, G, P, N, L)
+    if return_final_states:
+        return y, final, (dt, a, sprev, y_ssm)
     return y, (dt, a, sprev, y_ssm)
 
 
-def ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, saved, red_out=None):
+def ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, saved, red_out=None,
+            dfinal_states=None, want_dinitial=False, dt_limit=(0.0, INF)):
+    """``dfinal_states``: gradient of the final state (when forward returned it); ``want_dinitial``: also return
+    the gradient of the initial state as a 4th value."""
     d_in, H, P, G, N, L = (cfg["d_inner"], cfg["nheads"], cfg["headdim"], cfg["ngroups"], cfg["d_state"],
                            cfg["chunk_size"])
     dt, a, sprev, y_ssm = saved
@@ -61,11 +93,18 @@ def ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, s
     x, Bm, Cm, dt_raw = _slices(xBC, zxbcdt, cfg)
     dt_bias, A_log, D = dt_bias.float().contiguous(), A_log.float().contiguous(), D.float().contiguous()
     lddy = dy.stride(0)
-    dstates = torch.empty(Bsz, nc, H, P, N, dtype=torch.float32, device=dev)
-    call("mb_ssd_chunk_state", dy, lddy, Cm, ld, dt, a, dstates, 1, Bsz, T, H, G, P, N, L)
     ds = torch.empty(Bsz, nc, H, P, N, dtype=torch.bfloat16, device=dev)
-    da_last = torch.empty(Bsz, nc, H, dtype=torch.float32, device=dev)
-    call("mb_ssd_state_passing_bwd", dstates, sprev, a, ds, da_last, Bsz, nc, H, P * N, L)
+    dinit = None
+    if _seq_states(Bsz, H, G, dfinal_states is not None or want_dinitial):
+        da_last = torch.zeros(Bsz, nc, H, dtype=torch.float32, device=dev)
+        dinit = torch.empty(Bsz, H, P, N, dtype=torch.float32, device=dev) if want_dinitial else None
+        dfin = dfinal_states.float().contiguous() if dfinal_states is not None else None
+        call("mb_ssd_states_seq", dy, lddy, Cm, ld, dt, a, ds, sprev, da_last, dfin, dinit, 1, Bsz, T, H, G, P, N, L)
+    else:
+        dstates = torch.empty(Bsz, nc, H, P, N, dtype=torch.float32, device=dev)
+        call("mb_ssd_chunk_state", dy, lddy, Cm, ld, dt, a, dstates, 1, Bsz, T, H, G, P, N, L)
+        da_last = torch.empty(Bsz, nc, H, dtype=torch.float32, device=dev)
+        call("mb_ssd_state_passing_bwd", dstates, sprev, a, ds, da_last, Bsz, nc, H, P * N, L)
     ddt12 = torch.zeros(3, Bsz, nc, H, L, dtype=torch.float32, device=dev)  # ddt1 | ddt2 | row sums of dM o M
     lddx = dxBC.stride(0)
     if red_out is not None:   # (ddt_bias, dA_log, dD) fp32 [H] buffers the kernels add into (parameter .grad)
@@ -81,5 +120,8 @@ def ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, s
     call("mb_ssd_bwd_dbdc", dcb, Bm, Cm, ld, dy, lddy, x, ld, sprev, ds, dt, a, dB, dC, lddx, Bsz, T, H, G, P, N, L)
     draw = dzxbcdt[:, dzxbcdt.shape[1] - H:]
     call("mb_ssd_bwd_finalize", dy, lddy, y_ssm, y_ssm.stride(0), dt_raw, zxbcdt.stride(0), dt, ddt12[0], ddt12[1],
-         ddt12[2], da_last, dt_bias, A_log, draw, dzxbcdt.stride(0), red[0], red[1], Bsz, T, H, P, L)
+         ddt12[2], da_last, dt_bias, A_log, draw, dzxbcdt.stride(0), red[0], red[1], Bsz, T, H, P, L,
+         float(dt_limit[0]), min(float(dt_limit[1]), 3.0e38))
+    if want_dinitial:
+        return red[1], red[0], red[2], dinit
     return red[1], red[0], red[2]  # ddt_bias, dA_log, dD

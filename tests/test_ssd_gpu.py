@@ -123,3 +123,66 @@ def test_mamba2_mixer_and_model_match_torch_path():
         if e > lim:
             bad[n] = e
     assert not bad, bad
+
+
+@pytest.mark.parametrize("B,T,H,G", [(2, 1024, 4, 1), (3, 700, 8, 2)])
+def test_fused_states_kernel_matches_per_chunk_kernels(B, T, H, G, monkeypatch):
+    """K9 + K10 in one kernel (sequential over chunks, state carried in registers) against the per-chunk
+    chunk-state kernel + stand-alone state passing: same y, same gradients."""
+    from mamba_distributed_b200.ops import ssd_kernels, ssd_native
+    x, dt, A, Bm, Cm, D, dt_bias = _mk(B, T, H, G, seed=5)
+    dy = None
+    res = {}
+    for seq in (False, True):
+        monkeypatch.setattr(ssd_kernels, "FORCE_SEQ_STATES", seq)
+        leaves = [t.clone().requires_grad_(True) for t in (x, dt, A, Bm, Cm, D, dt_bias)]
+        y = ssd_native.ssd_combined(*leaves[:5], 256, leaves[5], None, leaves[6], True)
+        if dy is None:
+            dy = torch.randn_like(y)
+        res[seq] = (y.detach(), torch.autograd.grad(y, leaves, dy))
+    assert _rel(res[True][0], res[False][0]) < 2e-3
+    for n, g1, g0 in zip(["dx", "ddt", "dA", "dB", "dC", "dD", "ddt_bias"], res[True][1], res[False][1]):
+        assert _rel(g1, g0) < 5e-3, (n, _rel(g1, g0))
+
+
+@pytest.mark.parametrize("B,T,H,G", [(2, 512, 4, 1), (1, 900, 8, 2)])
+def test_ssd_initial_and_final_states_native(B, T, H, G):
+    """initial_states / return_final_states and their gradients (dinitial_states, the gradient flowing in through
+    the final state) run in the kernels, not in the PyTorch oracle."""
+    from mamba_distributed_b200.ops import ssd_native
+    x, dt, A, Bm, Cm, D, dt_bias = _mk(B, T, H, G, seed=7)
+    s0 = torch.randn(B, H, 64, 128, device="cuda") * 0.5
+    leaves = [t.clone().requires_grad_(True) for t in (x, dt, A, Bm, Cm, D, dt_bias, s0)]
+    y, fin = ssd_native.ssd_combined(*leaves[:5], 256, leaves[5], None, leaves[6], True,
+                                     initial_states=leaves[7], return_final_states=True)
+    rl = [t.detach().float().requires_grad_(True) for t in (x, dt, A, Bm, Cm, D, dt_bias, s0)]
+    y_ref, fin_ref = ref.ssd_chunked_ref(rl[0], rl[1], rl[2], rl[3], rl[4], 256, rl[5], None, rl[6], True,
+                                         initial_states=rl[7], return_final_states=True)
+    assert fin.dtype == torch.float32 and fin.shape == (B, H, 64, 128)
+    assert _rel(y, y_ref) < 1.5e-2 and _rel(fin, fin_ref) < 1.5e-2, (_rel(y, y_ref), _rel(fin, fin_ref))
+    dy = (y_ref.detach() - D.view(1, 1, H, 1) * x.float()).bfloat16()
+    dfin = fin_ref.detach() * 0.1
+    grads = torch.autograd.grad([y, fin], leaves, [dy, dfin])
+    grads_ref = torch.autograd.grad([y_ref, fin_ref], rl, [dy.float(), dfin])
+    lim = {"dx": 1e-2, "dB": 1e-2, "dC": 1e-2, "dD": 1e-2, "dinit": 1.5e-2, "ddt": 3e-2, "dA": 3e-2, "ddt_bias": 3e-2}
+    for n, g, gr in zip(["dx", "ddt", "dA", "dB", "dC", "dD", "ddt_bias", "dinit"], grads, grads_ref):
+        assert _rel(g, gr) < lim[n], (n, _rel(g, gr))
+
+
+def test_ssd_dt_limit_native():
+    """dt_limit clamps softplus(dt + bias) in the prep kernel and stops its gradient in the finalize kernel."""
+    from mamba_distributed_b200.ops import ssd_native
+    x, dt, A, Bm, Cm, D, dt_bias = _mk(2, 512, 4, 1, seed=9)
+    lim = (0.05, 0.3)
+    leaves = [t.clone().requires_grad_(True) for t in (x, dt, A, Bm, Cm, D, dt_bias)]
+    y = ssd_native.ssd_combined(*leaves[:5], 256, leaves[5], None, leaves[6], True, dt_limit=lim)
+    rl = [t.detach().float().requires_grad_(True) for t in (x, dt, A, Bm, Cm, D, dt_bias)]
+    y_ref = ref.ssd_chunked_ref(rl[0], rl[1], rl[2], rl[3], rl[4], 256, rl[5], None, rl[6], True, dt_limit=lim)
+    assert _rel(y, y_ref) < 1.5e-2
+    dy = (y_ref.detach() - D.view(1, 1, 4, 1) * x.float()).bfloat16()
+    g = torch.autograd.grad(y, leaves, dy)
+    gr = torch.autograd.grad(y_ref, rl, dy.float())
+    assert _rel(g[0], gr[0]) < 1e-2 and _rel(g[1], gr[1]) < 3e-2 and _rel(g[6], gr[6]) < 3e-2, \
+        (_rel(g[0], gr[0]), _rel(g[1], gr[1]), _rel(g[6], gr[6]))
+    frac_clamped = ((gr[1] == 0).float().mean()).item()
+    assert 0.05 < frac_clamped < 0.95      # the clamp is active for part of the tokens
