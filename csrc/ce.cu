@@ -1,5 +1,7 @@
 // K17 (part): cross-entropy over one slab of logits, forward and gradient in a single pass pair.
-// The lm_head GEMM (csrc/gemm.cu) writes an fp32 [R, V] slab; this kernel turns it into
+// The lm_head GEMM (csrc/gemm.cu) writes an [R, V] slab — bf16 in training (the precision the reference's
+// logits have under autocast, /root/reference/train.py:211; halves the slab traffic and lets the gradient
+// overwrite the logits in place), fp32 for loss-only scoring — and this kernel turns it into
 //   loss[r]      = logsumexp(logits[r, :]) - logits[r, target[r]]
 //   dlogits[r,:] = (softmax(logits[r, :]) - onehot(target[r])) * scale        (bf16, in place of a
 //                  separate softmax / scatter / scale / cast sequence of ATen kernels)
@@ -16,24 +18,41 @@ constexpr int kCeThreads = 512;
 // exp(m - nm) with the empty-partial case (m = -inf, possibly nm = -inf too) mapped to 0, not NaN
 __device__ __forceinline__ float scale_to(float m, float nm) { return m == -INFINITY ? 0.f : fast_exp(m - nm); }
 
+// 8 consecutive logits of a row as fp32, from either slab precision
+template <bool BF16_IN>
+__device__ __forceinline__ void ld_logits8(const void* row, int i8, float* f) {
+  if (BF16_IN) unpack8(ld8(reinterpret_cast<const bf16*>(row) + 8 * i8), f);
+  else ld8f(reinterpret_cast<const float*>(row) + 8 * i8, f);
+}
+template <bool BF16_IN>
+__device__ __forceinline__ float ld_logit(const void* row, long long i) {
+  return BF16_IN ? __bfloat162float(reinterpret_cast<const bf16*>(row)[i]) : reinterpret_cast<const float*>(row)[i];
+}
+
+// dlogits may alias logits (bf16 slab): element i is read and then written by the same thread.
+template <bool BF16_IN>
 __global__ void __launch_bounds__(kCeThreads)
-ce_slab_kernel(const float* __restrict__ logits, long long ld, const long long* __restrict__ targets,
-               float* __restrict__ loss, bf16* __restrict__ dlogits, long long ldd, int V, float scale) {
+ce_slab_kernel(const void* logits, long long ld, const long long* __restrict__ targets,
+               float* __restrict__ loss, bf16* dlogits, long long ldd, int V, float scale) {
   __shared__ float s_m[kCeThreads / 32], s_s[kCeThreads / 32];
   __shared__ float s_max, s_lse;
   const int row = blockIdx.x, tid = threadIdx.x;
-  const float* lr = logits + (size_t)row * ld;
-  const int nvec = V >> 2;
+  const void* lr = reinterpret_cast<const char*>(logits) + (size_t)row * ld * (BF16_IN ? 2 : 4);
+  const int nv8 = V >> 3;
   // pass 1: online max / sum-exp
   float m = -INFINITY, s = 0.f;
-  for (int i = tid; i < nvec; i += kCeThreads) {
-    const float4 v = *reinterpret_cast<const float4*>(lr + 4 * i);
-    const float vm = fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w));
+  for (int i = tid; i < nv8; i += kCeThreads) {
+    float v[8];
+    ld_logits8<BF16_IN>(lr, i, v);
+    float vm = v[0];
+#pragma unroll
+    for (int j = 1; j < 8; ++j) vm = fmaxf(vm, v[j]);
     if (vm > m) { s *= fast_exp(m - vm); m = vm; }
-    s += fast_exp(v.x - m) + fast_exp(v.y - m) + fast_exp(v.z - m) + fast_exp(v.w - m);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += fast_exp(v[j] - m);
   }
-  for (int i = (nvec << 2) + tid; i < V; i += kCeThreads) {
-    const float v = lr[i];
+  for (int i = (nv8 << 3) + tid; i < V; i += kCeThreads) {
+    const float v = ld_logit<BF16_IN>(lr, i);
     if (v > m) { s *= fast_exp(m - v); m = v; }
     s += fast_exp(v - m);
   }
@@ -57,7 +76,7 @@ ce_slab_kernel(const float* __restrict__ logits, long long ld, const long long* 
     s_max = M;
     s_lse = lse;
     const long long t = targets[row];
-    loss[row] = (t >= 0 && t < V) ? lse - lr[t] : 0.f;
+    loss[row] = (t >= 0 && t < V) ? lse - ld_logit<BF16_IN>(lr, t) : 0.f;
   }
   __syncthreads();
   if (dlogits == nullptr) return;
@@ -65,10 +84,9 @@ ce_slab_kernel(const float* __restrict__ logits, long long ld, const long long* 
   const float lse = s_lse;
   const long long t = targets[row];
   bf16* dr = dlogits + (size_t)row * ldd;
-  const int nv8 = V >> 3;
   for (int i = tid; i < nv8; i += kCeThreads) {
     float f[8];
-    ld8f(lr + 8 * i, f);
+    ld_logits8<BF16_IN>(lr, i, f);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       float p = fast_exp(f[j] - lse);
@@ -78,7 +96,7 @@ ce_slab_kernel(const float* __restrict__ logits, long long ld, const long long* 
     st8(dr + 8 * i, pack8(f));
   }
   for (int i = (nv8 << 3) + tid; i < V; i += kCeThreads) {
-    float p = fast_exp(lr[i] - lse);
+    float p = fast_exp(ld_logit<BF16_IN>(lr, i) - lse);
     if (i == t) p -= 1.f;
     dr[i] = __float2bfloat16(p * scale);
   }
@@ -87,10 +105,13 @@ ce_slab_kernel(const float* __restrict__ logits, long long ld, const long long* 
 }  // namespace mb
 using namespace mb;
 
-extern "C" int mb_ce_slab(const float* logits, long long ld, const long long* targets, float* loss,
+// logits: [R, V] slab, fp32 (logits_bf16 = 0) or bf16 (1); dlogits_bf16 may be the bf16 logits slab itself (in place)
+extern "C" int mb_ce_slab(const void* logits, int logits_bf16, long long ld, const long long* targets, float* loss,
                           void* dlogits_bf16, long long ldd, int R, int V, float scale, cudaStream_t stream) {
-  MB_REQUIRE(ld % 4 == 0 && (dlogits_bf16 == nullptr || ldd % 8 == 0), "ce_slab: row strides must keep 16-byte alignment");
+  MB_REQUIRE(ld % 8 == 0 && (dlogits_bf16 == nullptr || ldd % 8 == 0), "ce_slab: row strides must keep 16-byte alignment");
+  MB_REQUIRE(dlogits_bf16 != logits || logits_bf16, "ce_slab: the gradient can only overwrite a bf16 logits slab");
   if (R == 0) return 0;
-  ce_slab_kernel<<<R, kCeThreads, 0, stream>>>(logits, ld, targets, loss, (bf16*)dlogits_bf16, ldd, V, scale);
+  if (logits_bf16) ce_slab_kernel<true><<<R, kCeThreads, 0, stream>>>(logits, ld, targets, loss, (bf16*)dlogits_bf16, ldd, V, scale);
+  else ce_slab_kernel<false><<<R, kCeThreads, 0, stream>>>(logits, ld, targets, loss, (bf16*)dlogits_bf16, ldd, V, scale);
   return check_launch("ce_slab");
 }

@@ -73,8 +73,9 @@ int mb_cast_f32_bf16(const float* in, void* out_bf16, long long n, cudaStream_t 
 
 /* ---- K17: cross-entropy over a slab of lm_head logits: per-row loss and, in the same launch,
  *      (softmax - onehot) * scale in bf16 for the dgrad / wgrad GEMMs (ATen log_softmax + nll_loss
- *      fwd/bwd behind F.cross_entropy, /root/reference/model.py:43-46) ------------------------- */
-int mb_ce_slab(const float* logits, long long ld, const long long* targets, float* loss,
+ *      fwd/bwd behind F.cross_entropy, /root/reference/model.py:43-46).  The slab is bf16 in training
+ *      (the gradient then overwrites it in place) or fp32 for loss-only scoring -------------------- */
+int mb_ce_slab(const void* logits, int logits_bf16, long long ld, const long long* targets, float* loss,
                void* dlogits_bf16, long long ldd, int R, int V, float scale, cudaStream_t stream);
 
 /* ---- K16: bf16 GEMM on tcgen05/TMEM/TMA (cuBLAS behind nn.Linear) ------------------------- */

@@ -2,10 +2,12 @@
 
 The reference computes ``F.cross_entropy(lm_head(h))`` on fully materialised logits
 (/root/reference/model.py:35-46: 3.3 GB bf16 + 6.6 GB fp32 per micro-batch at B=32, T=1024).
-Here rows are processed in slabs: logits slab (tcgen05 GEMM, fp32 out) -> one kernel
-(``csrc/ce.cu``) computing the per-row loss and (p - onehot) * scale in bf16 -> dgrad and wgrad
-GEMMs, all inside forward, so only an ``[R, V]`` slab ever exists.  Backward just scales the stored ``dh`` / ``dW`` by the incoming
-scalar gradient."""
+Here rows are processed in slabs: logits slab (tcgen05 GEMM) -> one kernel (``csrc/ce.cu``) computing the
+per-row loss and (p - onehot) * scale in bf16 -> dgrad and wgrad GEMMs, all inside forward, so only an
+``[R, V]`` slab ever exists.  In training the slab is bf16 — the precision the reference's logits have under
+autocast — and the gradient overwrites the logits in place (one 0.6 GB buffer instead of a 1.2 GB fp32 slab plus
+a bf16 one); loss-only scoring (``eval.py``) keeps an fp32 slab.  Backward just scales the stored ``dh`` / ``dW``
+by the incoming scalar gradient."""
 from __future__ import annotations
 
 import torch
@@ -45,13 +47,14 @@ class LinearCrossEntropyFn(torch.autograd.Function):
         targets = targets.contiguous()
         slab = slab_rows(d, h2.device)
         R = min(slab, M)
-        logits = torch.empty(R, V, dtype=torch.float32, device=h2.device)
-        pb = torch.empty(R, V, dtype=torch.bfloat16, device=h2.device) if need_grad else None
+        # training: one bf16 slab, logits in, (p - onehot) * scale out, in place; scoring: fp32 logits, no gradient
+        logits = torch.empty(R, V, dtype=torch.bfloat16 if need_grad else torch.float32, device=h2.device)
+        pb = logits if need_grad else None
         for s in range(0, M, slab):
             e = min(M, s + slab)
             r = e - s
-            gemm_nt(h2[s:e], w, out=logits[:r])                      # tcgen05 GEMM, fp32 slab
-            call("mb_ce_slab", logits, V, targets[s:e], losses[s:e], pb, V, r, V, scale)
+            gemm_nt(h2[s:e], w, out=logits[:r])                      # tcgen05 GEMM into the slab
+            call("mb_ce_slab", logits, int(need_grad), V, targets[s:e], losses[s:e], pb, V, r, V, scale)
             if need_grad:
                 gemm_nn(pb[:r], w, out=dh[s:e])                      # dh   = (p - onehot) W
                 gemm_tn_acc(pb[:r], h2[s:e], dW)                     # dW  += (p - onehot)^T h
