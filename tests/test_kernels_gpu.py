@@ -184,6 +184,26 @@ def test_linear_fn_accumulates_weight_grad_in_place():
     assert len(calls) == 2
 
 
+def test_gemm_benchmark_rows_M32768():
+    """The in_proj shapes of the benchmark micro-batch (M = B*T = 32768, ragged N = 3352): forward, dgrad, wgrad."""
+    from mamba_distributed_b200.ops import native as nat
+    torch.manual_seed(3)
+    M, N, K = 32768, 3352, 768
+    x = torch.randn(M, K, device="cuda").bfloat16()
+    w = (torch.randn(N, K, device="cuda") / K ** 0.5).bfloat16()
+    y = nat.gemm_nt(x, w)
+    rows = torch.tensor([0, 1, 127, 128, 4095, 16384, 32767], device="cuda")
+    _close(y[rows], x[rows].float() @ w.float().t(), 3e-2, 2e-2, "y rows")
+    dy = (torch.randn(M, N, device="cuda") / N ** 0.5).bfloat16()
+    dx = nat.gemm_nn(dy, w)
+    _close(dx[rows], dy[rows].float() @ w.float(), 3e-2, 2e-2, "dx rows")
+    g = torch.zeros(N, K, device="cuda")
+    nat.gemm_tn_acc(dy, x, g)
+    cols = torch.tensor([0, 255, 256, 3327, 3328, 3351], device="cuda")
+    exp = dy[:, cols].float().t() @ x.float()
+    _close(g[cols], exp, 3e-2 * exp.abs().max().item(), 2e-2, "dW rows")
+
+
 @pytest.mark.parametrize("M,V,d", [(300, 50304, 256), (4500, 1024, 128)])
 @pytest.mark.parametrize("reduction", ["mean", "sum"])
 def test_linear_cross_entropy_fwd_bwd(M, V, d, reduction):

@@ -118,8 +118,9 @@ def test_mamba2_mixer_and_model_match_torch_path():
     bad = {}
     for n, p in m.named_parameters():
         e = _rel(g_native[n], p.grad)
-        # A_log / dt_bias gradients are heavily cancelling sums (see test above): direction only
-        lim = 0.6 if n.endswith(("A_log", "dt_bias")) else 8e-2
+        # measured on a B200: 0.4 - 1.6 % for every tensor, A_log / dt_bias included (their row / column sums are
+        # built from bit-identical bf16 operands, so the cancellation does not amplify the rounding)
+        lim = 3e-2
         if e > lim:
             bad[n] = e
     assert not bad, bad
@@ -186,3 +187,40 @@ def test_ssd_dt_limit_native():
         (_rel(g[0], gr[0]), _rel(g[1], gr[1]), _rel(g[6], gr[6]))
     frac_clamped = ((gr[1] == 0).float().mean()).item()
     assert 0.05 < frac_clamped < 0.95      # the clamp is active for part of the tokens
+
+
+def test_ssd_long_sequence_T8192():
+    """BASELINE.json config 4 geometry: 32 chunks per sequence (the inter-chunk recurrence is 32 deep), both state
+    paths, forward and every gradient against the fp32 oracle."""
+    from mamba_distributed_b200.ops import ssd_kernels, ssd_native
+    import pytest as _pt
+    x, dt, A, Bm, Cm, D, dt_bias = _mk(1, 8192, 4, 1, seed=11)
+    rl = [t.detach().float().requires_grad_(True) for t in (x, dt, A, Bm, Cm, D, dt_bias)]
+    y_ref = ref.ssd_chunked_ref(rl[0], rl[1], rl[2], rl[3], rl[4], 256, rl[5], None, rl[6], True)
+    dy = (y_ref.detach() - D.view(1, 1, 4, 1) * x.float()).bfloat16()
+    grads_ref = torch.autograd.grad(y_ref, rl, dy.float())
+    mp = _pt.MonkeyPatch()
+    try:
+        for seq in (True, False):
+            mp.setattr(ssd_kernels, "FORCE_SEQ_STATES", seq)
+            leaves = [t.clone().requires_grad_(True) for t in (x, dt, A, Bm, Cm, D, dt_bias)]
+            y = ssd_native.ssd_combined(*leaves[:5], 256, leaves[5], None, leaves[6], True)
+            assert _rel(y, y_ref) < 1.5e-2, (seq, _rel(y, y_ref))
+            grads = torch.autograd.grad(y, leaves, dy)
+            lim = {"dx": 1e-2, "dB": 1e-2, "dC": 1e-2, "dD": 1e-2, "ddt": 3e-2, "dA": 3e-2, "ddt_bias": 3e-2}
+            for n, g, gr in zip(["dx", "ddt", "dA", "dB", "dC", "dD", "ddt_bias"], grads, grads_ref):
+                assert _rel(g, gr) < lim[n], (seq, n, _rel(g, gr))
+    finally:
+        mp.undo()
+
+
+def test_ssd_benchmark_shape_rows():
+    """B * T = 32768 rows (the benchmark micro-batch) through the SSD kernels: forward vs the oracle on a slice of
+    heads (the oracle at 24 heads would need tens of GB)."""
+    from mamba_distributed_b200.ops import ssd_native
+    x, dt, A, Bm, Cm, D, dt_bias = _mk(32, 1024, 4, 1, seed=13)
+    y = ssd_native.ssd_combined(x, dt, A, Bm, Cm, 256, D, None, dt_bias, True)
+    for b0 in (0, 31):   # first and last sequence of the batch
+        y_ref = ref.ssd_chunked_ref(x[b0:b0 + 1].float(), dt[b0:b0 + 1].float(), A, Bm[b0:b0 + 1].float(),
+                                    Cm[b0:b0 + 1].float(), 256, D, None, dt_bias, True)
+        assert _rel(y[b0:b0 + 1], y_ref) < 1.5e-2

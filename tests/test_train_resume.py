@@ -87,3 +87,25 @@ def test_fused_checkpoint_and_resume_multi_gpu(tmp_path, world):
              "--total_batch_size", str(2 * 256 * world * 2), "--val_every", "4", "--val_steps", "1",
              "--sample_every", "1000", "--warmup_steps", "3", "--max_lr", "3e-3"]
     _check_resume(tmp_path, world, ["--cuda_graphs", "2"], 29751 + 10 * world, tol=2e-2, base=small)
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_loss_curve_matches_single_gpu_on_fresh_data(tmp_path, world):
+    """T6: the same global batch per step (fresh tokens from the loader every step, not a fixed ring) trained on 1 GPU
+    and on `world` GPUs gives the same loss curve within bf16 / reduction-order noise."""
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    cfg = ["--synthetic", "--d_model", "256", "--n_layer", "2", "--vocab_size", "50304", "--B", "2", "--T", "256",
+           "--total_batch_size", str(2 * 256 * 8), "--val_every", "1000", "--val_steps", "1", "--sample_every", "1000",
+           "--ckpt_every", "1000", "--warmup_steps", "3", "--max_lr", "3e-3", "--max_steps", "12"]
+    one = _torchrun(1, cfg + ["--log_dir", "log_w1"], str(tmp_path), 29811)
+    assert one.returncode == 0, (one.stdout[-2000:], one.stderr[-4000:])
+    many = _torchrun(world, cfg + ["--log_dir", f"log_w{world}"], str(tmp_path), 29821 + world)
+    assert many.returncode == 0, (many.stdout[-2000:], many.stderr[-4000:])
+    l1, ln = _losses(one.stdout), _losses(many.stdout)
+    assert sorted(l1) == sorted(ln) == list(range(12))
+    assert l1[11] < l1[0] - 0.5            # it trains
+    for s in range(12):
+        assert abs(l1[s] - ln[s]) <= 2e-2 * l1[s], (s, l1[s], ln[s])
