@@ -9,21 +9,26 @@
 //
 // Layout is channel-last ([B, T, Dn] activations, [B, T, N] for B/C, all possibly strided column
 // slices), N = 16.  No tensor-core content: a first-order recurrence.  Parallelisation: time is cut
-// into tiles of 64 tokens; one half-warp owns one channel of one (batch, tile) with one lane per
-// state n, so the state history of a tile lives in registers (needed by backward) and the sum
-// over n is four shuffles.  Tile-entry states come from a carry pass:
+// into tiles of 32 tokens; FOUR lanes own one channel of one (batch, tile), each lane carrying 4 of the
+// 16 states in registers (4 independent recurrences per thread: the FMA latency of one hides behind the
+// other three, and a sum over n is 3 in-thread adds + 2 shuffles instead of 4 shuffle rounds).  A block is
+// 32 channels x 4 lanes.  Tile-entry states come from a carry pass:
 //   fwd:  pass 1 per tile (decay product, local end state) -> sequential carry over tiles ->
 //         pass 2 per tile produces y (and keeps the tile-entry states for backward)
-//   bwd:  tiles in parallel using the stored entry states; the gradient flowing between tiles
-//         (dh at the tile boundary) is resolved with the same two-pass scheme in reverse.
+//   bwd:  tiles in parallel using the stored entry states (the state history of a tile is rebuilt into
+//         registers 8 steps at a time); the gradient flowing between tiles (dh at the tile boundary) is
+//         resolved with the same two-pass scheme in reverse.
 #include "common.cuh"
 #include "../include/mamba_b200.h"
 
 namespace mb {
 
 constexpr int kSN = 16;        // d_state
-constexpr int kSTile = 64;     // tokens per tile
-constexpr int kSChan = 8;      // channels per block (8 half-warps = 128 threads)
+constexpr int kSQ = 4;         // states per lane
+constexpr int kSTile = 32;     // tokens per tile
+constexpr int kSChan = 32;     // channels per block (32 x 4 lanes = 128 threads)
+constexpr int kSThreads = kSChan * (kSN / kSQ);
+constexpr float kLog2e = 1.4426950408889634f;
 
 struct SScanArgs {
   const bf16* u; long long ldu;
@@ -37,13 +42,27 @@ struct SScanArgs {
   int Bsz, T, Dn, ntiles, softplus;
 };
 
+// sum over a half-warp (single-token update kernel: one lane per state)
 __device__ __forceinline__ float half_warp_sum(float v) {
 #pragma unroll
   for (int o = 8; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
+// sum over the 4 lanes of a channel (lanes 4c .. 4c+3 of a warp)
+__device__ __forceinline__ float quad_sum(float v) {
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  return v;
+}
+// sum over the 8 channels of a warp for a fixed state quad (lanes q, q+4, ..., q+28)
+__device__ __forceinline__ float chan8_sum(float v) {
+  v += __shfl_xor_sync(0xffffffffu, v, 4);
+  v += __shfl_xor_sync(0xffffffffu, v, 8);
+  v += __shfl_xor_sync(0xffffffffu, v, 16);
+  return v;
+}
 
-// Per-token inputs of one (batch, tile, 8-channel block), staged in shared memory so that the 64-step
+// Per-token inputs of one (batch, tile, 32-channel block), staged in shared memory so that the 32-step
 // recurrences below never wait on global memory inside the loop (dt = 0 / u = 0 pad the ragged end: the
 // state then just carries through).
 struct SScanTile {
@@ -52,7 +71,7 @@ struct SScanTile {
 };
 __device__ __forceinline__ void sscan_stage(const SScanArgs& a, SScanTile& s, int b, int t0, int nt, int d0,
                                             bool want_u, bool want_b, bool want_c) {
-  for (int idx = threadIdx.x; idx < kSTile * kSChan; idx += blockDim.x) {
+  for (int idx = threadIdx.x; idx < kSTile * kSChan; idx += kSThreads) {
     const int i = idx / kSChan, cch = idx % kSChan, dch = d0 + cch;
     float dt = 0.f, uu = 0.f;
     if (i < nt && dch < a.Dn) {
@@ -63,7 +82,7 @@ __device__ __forceinline__ void sscan_stage(const SScanArgs& a, SScanTile& s, in
     }
     s.dt[i][cch] = dt; s.u[i][cch] = uu;
   }
-  for (int idx = threadIdx.x; idx < kSTile * kSN; idx += blockDim.x) {
+  for (int idx = threadIdx.x; idx < kSTile * kSN; idx += kSThreads) {
     const int i = idx / kSN, nn = idx % kSN;
     float bv = 0.f, cv = 0.f;
     if (i < nt) {
@@ -75,8 +94,28 @@ __device__ __forceinline__ void sscan_stage(const SScanArgs& a, SScanTile& s, in
   }
 }
 
-// pass 1: per (b, tile, d, n): P = prod_t exp(dt_t A), S = local end state from zero
-__global__ void __launch_bounds__(kSChan * kSN)
+struct Lane {
+  int q, dl, d;       // state quad, channel inside the block, channel (clamped to 0 when out of range)
+  bool active;
+  float2 An2[2];      // A[d, 4q + {0,1}] and A[d, 4q + {2,3}], times log2(e): exp(dt A) = ex2(dt * An2)
+};
+// exp2 of both halves of a pair (one MUFU each; everything around it is packed fp32: FMUL2 / FFMA2)
+__device__ __forceinline__ float2 ex2_pair(float2 x) { return f2(ex2_approx(x.x), ex2_approx(x.y)); }
+__device__ __forceinline__ Lane make_lane(const SScanArgs& a, int d0) {
+  Lane l;
+  l.q = threadIdx.x & 3;
+  l.dl = threadIdx.x >> 2;
+  const int dr = d0 + l.dl;
+  l.active = dr < a.Dn;
+  l.d = l.active ? dr : 0;
+  const float4 A4 = *reinterpret_cast<const float4*>(a.A + (size_t)l.d * kSN + l.q * kSQ);
+  l.An2[0] = f2(A4.x * kLog2e, A4.y * kLog2e);
+  l.An2[1] = f2(A4.z * kLog2e, A4.w * kLog2e);
+  return l;
+}
+
+// pass 1: per (b, tile, d, n): P = log of prod_t exp(dt_t A) = A sum_t dt_t, S = local end state from zero
+__global__ void __launch_bounds__(kSThreads)
 sscan_local_kernel(SScanArgs a, float* __restrict__ P, float* __restrict__ S) {
   __shared__ SScanTile st;
   const int tile = blockIdx.y, b = blockIdx.z;
@@ -84,21 +123,24 @@ sscan_local_kernel(SScanArgs a, float* __restrict__ P, float* __restrict__ S) {
   const int d0 = blockIdx.x * kSChan;
   sscan_stage(a, st, b, t0, nt, d0, true, true, false);
   __syncthreads();
-  const int n = threadIdx.x & (kSN - 1), dl = threadIdx.x >> 4;
-  const int d = d0 + dl;
-  if (d >= a.Dn) return;
-  const float An = a.A[d * kSN + n];
-  float h = 0.f, lp = 0.f;
+  const Lane l = make_lane(a, d0);
+  float2 h[2] = {f2(0.f, 0.f), f2(0.f, 0.f)};
+  float sum_dt = 0.f;
 #pragma unroll 8
   for (int i = 0; i < kSTile; ++i) {
-    const float dt = st.dt[i][dl];
-    const float la = dt * An;
-    lp += la;
-    h = fast_exp(la) * h + dt * st.B[i][n] * st.u[i][dl];
+    const float dt = st.dt[i][l.dl];
+    const float dtu = dt * st.u[i][l.dl];
+    const float4 b4 = *reinterpret_cast<const float4*>(&st.B[i][l.q * kSQ]);
+    const float2 bb[2] = {f2(b4.x, b4.y), f2(b4.z, b4.w)};
+    sum_dt += dt;
+#pragma unroll
+    for (int p = 0; p < 2; ++p) h[p] = fma2(ex2_pair(mul2(f2(dt, dt), l.An2[p])), h[p], mul2(f2(dtu, dtu), bb[p]));
   }
-  const size_t o = (((size_t)b * a.ntiles + tile) * a.Dn + d) * kSN + n;
-  P[o] = lp;  // log of the decay product (kept in log space: no underflow surprises)
-  S[o] = h;
+  if (!l.active) return;
+  const size_t o = (((size_t)b * a.ntiles + tile) * a.Dn + l.d) * kSN + l.q * kSQ;
+  const float k = sum_dt * 0.6931471805599453f;   // P stays in natural-log space (carry kernels use exp)
+  *reinterpret_cast<float4*>(P + o) = make_float4(k * l.An2[0].x, k * l.An2[0].y, k * l.An2[1].x, k * l.An2[1].y);
+  *reinterpret_cast<float4*>(S + o) = make_float4(h[0].x, h[0].y, h[1].x, h[1].y);
 }
 
 // carry: hin[tile] = state entering the tile  (forward order), one thread per (b, d, n)
@@ -115,8 +157,8 @@ __global__ void sscan_carry_fwd_kernel(const float* __restrict__ P, const float*
   }
 }
 
-// pass 2: output.  One half-warp per channel, lane = n.
-__global__ void __launch_bounds__(kSChan * kSN)
+// pass 2: output.  Four lanes per channel, 4 states each.
+__global__ void __launch_bounds__(kSThreads)
 sscan_fwd_kernel(SScanArgs a, const float* __restrict__ hin, bf16* __restrict__ y, long long ldy) {
   __shared__ SScanTile st;
   __shared__ float s_g[kSTile][kSChan];   // silu(z) on the way in, y on the way out
@@ -124,29 +166,38 @@ sscan_fwd_kernel(SScanArgs a, const float* __restrict__ hin, bf16* __restrict__ 
   const int t0 = tile * kSTile, nt = min(t0 + kSTile, a.T) - t0;
   const int d0 = blockIdx.x * kSChan;
   sscan_stage(a, st, b, t0, nt, d0, true, true, true);
-  for (int idx = threadIdx.x; idx < kSTile * kSChan; idx += blockDim.x) {
+  for (int idx = threadIdx.x; idx < kSTile * kSChan; idx += kSThreads) {
     const int i = idx / kSChan, cch = idx % kSChan, dch = d0 + cch;
     float gz = 1.f;
     if (a.z && i < nt && dch < a.Dn) gz = silu_f(__bfloat162float(a.z[((size_t)b * a.T + t0 + i) * a.ldz + dch]));
     s_g[i][cch] = gz;
   }
   __syncthreads();
-  const int n = threadIdx.x & (kSN - 1), dl = threadIdx.x >> 4;
-  const int d_real = d0 + dl;
-  const bool active = d_real < a.Dn;
-  const int d = active ? d_real : 0;
-  const float An = a.A[d * kSN + n];
-  const float Dd = a.D ? a.D[d] : 0.f;
-  float h = active ? hin[(((size_t)b * a.ntiles + tile) * a.Dn + d) * kSN + n] : 0.f;
+  const Lane l = make_lane(a, d0);
+  const float Dd = a.D ? a.D[l.d] : 0.f;
+  float2 h[2] = {f2(0.f, 0.f), f2(0.f, 0.f)};
+  if (l.active) {
+    const float4 h4 = *reinterpret_cast<const float4*>(hin + (((size_t)b * a.ntiles + tile) * a.Dn + l.d) * kSN + l.q * kSQ);
+    h[0] = f2(h4.x, h4.y); h[1] = f2(h4.z, h4.w);
+  }
 #pragma unroll 8
   for (int i = 0; i < kSTile; ++i) {
-    const float dt = st.dt[i][dl], uu = st.u[i][dl];
-    h = fast_exp(dt * An) * h + dt * st.B[i][n] * uu;
-    const float yy = half_warp_sum(st.C[i][n] * h);
-    if (n == 0) s_g[i][dl] = (yy + Dd * uu) * s_g[i][dl];   // only this lane reads / writes the slot
+    const float dt = st.dt[i][l.dl], uu = st.u[i][l.dl];
+    const float dtu = dt * uu;
+    const float4 b4 = *reinterpret_cast<const float4*>(&st.B[i][l.q * kSQ]);
+    const float4 c4 = *reinterpret_cast<const float4*>(&st.C[i][l.q * kSQ]);
+    const float2 bb[2] = {f2(b4.x, b4.y), f2(b4.z, b4.w)}, cc[2] = {f2(c4.x, c4.y), f2(c4.z, c4.w)};
+    float2 yp = f2(0.f, 0.f);
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+      h[p] = fma2(ex2_pair(mul2(f2(dt, dt), l.An2[p])), h[p], mul2(f2(dtu, dtu), bb[p]));
+      yp = fma2(cc[p], h[p], yp);
+    }
+    const float yy = quad_sum(yp.x + yp.y);
+    if (l.q == 0) s_g[i][l.dl] = (yy + Dd * uu) * s_g[i][l.dl];   // only this lane reads / writes the slot
   }
   __syncthreads();
-  for (int idx = threadIdx.x; idx < nt * kSChan; idx += blockDim.x) {
+  for (int idx = threadIdx.x; idx < nt * kSChan; idx += kSThreads) {
     const int i = idx / kSChan, cch = idx % kSChan, dch = d0 + cch;
     if (dch < a.Dn) y[((size_t)b * a.T + t0 + i) * ldy + dch] = __float2bfloat16(s_g[i][cch]);
   }
@@ -155,15 +206,14 @@ sscan_fwd_kernel(SScanArgs a, const float* __restrict__ hin, bf16* __restrict__ 
 // Backward, pass 1: per tile, with dh entering from the right assumed zero, compute the local
 // gradient that leaves the tile on the left: G = dh_{t0-1 <- tile} and the decay product (log).
 // Needs only C, dy, z, dt: dh_{t} = C_t dyy_t + exp(dt_{t+1} A) dh_{t+1}.
-__global__ void __launch_bounds__(kSChan * kSN)
-sscan_bwd_local_kernel(SScanArgs a, const bf16* __restrict__ dy, long long lddy, const float* __restrict__ hin,
-                       float* __restrict__ Gl) {
+__global__ void __launch_bounds__(kSThreads)
+sscan_bwd_local_kernel(SScanArgs a, const bf16* __restrict__ dy, long long lddy, float* __restrict__ Gl) {
   __shared__ SScanTile st;                 // u slot holds dyy = dy * silu(z)
   const int tile = blockIdx.y, b = blockIdx.z;
   const int t0 = tile * kSTile, nt = min(t0 + kSTile, a.T) - t0;
   const int d0 = blockIdx.x * kSChan;
   sscan_stage(a, st, b, t0, nt, d0, false, false, true);
-  for (int idx = threadIdx.x; idx < kSTile * kSChan; idx += blockDim.x) {
+  for (int idx = threadIdx.x; idx < kSTile * kSChan; idx += kSThreads) {
     const int i = idx / kSChan, cch = idx % kSChan, dch = d0 + cch;
     float dyy = 0.f;
     if (i < nt && dch < a.Dn) {
@@ -175,17 +225,21 @@ sscan_bwd_local_kernel(SScanArgs a, const bf16* __restrict__ dy, long long lddy,
     st.u[i][cch] = dyy;
   }
   __syncthreads();
-  const int n = threadIdx.x & (kSN - 1), dl = threadIdx.x >> 4;
-  const int d = d0 + dl;
-  if (d >= a.Dn) return;
-  const float An = a.A[d * kSN + n];
+  const Lane l = make_lane(a, d0);
   // gradient w.r.t. the state *entering* the tile, from the tile's own outputs only
-  float g = 0.f;  // dL/dh_t accumulated right-to-left (padding steps: dt = 0, dyy = 0 leave it unchanged)
+  float2 g[2] = {f2(0.f, 0.f), f2(0.f, 0.f)};  // dL/dh_t accumulated right-to-left (padding steps: dt = 0, dyy = 0 leave it unchanged)
 #pragma unroll 8
-  for (int i = kSTile - 1; i >= 0; --i)
-    g = (g + st.C[i][n] * st.u[i][dl]) * fast_exp(st.dt[i][dl] * An);  // after this line g = dL/dh_{t-1} through h_t
-  (void)hin;
-  Gl[(((size_t)b * a.ntiles + tile) * a.Dn + d) * kSN + n] = g;
+  for (int i = kSTile - 1; i >= 0; --i) {
+    const float dt = st.dt[i][l.dl], dyy = st.u[i][l.dl];
+    const float4 c4 = *reinterpret_cast<const float4*>(&st.C[i][l.q * kSQ]);
+    const float2 cc[2] = {f2(c4.x, c4.y), f2(c4.z, c4.w)};
+#pragma unroll
+    for (int p = 0; p < 2; ++p)   // now dL/dh_{t-1} through h_t
+      g[p] = mul2(fma2(cc[p], f2(dyy, dyy), g[p]), ex2_pair(mul2(f2(dt, dt), l.An2[p])));
+  }
+  if (!l.active) return;
+  *reinterpret_cast<float4*>(Gl + (((size_t)b * a.ntiles + tile) * a.Dn + l.d) * kSN + l.q * kSQ) =
+      make_float4(g[0].x, g[0].y, g[1].x, g[1].y);
 }
 
 // reverse carry: gin[tile] = dL/dh at the tile's right boundary (gradient w.r.t. the state leaving
@@ -203,28 +257,44 @@ __global__ void sscan_carry_bwd_kernel(const float* __restrict__ P, const float*
   }
 }
 
-// Backward, pass 2: everything.  Recomputes the tile's states from hin (kept in registers), then
+// Backward, pass 2: everything.  Rebuilds the tile's states from hin (8 steps at a time, in registers), then
 // walks right-to-left starting from gin.
 //
 // All per-token inputs of the tile are staged in shared memory first and all per-token outputs leave through
-// shared memory afterwards, so the two 64-step recurrences touch no global memory: with loads, stores and
-// atomics inside the loop every step paid a full global round trip (5.4 ms per call, 70 % of a Mamba-1 step).
-// dB[t, n] / dC[t, n] are sums over all channels: the block sums its 8 channels (warp shuffle + shared-memory
-// atomics) and issues one global atomic per (token, state).
-__global__ void __launch_bounds__(kSChan * kSN)
+// shared memory afterwards (they overwrite the input slots they no longer need), so the recurrences touch no
+// global memory.  The arithmetic runs on state PAIRS (FFMA2 / FMUL2: two fp32 lanes per issued instruction).
+// dB[t, n] / dC[t, n] are sums over all channels: every thread drops its 4 + 4 terms of a step into a shared
+// [8 steps][32 channels][16 states] buffer (one 16-byte store each), and after each block of 8 steps the CTA sums
+// the 32 channels with conflict-free loads — 18 instructions per thread and step instead of the 48 a shuffle
+// reduction over the warp's 8 channels costs; the block then issues one global atomic per (token, state).
+constexpr int kBwdBlk = 8;
+constexpr int kVStep = kSChan * kSN + 16;   // floats per step in the dB / dC term buffers: +16 keeps the two steps a warp sums in different banks
+constexpr int kBwdSmem = (6 * kSTile * kSChan + 2 * kSTile * kSN + 2 * kSTile * kSN + 2 * kBwdBlk * kVStep) * 4;
+
+__global__ void __launch_bounds__(kSThreads)
 sscan_bwd_kernel(SScanArgs a, const bf16* __restrict__ dy, long long lddy, const float* __restrict__ hin,
                  const float* __restrict__ gin, bf16* __restrict__ du, long long lddu, bf16* __restrict__ ddelta,
                  long long lddd, float* __restrict__ dA, float* __restrict__ dBf, float* __restrict__ dCf,
                  float* __restrict__ dD, bf16* __restrict__ dz, long long lddz, float* __restrict__ dbias) {
-  __shared__ float s_dt[kSTile][kSChan], s_u[kSTile][kSChan], s_dy[kSTile][kSChan], s_sig[kSTile][kSChan];
-  __shared__ float s_sz[kSTile][kSChan], s_dsz[kSTile][kSChan];
-  __shared__ float s_o_dt[kSTile][kSChan], s_o_du[kSTile][kSChan], s_o_dz[kSTile][kSChan];
-  __shared__ float s_B[kSTile][kSN], s_C[kSTile][kSN], s_dB[kSTile][kSN], s_dC[kSTile][kSN];
+  extern __shared__ __align__(16) float sm[];
+  // inputs; three of them are overwritten by outputs once consumed: s_sig -> d(delta), s_u -> du, s_dsz -> dz
+  float (*s_dt)[kSChan] = reinterpret_cast<float (*)[kSChan]>(sm);
+  float (*s_u)[kSChan] = s_dt + kSTile;
+  float (*s_dy)[kSChan] = s_u + kSTile;
+  float (*s_sig)[kSChan] = s_dy + kSTile;
+  float (*s_sz)[kSChan] = s_sig + kSTile;
+  float (*s_dsz)[kSChan] = s_sz + kSTile;
+  float (*s_B)[kSN] = reinterpret_cast<float (*)[kSN]>(s_dsz + kSTile);
+  float (*s_C)[kSN] = s_B + kSTile;
+  float (*s_dB)[kSN] = s_C + kSTile;       // [token][state] sums over the block's 32 channels
+  float (*s_dC)[kSN] = s_dB + kSTile;
+  float* s_vb = reinterpret_cast<float*>(s_dC + kSTile);   // [8 steps][32 channels][16 states] per-channel terms
+  float* s_vc = s_vb + kBwdBlk * kVStep;
   const int tile = blockIdx.y, b = blockIdx.z;
   const int t0 = tile * kSTile, t1 = min(t0 + kSTile, a.T);
   const int nt = t1 - t0;
   const int d0 = blockIdx.x * kSChan;
-  for (int idx = threadIdx.x; idx < kSTile * kSChan; idx += blockDim.x) {
+  for (int idx = threadIdx.x; idx < kSTile * kSChan; idx += kSThreads) {
     const int i = idx / kSChan, cch = idx % kSChan, dch = d0 + cch;
     float dt = 0.f, uu = 0.f, dyv = 0.f, sig = 0.f, sz = 1.f, dsz = 0.f;
     if (i < nt && dch < a.Dn) {
@@ -238,7 +308,7 @@ sscan_bwd_kernel(SScanArgs a, const bf16* __restrict__ dy, long long lddy, const
     }
     s_dt[i][cch] = dt; s_u[i][cch] = uu; s_dy[i][cch] = dyv; s_sig[i][cch] = sig; s_sz[i][cch] = sz; s_dsz[i][cch] = dsz;
   }
-  for (int idx = threadIdx.x; idx < kSTile * kSN; idx += blockDim.x) {
+  for (int idx = threadIdx.x; idx < kSTile * kSN; idx += kSThreads) {
     const int i = idx / kSN, nn = idx % kSN;
     float bv = 0.f, cv = 0.f;
     if (i < nt) {
@@ -246,75 +316,140 @@ sscan_bwd_kernel(SScanArgs a, const bf16* __restrict__ dy, long long lddy, const
       bv = __bfloat162float(a.Bm[row * a.ldb + nn]);
       cv = __bfloat162float(a.Cm[row * a.ldc + nn]);
     }
-    s_B[i][nn] = bv; s_C[i][nn] = cv; s_dB[i][nn] = 0.f; s_dC[i][nn] = 0.f;
+    s_B[i][nn] = bv; s_C[i][nn] = cv;
   }
   __syncthreads();
 
-  const int n = threadIdx.x & (kSN - 1), dl = threadIdx.x >> 4;
-  const int d_real = d0 + dl;
-  const bool active = d_real < a.Dn;     // inactive half-warps run along on channel 0 with zero inputs
-  const int d = active ? d_real : 0;
-  const float An = a.A[d * kSN + n];
-  const float Dd = a.D ? a.D[d] : 0.f;
-  const size_t o = (((size_t)b * a.ntiles + tile) * a.Dn + d) * kSN + n;
-  float hist[kSTile + 1];
-  hist[0] = active ? hin[o] : 0.f;
+  const Lane l = make_lane(a, d0);     // inactive channels run along on channel 0 with zero inputs
+  const float Dd = a.D ? a.D[l.d] : 0.f;
+  const size_t o = (((size_t)b * a.ntiles + tile) * a.Dn + l.d) * kSN + l.q * kSQ;
+  const float2 An[2] = {mul2(l.An2[0], f2(0.6931471805599453f, 0.6931471805599453f)),
+                        mul2(l.An2[1], f2(0.6931471805599453f, 0.6931471805599453f))};   // A in natural units
+  // State history: keeping all 32 x 4 states of a thread live costs > 255 registers.  Instead a first sweep keeps
+  // the state entering each block of 8 steps (4 x 4 values), and the backward walk rebuilds one block's 8 states
+  // at a time (9 x 4 values) right before it consumes them: a few more instructions per state, half the registers.
+  constexpr int kBlk = kBwdBlk, kNBlk = kSTile / kBlk;
+  float2 ck[kNBlk][2];   // indexed by the (rolled) block loops: lives in local memory, 16 values, touched once per block
+  {
+    const float4 h4 = l.active ? *reinterpret_cast<const float4*>(hin + o) : make_float4(0.f, 0.f, 0.f, 0.f);
+    float2 h[2] = {f2(h4.x, h4.y), f2(h4.z, h4.w)};
+    // (the block loops are deliberately NOT unrolled: unrolled, the compiler recognises the rebuild below as the same
+    // expressions as this sweep and keeps all 32 x 4 states live instead of recomputing them)
+#pragma unroll 1
+    for (int blk = 0; blk < kNBlk; ++blk) {
+      ck[blk][0] = h[0]; ck[blk][1] = h[1];
+      if (blk == kNBlk - 1) break;   // the last block's states are rebuilt below anyway
 #pragma unroll
-  for (int i = 0; i < kSTile; ++i) {
-    const float dt = s_dt[i][dl];   // 0 past the end of the tile: h carries through unchanged
-    hist[i + 1] = fast_exp(dt * An) * hist[i] + dt * s_B[i][n] * s_u[i][dl];
-  }
-  float g = active ? gin[o] : 0.f;  // dL/dh_{t1-1} coming from the right
-  float dA_acc = 0.f, dD_acc = 0.f, db_acc = 0.f;
+      for (int s2 = 0; s2 < kBlk; ++s2) {
+        const int i = blk * kBlk + s2;
+        const float dt = s_dt[i][l.dl];   // 0 past the end of the tile: h carries through unchanged
+        const float dtu = dt * s_u[i][l.dl];
+        const float4 b4 = *reinterpret_cast<const float4*>(&s_B[i][l.q * kSQ]);
+        const float2 bb[2] = {f2(b4.x, b4.y), f2(b4.z, b4.w)};
 #pragma unroll
-  for (int i = kSTile - 1; i >= 0; --i) {
-    if (i < nt) {   // uniform over the block
-      const float dt = s_dt[i][dl], uu = s_u[i][dl], Bn = s_B[i][n], Cn = s_C[i][n];
-      const float dyv = s_dy[i][dl], sz = s_sz[i][dl];
-      const float dyy = dyv * sz;                         // gradient into (ssm + D u)
-      const float h_t = hist[i + 1], h_prev = hist[i];
-      const float ssm = half_warp_sum(Cn * h_t);
-      g += Cn * dyy;                                      // dL/dh_t (total)
-      const float dec = fast_exp(dt * An);
-      const float ddt = half_warp_sum(g * (An * dec * h_prev + Bn * uu));
-      const float duu = half_warp_sum(g * dt * Bn);
-      dA_acc += g * dt * dec * h_prev;
-      float vb = g * dt * uu, vc = dyy * h_t;             // summed over channels d (inactive ones contribute 0)
-      vb += __shfl_xor_sync(0xffffffffu, vb, 16);
-      vc += __shfl_xor_sync(0xffffffffu, vc, 16);
-      if ((threadIdx.x & 16) == 0) { atomicAdd(&s_dB[i][n], vb); atomicAdd(&s_dC[i][n], vc); }
-      if (n == 0) {
-        const float draw = ddt * s_sig[i][dl];
-        s_o_dt[i][dl] = draw;
-        db_acc += draw;
-        s_o_du[i][dl] = duu + Dd * dyy;
-        dD_acc += dyy * uu;
-        s_o_dz[i][dl] = dyv * (ssm + Dd * uu) * s_dsz[i][dl];
+        for (int p = 0; p < 2; ++p) h[p] = fma2(ex2_pair(mul2(f2(dt, dt), l.An2[p])), h[p], mul2(f2(dtu, dtu), bb[p]));
       }
-      g *= dec;                                           // becomes dL/dh_{t-1} through h_t
     }
   }
-  if (active) {
-    atomicAdd(dA + d * kSN + n, dA_acc);
-    if (n == 0) {
-      if (dD) atomicAdd(dD + d, dD_acc);
-      if (dbias) atomicAdd(dbias + d, db_acc);
+  float2 g[2] = {f2(0.f, 0.f), f2(0.f, 0.f)};  // dL/dh_{t1-1} coming from the right
+  if (l.active) {
+    const float4 g4 = *reinterpret_cast<const float4*>(gin + o);
+    g[0] = f2(g4.x, g4.y); g[1] = f2(g4.z, g4.w);
+  }
+  float2 dA_acc[2] = {f2(0.f, 0.f), f2(0.f, 0.f)};
+  float dD_acc = 0.f, db_acc = 0.f;
+#pragma unroll 1
+  for (int blk = kNBlk - 1; blk >= 0; --blk) {
+    float2 hist[kBlk + 1][2];
+    hist[0][0] = ck[blk][0]; hist[0][1] = ck[blk][1];
+#pragma unroll
+    for (int s2 = 0; s2 < kBlk; ++s2) {
+      const int i = blk * kBlk + s2;
+      const float dt = s_dt[i][l.dl];
+      const float dtu = dt * s_u[i][l.dl];
+      const float4 b4 = *reinterpret_cast<const float4*>(&s_B[i][l.q * kSQ]);
+      const float2 bb[2] = {f2(b4.x, b4.y), f2(b4.z, b4.w)};
+#pragma unroll
+      for (int p = 0; p < 2; ++p)
+        hist[s2 + 1][p] = fma2(ex2_pair(mul2(f2(dt, dt), l.An2[p])), hist[s2][p], mul2(f2(dtu, dtu), bb[p]));
+    }
+#pragma unroll
+    for (int s2 = kBlk - 1; s2 >= 0; --s2) {
+      const int i = blk * kBlk + s2;
+      // steps past the end of the tile have dt = u = dy = 0 (staged so): they leave g unchanged and contribute zeros
+      const float dt = s_dt[i][l.dl], uu = s_u[i][l.dl];
+      const float dyv = s_dy[i][l.dl], sz = s_sz[i][l.dl];
+      const float4 b4 = *reinterpret_cast<const float4*>(&s_B[i][l.q * kSQ]);
+      const float4 c4 = *reinterpret_cast<const float4*>(&s_C[i][l.q * kSQ]);
+      const float2 bb[2] = {f2(b4.x, b4.y), f2(b4.z, b4.w)}, cc[2] = {f2(c4.x, c4.y), f2(c4.z, c4.w)};
+      const float dyy = dyv * sz;                         // gradient into (ssm + D u)
+      const float2 dyy2 = f2(dyy, dyy), uu2 = f2(uu, uu), dt2 = f2(dt, dt);
+      float2 ssm_p = f2(0.f, 0.f), ddt_p = f2(0.f, 0.f), du_p = f2(0.f, 0.f);
+      float2 vb[2], vc[2];
+#pragma unroll
+      for (int p = 0; p < 2; ++p) {
+        const float2 h_t = hist[s2 + 1][p], h_prev = hist[s2][p];
+        ssm_p = fma2(cc[p], h_t, ssm_p);
+        g[p] = fma2(cc[p], dyy2, g[p]);                   // dL/dh_t (total)
+        const float2 dec = ex2_pair(mul2(dt2, l.An2[p]));
+        const float2 dh = mul2(dec, h_prev);
+        ddt_p = fma2(g[p], fma2(An[p], dh, mul2(bb[p], uu2)), ddt_p);
+        du_p = fma2(g[p], bb[p], du_p);
+        const float2 gdt = mul2(g[p], dt2);
+        dA_acc[p] = fma2(gdt, dh, dA_acc[p]);
+        vb[p] = mul2(gdt, uu2);                           // dB[t, n] terms of this channel
+        vc[p] = mul2(dyy2, h_t);                          // dC[t, n] terms of this channel
+        g[p] = mul2(g[p], dec);                           // becomes dL/dh_{t-1} through h_t
+      }
+      const float ssm = quad_sum(ssm_p.x + ssm_p.y), ddt = quad_sum(ddt_p.x + ddt_p.y), duu = quad_sum(du_p.x + du_p.y) * dt;
+      *reinterpret_cast<float4*>(s_vb + s2 * kVStep + l.dl * kSN + l.q * kSQ) = make_float4(vb[0].x, vb[0].y, vb[1].x, vb[1].y);
+      *reinterpret_cast<float4*>(s_vc + s2 * kVStep + l.dl * kSN + l.q * kSQ) = make_float4(vc[0].x, vc[0].y, vc[1].x, vc[1].y);
+      if (l.q == 0) {
+        const float draw = ddt * s_sig[i][l.dl];
+        s_sig[i][l.dl] = draw;                            // d(delta) out
+        db_acc += draw;
+        s_u[i][l.dl] = duu + Dd * dyy;                    // du out (s_u of this step is dead for every lane of the warp)
+        dD_acc += dyy * uu;
+        s_dsz[i][l.dl] = dyv * (ssm + Dd * uu) * s_dsz[i][l.dl];   // dz out
+      }
+    }
+    // sum the 32 channels of this block of steps: thread -> (step, state), consecutive lanes = consecutive states
+    __syncthreads();
+    {
+      const int s2 = threadIdx.x >> 4, nn = threadIdx.x & 15;   // 128 threads = 8 steps x 16 states
+      const float* pb = s_vb + s2 * kVStep + nn;
+      const float* pc = s_vc + s2 * kVStep + nn;
+      float sb = 0.f, sc = 0.f;
+#pragma unroll 8
+      for (int c = 0; c < kSChan; ++c) { sb += pb[c * kSN]; sc += pc[c * kSN]; }
+      s_dB[blk * kBlk + s2][nn] = sb;
+      s_dC[blk * kBlk + s2][nn] = sc;
+    }
+    __syncthreads();
+  }
+  if (l.active) {
+    float* dAp = dA + (size_t)l.d * kSN + l.q * kSQ;
+    atomicAdd(dAp + 0, dA_acc[0].x); atomicAdd(dAp + 1, dA_acc[0].y);
+    atomicAdd(dAp + 2, dA_acc[1].x); atomicAdd(dAp + 3, dA_acc[1].y);
+    if (l.q == 0) {
+      if (dD) atomicAdd(dD + l.d, dD_acc);
+      if (dbias) atomicAdd(dbias + l.d, db_acc);
     }
   }
-  __syncthreads();
-  for (int idx = threadIdx.x; idx < nt * kSChan; idx += blockDim.x) {
+  for (int idx = threadIdx.x; idx < nt * kSChan; idx += kSThreads) {
     const int i = idx / kSChan, cch = idx % kSChan, dch = d0 + cch;
     if (dch < a.Dn) {
       const size_t row = (size_t)b * a.T + t0 + i;
-      ddelta[row * lddd + dch] = __float2bfloat16(s_o_dt[i][cch]);
-      du[row * lddu + dch] = __float2bfloat16(s_o_du[i][cch]);
-      if (a.z) dz[row * lddz + dch] = __float2bfloat16(s_o_dz[i][cch]);
+      ddelta[row * lddd + dch] = __float2bfloat16(s_sig[i][cch]);
+      du[row * lddu + dch] = __float2bfloat16(s_u[i][cch]);
+      if (a.z) dz[row * lddz + dch] = __float2bfloat16(s_dsz[i][cch]);
     }
   }
-  for (int idx = threadIdx.x; idx < nt * kSN; idx += blockDim.x) {
-    const size_t row = (size_t)b * a.T + t0 + idx / kSN;
-    atomicAdd(dBf + row * kSN + (idx % kSN), (&s_dB[0][0])[idx]);
-    atomicAdd(dCf + row * kSN + (idx % kSN), (&s_dC[0][0])[idx]);
+  for (int idx = threadIdx.x; idx < nt * kSN; idx += kSThreads) {
+    const int i = idx / kSN, nn = idx % kSN;
+    const size_t row = (size_t)b * a.T + t0 + i;
+    atomicAdd(dBf + row * kSN + nn, s_dB[i][nn]);
+    atomicAdd(dCf + row * kSN + nn, s_dC[i][nn]);
   }
 }
 
@@ -372,11 +507,11 @@ extern "C" int mb_sscan_fwd(const void* u, long long ldu, const void* delta, lon
   const size_t one = (size_t)B * a.ntiles * Dn * N;
   float *P = scratch, *S = scratch + one, *hin = scratch + 2 * one;
   dim3 grid(cdiv(Dn, kSChan), a.ntiles, B);
-  sscan_local_kernel<<<grid, kSChan * kSN, 0, stream>>>(a, P, S);
+  sscan_local_kernel<<<grid, kSThreads, 0, stream>>>(a, P, S);
   if (check_launch("sscan_fwd/local")) return 1;
   sscan_carry_fwd_kernel<<<cdiv((long long)B * Dn * N, 256), 256, 0, stream>>>(P, S, hin, B, a.ntiles, Dn * N);
   if (check_launch("sscan_fwd/carry")) return 1;
-  sscan_fwd_kernel<<<grid, kSChan * kSN, 0, stream>>>(a, hin, (bf16*)y, ldy);
+  sscan_fwd_kernel<<<grid, kSThreads, 0, stream>>>(a, hin, (bf16*)y, ldy);
   return check_launch("sscan_fwd");
 }
 
@@ -395,11 +530,13 @@ extern "C" int mb_sscan_bwd(const void* u, long long ldu, const void* delta, lon
   const float *P = scratch, *hin = scratch + 2 * one;
   float *Gl = scratch2, *gin = scratch2 + one;
   dim3 grid(cdiv(Dn, kSChan), a.ntiles, B);
-  sscan_bwd_local_kernel<<<grid, kSChan * kSN, 0, stream>>>(a, (const bf16*)dy, lddy, hin, Gl);
+  sscan_bwd_local_kernel<<<grid, kSThreads, 0, stream>>>(a, (const bf16*)dy, lddy, Gl);
   if (check_launch("sscan_bwd/local")) return 1;
   sscan_carry_bwd_kernel<<<cdiv((long long)B * Dn * N, 256), 256, 0, stream>>>(P, Gl, gin, B, a.ntiles, Dn * N);
   if (check_launch("sscan_bwd/carry")) return 1;
-  sscan_bwd_kernel<<<grid, kSChan * kSN, 0, stream>>>(a, (const bf16*)dy, lddy, hin, gin, (bf16*)du, lddu, (bf16*)ddelta,
+  static bool attr_set = false;
+  if (!attr_set) { MB_CUDA(cudaFuncSetAttribute(sscan_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem)); attr_set = true; }
+  sscan_bwd_kernel<<<grid, kSThreads, kBwdSmem, stream>>>(a, (const bf16*)dy, lddy, hin, gin, (bf16*)du, lddu, (bf16*)ddelta,
                                                       lddd, dA, dB, dC, dD, (bf16*)dz, lddz, dbias);
   return check_launch("sscan_bwd");
 }

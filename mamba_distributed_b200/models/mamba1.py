@@ -72,6 +72,10 @@ class Mamba(nn.Module):
             if inference_params.seqlen_offset > 0:
                 out, _, _ = self.step(hidden_states, conv_state, ssm_state)
                 return out
+        if ops.use_native(hidden_states) and inference_params is None and self.d_state == 16 \
+                and self.in_proj.bias is None and self.out_proj.bias is None and self.dt_rank % 8 == 0:
+            from ..ops import native
+            return native.mamba1_mixer(self, hidden_states)   # K6: the whole mixer as one autograd node
         xz = ops.linear(hidden_states, self.in_proj.weight, self.in_proj.bias)
         x, z = xz.chunk(2, dim=-1)
         if conv_state is not None:

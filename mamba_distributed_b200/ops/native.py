@@ -473,6 +473,106 @@ def mamba2_mixer(mod, u):
 
 
 # ------------------------------------------------------------------------------------------
+# K6: the whole Mamba-1 mixer as one autograd node
+# ------------------------------------------------------------------------------------------
+class Mamba1MixerFn(torch.autograd.Function):
+    """in_proj -> causal conv1d + SiLU -> x_proj -> dt_proj -> selective scan (softplus(dt + bias), D skip,
+    * silu(z)) -> out_proj, i.e. what ``mamba_inner_fn`` fuses upstream, with the conventions of
+    :class:`Mamba2MixerFn`: ``x | z`` and ``dt | B | C`` are consumed as column slices of the GEMM outputs (no
+    ``chunk`` / ``split`` copies), the scan writes ``dz`` straight into the z half of ``d(xz)``, every GEMM weight
+    gradient accumulates into the fp32 arena from the wgrad epilogue and the small parameters (conv, ``A_log``,
+    ``D``, ``dt_proj.bias``) add into their ``.grad`` slices.  Policy: store, don't recompute (upstream re-runs the
+    conv and dt_proj in backward to save memory; at 180 GB the activations are kept)."""
+
+    @staticmethod
+    def forward(ctx, u, in_w, conv_w, conv_b, xproj_w, dtproj_w, dtproj_b, A_log, D, out_w, cfg):
+        from . import sscan_kernels
+        Bsz, T, dm = u.shape
+        M = Bsz * T
+        d_in, R, N = cfg["d_inner"], cfg["dt_rank"], cfg["d_state"]
+        u2 = u.reshape(M, dm)
+        if u2.dtype != torch.bfloat16:
+            u2 = u2.to(torch.bfloat16)
+        u2 = u2.contiguous()
+        w_in, w_x, w_dt, w_out = (bf16_weight(w) for w in (in_w, xproj_w, dtproj_w, out_w))
+        xz = gemm_nt(u2, w_in)                                        # [M, 2 d_in] = x | z
+        cw = conv_w.reshape(d_in, -1).float().contiguous()
+        cb = conv_b.float().contiguous() if conv_b is not None else None
+        xc = torch.empty(M, d_in, dtype=torch.bfloat16, device=u.device)
+        k_conv1d_fwd(xz.view(Bsz, T, -1)[:, :, :d_in], cw, cb, xc.view(Bsz, T, d_in), True)
+        x_dbl = gemm_nt(xc, w_x)                                      # [M, R + 2N] = dt_low | B | C
+        dt = gemm_nt(x_dbl[:, :R], w_dt)                              # [M, d_in]; the bias is added inside the scan
+        A = -torch.exp(A_log.float())
+        y, scratch = sscan_kernels.sscan_fwd(xc.view(Bsz, T, d_in), dt.view(Bsz, T, d_in), A,
+                                             x_dbl.view(Bsz, T, -1)[:, :, R:R + N], x_dbl.view(Bsz, T, -1)[:, :, R + N:],
+                                             D.float(), xz.view(Bsz, T, -1)[:, :, d_in:], dtproj_b.float(), True)
+        y2 = y.view(M, d_in)
+        out = gemm_nt(y2, w_out)
+        ctx.save_for_backward(u2, xz, xc, x_dbl, dt, y2, scratch, A, in_w, conv_w, conv_b, xproj_w, dtproj_w, dtproj_b,
+                              A_log, D, out_w, cw, cb, w_in, w_x, w_dt, w_out)
+        ctx.cfg, ctx.dims, ctx.udtype = cfg, (Bsz, T, dm), u.dtype
+        return out.view(Bsz, T, dm)
+
+    @staticmethod
+    def backward(ctx, dout):
+        from . import sscan_kernels
+        (u2, xz, xc, x_dbl, dt, y2, scratch, A, in_w, conv_w, conv_b, xproj_w, dtproj_w, dtproj_b, A_log, D, out_w, cw, cb,
+         w_in, w_x, w_dt, w_out) = ctx.saved_tensors
+        cfg = ctx.cfg
+        Bsz, T, dm = ctx.dims
+        M = Bsz * T
+        d_in, R, N = cfg["d_inner"], cfg["dt_rank"], cfg["d_state"]
+        dout2 = dout.reshape(M, dm)
+        if dout2.dtype != torch.bfloat16 or not dout2.is_contiguous():
+            dout2 = dout2.to(torch.bfloat16).contiguous()
+        # out_proj
+        dy = gemm_nn(dout2, w_out)
+        gemm_tn_acc(dout2, y2, grad_buffer(out_w))
+        # selective scan: dz lands in the z half of d(xz); dB / dC come back as fp32 sums over channels
+        dxz = torch.empty_like(xz)
+        g_D, g_b = inplace_grad(D), inplace_grad(dtproj_b)
+        dxc, ddt, dA, dB, dC, dD, dbias = sscan_kernels.sscan_bwd(
+            xc.view(Bsz, T, d_in), dt.view(Bsz, T, d_in), A, x_dbl.view(Bsz, T, -1)[:, :, R:R + N],
+            x_dbl.view(Bsz, T, -1)[:, :, R + N:], D.float(), xz.view(Bsz, T, -1)[:, :, d_in:], dtproj_b.float(), True,
+            dy.view(Bsz, T, d_in), scratch, dz_out=dxz.view(Bsz, T, -1)[:, :, d_in:], dD_acc=g_D, dbias_acc=g_b)
+        g_A = inplace_grad(A_log)
+        if g_A is not None:
+            g_A.addcmul_(dA, A)                                       # A = -exp(A_log)  =>  dA_log = dA * A
+        dx_dbl = torch.empty_like(x_dbl)
+        dx_dbl[:, R:R + N].copy_(dB.view(M, N))
+        dx_dbl[:, R + N:].copy_(dC.view(M, N))
+        # dt_proj
+        ddt2 = ddt.view(M, d_in)
+        gemm_nn(ddt2, w_dt, out=dx_dbl[:, :R])
+        gemm_tn_acc(ddt2, x_dbl[:, :R], grad_buffer(dtproj_w))
+        # x_proj: its input gradient joins the scan's du
+        dxc2 = dxc.view(M, d_in)
+        dxc2.add_(gemm_nn(dx_dbl, w_x))
+        gemm_tn_acc(dx_dbl, xc, grad_buffer(xproj_w))
+        # conv
+        g_cw, g_cb = inplace_grad(conv_w), inplace_grad(conv_b)
+        dcw = g_cw.view(cw.shape) if g_cw is not None else torch.zeros_like(cw)
+        dcb = (g_cb if g_cb is not None else torch.zeros_like(cb)) if cb is not None else None
+        k_conv1d_bwd(xz.view(Bsz, T, -1)[:, :, :d_in], cw, cb, dxc2.view(Bsz, T, d_in),
+                     dxz.view(Bsz, T, -1)[:, :, :d_in], dcw, dcb, True)
+        # in_proj
+        du = gemm_nn(dxz, w_in).view(Bsz, T, dm)
+        gemm_tn_acc(dxz, u2, grad_buffer(in_w))
+        return (du.to(ctx.udtype), None,
+                None if g_cw is not None else dcw.view(conv_w.shape).to(conv_w.dtype),
+                None if (dcb is None or g_cb is not None) else dcb.to(conv_b.dtype),
+                None, None, None if g_b is not None else dbias.to(dtproj_b.dtype),
+                None if g_A is not None else (dA * A).to(A_log.dtype),
+                None if g_D is not None else dD.to(D.dtype), None, None)
+
+
+def mamba1_mixer(mod, u):
+    cfg = dict(d_inner=mod.d_inner, dt_rank=mod.dt_rank, d_state=mod.d_state)
+    return Mamba1MixerFn.apply(u, mod.in_proj.weight, mod.conv1d.weight, mod.conv1d.bias, mod.x_proj.weight,
+                               mod.dt_proj.weight, mod.dt_proj.bias, mod.A_log, mod.D, mod.out_proj.weight, cfg)
+
+
+# ------------------------------------------------------------------------------------------
 # K17: lm_head + cross-entropy
 # ------------------------------------------------------------------------------------------
 def linear_cross_entropy(h2, weight, targets, reduction):

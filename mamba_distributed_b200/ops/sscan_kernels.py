@@ -17,6 +17,45 @@ def _rowmajor(t, B, T):
     return t
 
 
+def _scratch_floats(Bsz, T, Dn, N):
+    lib = _lib.load()
+    lib.mb_sscan_scratch_floats.restype = __import__("ctypes").c_longlong
+    return int(lib.mb_sscan_scratch_floats(Bsz, T, Dn, N))
+
+
+def sscan_fwd(u, delta, A, Bm, Cm, D, z, delta_bias, softplus):
+    """Raw forward on ``[B, T, X]`` bf16 views (column slices allowed): returns ``(y, scratch)``; ``scratch`` goes
+    back to :func:`sscan_bwd` unchanged.  Used by ``native.Mamba1MixerFn``."""
+    Bsz, T, Dn = u.shape
+    N = A.shape[1]
+    scratch = torch.empty(_scratch_floats(Bsz, T, Dn, N), dtype=torch.float32, device=u.device)
+    y = torch.empty(Bsz, T, Dn, dtype=torch.bfloat16, device=u.device)
+    call("mb_sscan_fwd", u, u.stride(1), delta, delta.stride(1), A.float().contiguous(), Bm, Bm.stride(1), Cm,
+         Cm.stride(1), D, z, z.stride(1) if z is not None else 0, delta_bias, y, Dn, scratch, Bsz, T, Dn, N, int(softplus))
+    return y, scratch
+
+
+def sscan_bwd(u, delta, A, Bm, Cm, D, z, delta_bias, softplus, dy, scratch, dz_out=None, dD_acc=None, dbias_acc=None):
+    """Raw backward.  ``dz_out``: bf16 ``[B, T, Dn]`` view to receive dz (e.g. the z half of d(xz)); ``dD_acc`` /
+    ``dbias_acc``: fp32 ``[Dn]`` buffers the kernel ADDS into (parameter ``.grad``) instead of fresh tensors.
+    Returns ``(du, ddelta, dA, dB fp32 [B*T, N], dC fp32 [B*T, N], dD, dbias)``."""
+    Bsz, T, Dn = u.shape
+    N = A.shape[1]
+    dev = u.device
+    scratch2 = torch.empty(2 * (scratch.numel() // 3), dtype=torch.float32, device=dev)
+    du = torch.empty(Bsz, T, Dn, dtype=torch.bfloat16, device=dev)
+    ddelta = torch.empty_like(du)
+    dz = dz_out if dz_out is not None else (torch.empty_like(du) if z is not None else None)
+    dA = torch.zeros(Dn, N, dtype=torch.float32, device=dev)
+    dBC = torch.zeros(2, Bsz * T, N, dtype=torch.float32, device=dev)
+    dD = dD_acc if dD_acc is not None else torch.zeros(Dn, dtype=torch.float32, device=dev)
+    dbias = dbias_acc if dbias_acc is not None else torch.zeros(Dn, dtype=torch.float32, device=dev)
+    call("mb_sscan_bwd", u, u.stride(1), delta, delta.stride(1), A.float().contiguous(), Bm, Bm.stride(1), Cm,
+         Cm.stride(1), D, z, z.stride(1) if z is not None else 0, delta_bias, dy, dy.stride(1), scratch, scratch2, du, Dn,
+         ddelta, Dn, dA, dBC[0], dBC[1], dD, dz, dz.stride(1) if dz is not None else 0, dbias, Bsz, T, Dn, N, int(softplus))
+    return du, ddelta, dA, dBC[0], dBC[1], dD, dbias
+
+
 class SelectiveScanFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, u, delta, A, Bm, Cm, D, z, delta_bias, softplus):
