@@ -264,12 +264,12 @@ __global__ void sscan_carry_bwd_kernel(const float* __restrict__ P, const float*
 // shared memory afterwards (they overwrite the input slots they no longer need), so the recurrences touch no
 // global memory.  The arithmetic runs on state PAIRS (FFMA2 / FMUL2: two fp32 lanes per issued instruction).
 // dB[t, n] / dC[t, n] are sums over all channels: every thread drops its 4 + 4 terms of a step into a shared
-// [8 steps][32 channels][16 states] buffer (one 16-byte store each), and after each block of 8 steps the CTA sums
+// [4 steps][32 channels][16 states] buffer (one 16-byte store each), and after each block of 4 steps the CTA sums
 // the 32 channels with conflict-free loads — 18 instructions per thread and step instead of the 48 a shuffle
-// reduction over the warp's 8 channels costs; the block then issues one global atomic per (token, state).
-constexpr int kBwdBlk = 8;
+// reduction over the warp's 8 channels costs — and issues one global atomic per (token, state).
+constexpr int kBwdBlk = 4;   // steps per rebuilt block (4 keeps the term buffers at 17 KB -> 5 blocks per SM)
 constexpr int kVStep = kSChan * kSN + 16;   // floats per step in the dB / dC term buffers: +16 keeps the two steps a warp sums in different banks
-constexpr int kBwdSmem = (6 * kSTile * kSChan + 2 * kSTile * kSN + 2 * kSTile * kSN + 2 * kBwdBlk * kVStep) * 4;
+constexpr int kBwdSmem = (6 * kSTile * kSChan + 2 * kSTile * kSN + 2 * kBwdBlk * kVStep) * 4;
 
 __global__ void __launch_bounds__(kSThreads)
 sscan_bwd_kernel(SScanArgs a, const bf16* __restrict__ dy, long long lddy, const float* __restrict__ hin,
@@ -286,9 +286,7 @@ sscan_bwd_kernel(SScanArgs a, const bf16* __restrict__ dy, long long lddy, const
   float (*s_dsz)[kSChan] = s_sz + kSTile;
   float (*s_B)[kSN] = reinterpret_cast<float (*)[kSN]>(s_dsz + kSTile);
   float (*s_C)[kSN] = s_B + kSTile;
-  float (*s_dB)[kSN] = s_C + kSTile;       // [token][state] sums over the block's 32 channels
-  float (*s_dC)[kSN] = s_dB + kSTile;
-  float* s_vb = reinterpret_cast<float*>(s_dC + kSTile);   // [8 steps][32 channels][16 states] per-channel terms
+  float* s_vb = reinterpret_cast<float*>(s_C + kSTile);    // [4 steps][32 channels][16 states] per-channel terms
   float* s_vc = s_vb + kBwdBlk * kVStep;
   const int tile = blockIdx.y, b = blockIdx.z;
   const int t0 = tile * kSTile, t1 = min(t0 + kSTile, a.T);
@@ -326,8 +324,8 @@ sscan_bwd_kernel(SScanArgs a, const bf16* __restrict__ dy, long long lddy, const
   const float2 An[2] = {mul2(l.An2[0], f2(0.6931471805599453f, 0.6931471805599453f)),
                         mul2(l.An2[1], f2(0.6931471805599453f, 0.6931471805599453f))};   // A in natural units
   // State history: keeping all 32 x 4 states of a thread live costs > 255 registers.  Instead a first sweep keeps
-  // the state entering each block of 8 steps (4 x 4 values), and the backward walk rebuilds one block's 8 states
-  // at a time (9 x 4 values) right before it consumes them: a few more instructions per state, half the registers.
+  // the state entering each block of 4 steps, and the backward walk rebuilds one block's states at a time
+  // (5 x 4 values) right before it consumes them: a few more instructions per state, half the registers.
   constexpr int kBlk = kBwdBlk, kNBlk = kSTile / kBlk;
   float2 ck[kNBlk][2];   // indexed by the (rolled) block loops: lives in local memory, 16 values, touched once per block
   {
@@ -416,14 +414,15 @@ sscan_bwd_kernel(SScanArgs a, const bf16* __restrict__ dy, long long lddy, const
     // sum the 32 channels of this block of steps: thread -> (step, state), consecutive lanes = consecutive states
     __syncthreads();
     {
-      const int s2 = threadIdx.x >> 4, nn = threadIdx.x & 15;   // 128 threads = 8 steps x 16 states
-      const float* pb = s_vb + s2 * kVStep + nn;
-      const float* pc = s_vc + s2 * kVStep + nn;
-      float sb = 0.f, sc = 0.f;
+      // 128 threads = 4 steps x 16 states x {dB, dC}: each sums its 32 channel terms and adds them to the global
+      // fp32 [B*T, N] accumulator (one atomic per (token, state) and block of 32 channels)
+      const int which = threadIdx.x >> 6, s2 = (threadIdx.x >> 4) & 3, nn = threadIdx.x & 15;
+      const float* pv = (which ? s_vc : s_vb) + s2 * kVStep + nn;
+      float sv = 0.f;
 #pragma unroll 8
-      for (int c = 0; c < kSChan; ++c) { sb += pb[c * kSN]; sc += pc[c * kSN]; }
-      s_dB[blk * kBlk + s2][nn] = sb;
-      s_dC[blk * kBlk + s2][nn] = sc;
+      for (int c = 0; c < kSChan; ++c) sv += pv[c * kSN];
+      const int i = blk * kBlk + s2;
+      if (i < nt) atomicAdd((which ? dCf : dBf) + ((size_t)b * a.T + t0 + i) * kSN + nn, sv);
     }
     __syncthreads();
   }
@@ -444,12 +443,6 @@ sscan_bwd_kernel(SScanArgs a, const bf16* __restrict__ dy, long long lddy, const
       du[row * lddu + dch] = __float2bfloat16(s_u[i][cch]);
       if (a.z) dz[row * lddz + dch] = __float2bfloat16(s_dsz[i][cch]);
     }
-  }
-  for (int idx = threadIdx.x; idx < nt * kSN; idx += kSThreads) {
-    const int i = idx / kSN, nn = idx % kSN;
-    const size_t row = (size_t)b * a.T + t0 + i;
-    atomicAdd(dBf + row * kSN + nn, s_dB[i][nn]);
-    atomicAdd(dCf + row * kSN + nn, s_dC[i][nn]);
   }
 }
 
