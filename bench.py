@@ -445,6 +445,18 @@ def main(argv=None):
                                   "fraction_adamw_allgather": ag_ms / max(float(ct[1]), 1e-9),
                                   "nvlink_gbs_per_direction": 770, "hbm_gbs": 6500}
 
+    memory = None
+    if device_type == "cuda":
+        mem = torch.tensor([torch.cuda.max_memory_allocated(device), torch.cuda.max_memory_reserved(device)],
+                           dtype=torch.float64, device=device)
+        if ddp:
+            dist.all_reduce(mem, op=dist.ReduceOp.MAX)
+        impl = getattr(optimizer, "impl", None)
+        memory = {"max_allocated_gb": float(mem[0]) / 2 ** 30, "max_reserved_gb": float(mem[1]) / 2 ** 30,
+                  "optimizer_state_bytes_per_rank": int(2 * 4 * (impl.n_local if impl is not None else nparams)),
+                  "note": "high-water marks over the whole run, max over ranks; Adam moments are sharded over ranks "
+                          "(ZeRO-1) on the fused path"}
+
     if rank == 0:
         layer = "Mamba-2" if args.layer == "Mamba2" else "Mamba-1"
         print(json_line(
@@ -457,7 +469,7 @@ def main(argv=None):
                                          "one with its per-bucket reduce-scatter kernels)" if graph_last is not None else
                                          "non-final micro-steps replayed from one captured graph (forward+backward)"
                                          if graph is not None else "off")},
-            extra={"gpu_launches": int(counters.get("launches", 0)), "comm": comm_t}))
+            extra={"gpu_launches": int(counters.get("launches", 0)), "comm": comm_t, "memory": memory}))
     if fused:
         del graph, graph_last, graphs
         wrapped.close()

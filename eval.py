@@ -142,13 +142,24 @@ def evaluate(model_type="custom", hf_model_name: str = "state-spaces/mamba2-370m
     num_correct_norm = num_correct = num_total = 0
     pending = []
     import time
+    if dev_type == "cuda":
+        # untimed warm-up forward (library load, allocator, first-launch costs): the throughput printed below is
+        # the steady-state scoring rate, not process start-up
+        wt = torch.zeros(4, 64, dtype=torch.long, device=device)
+        with torch.autocast(dev_type, dtype=torch.bfloat16, enabled=use_bf16):
+            model.token_losses(wt[:, :-1], wt[:, 1:])
+        torch.cuda.synchronize()
+        if ddp:
+            dist.barrier()
     t_start = time.time()
+    scored_tokens = 0
 
     def flush():
-        nonlocal num_correct_norm, num_correct, num_total
+        nonlocal num_correct_norm, num_correct, num_total, scored_tokens
         if not pending:
             return
         toks, mask = hs.pack_batch([(t, m) for (_, t, m, _, _) in pending])
+        scored_tokens += toks.numel()
         toks, mask = toks.to(device), mask.to(device)
         with torch.autocast(dev_type, dtype=torch.bfloat16, enabled=use_bf16):
             # loss of predicting token t+1 from position t, for every row/position
@@ -184,16 +195,17 @@ def evaluate(model_type="custom", hf_model_name: str = "state-spaces/mamba2-370m
     flush()
 
     if ddp:
-        c = torch.tensor([num_total, num_correct, num_correct_norm], dtype=torch.long, device=device)
+        c = torch.tensor([num_total, num_correct, num_correct_norm, scored_tokens], dtype=torch.long, device=device)
         dist.all_reduce(c)
-        num_total, num_correct, num_correct_norm = c.tolist()
+        num_total, num_correct, num_correct_norm, scored_tokens = c.tolist()
     acc_norm = num_correct_norm / max(num_total, 1)
     if dev_type == "cuda":
         torch.cuda.synchronize()
     elapsed = time.time() - t_start
     if rank == 0:
-        print(f"scored {num_total} examples in {elapsed:.2f} s = {num_total / max(elapsed, 1e-9):.1f} examples/s "
-              f"({world} rank(s), {batch_examples} examples per forward)")
+        print(f"scored {num_total} examples in {elapsed:.2f} s = {num_total / max(elapsed, 1e-9):.1f} examples/s, "
+              f"{scored_tokens / max(elapsed, 1e-9):.0f} padded tokens/s "
+              f"({world} rank(s), {batch_examples} examples per forward, warm-up excluded)")
         os.makedirs("log", exist_ok=True)
         with open("log/hellaswag_eval.txt", "a") as file:
             file.write(f"{num_total} {num_correct_norm}/{num_total} {acc_norm:.4f}\n")

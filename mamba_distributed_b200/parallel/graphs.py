@@ -105,13 +105,12 @@ class MicroStepGraph:
         ``0 .. grad_accum-2``, the second the final one together with its reduce-scatter kernels (fused comm path
         only).  Either is ``None`` when it is not needed or does not fit; the caller then runs that micro-step
         eagerly.  COLLECTIVE when the world is larger than 1 (the sync graph's warm-up communicates)."""
-        g0 = cls.build_if_it_fits(ddp, loss_scale, shape, device=device, **kw) if grad_accum > 1 else None
-        g1 = None
-        if ddp.symm is not None and (g0 is not None or grad_accum == 1):
-            if g0 is not None:
-                g1 = cls(ddp, loss_scale, shape, device=device, sync=True, share_pool_with=g0, **kw)
-            else:
-                g1 = cls(ddp, loss_scale, shape, device=device, sync=True, **kw)
+        if ddp.symm is None:
+            return (cls.build_if_it_fits(ddp, loss_scale, shape, device=device, **kw) if grad_accum > 1 else None), None
+        # both graphs replay strictly one after the other and share one memory pool, and no micro-step runs eagerly
+        # any more: one working set has to fit, not two (2.7B at T = 8192 on a 180 GB GPU)
+        g0 = cls(ddp, loss_scale, shape, device=device, **kw) if grad_accum > 1 else None
+        g1 = cls(ddp, loss_scale, shape, device=device, sync=True, share_pool_with=g0, **kw)
         return g0, g1
 
     def _micro(self):
