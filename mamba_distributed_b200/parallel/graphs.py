@@ -43,8 +43,14 @@ class MicroStepGraph:
             side = torch.cuda.Stream(device=device)
             side.wait_stream(torch.cuda.current_stream(device))
             with torch.cuda.stream(side):          # PyTorch's capture recipe: warm up on a side stream
-                for _ in range(warmup):
-                    self._micro()
+                if self.sync and share_pool_with is not None:
+                    # the no-sync graph's warm-up already ran every forward / backward kernel; an eager pass here would
+                    # need a second working set outside the shared pool (2.7B at T = 8192 does not have one).  Only the
+                    # communication kernels are new: run those once on their own.
+                    self._warm_comm()
+                else:
+                    for _ in range(warmup):
+                        self._micro()
             torch.cuda.current_stream(device).wait_stream(side)
             torch.cuda.synchronize(device)
             torch.cuda.empty_cache()               # the warm-up's blocks belong to the side stream: give them back
@@ -62,6 +68,16 @@ class MicroStepGraph:
         finally:
             ddp.require_backward_grad_sync = prev
         self.replays = 0
+
+    def _warm_comm(self):
+        ddp, arena = self.ddp, self.ddp.symm
+        cur = torch.cuda.current_stream(arena.device)
+        arena.stamp(0, cur)
+        for b, (s, e, _) in enumerate(ddp.buckets):
+            arena.bucket_ready(b, s, e)
+        arena.stamp(1, arena.comm_stream)
+        cur.wait_stream(arena.comm_stream)
+        arena._launched.clear()
 
     def _after_sync_build(self):
         """The warm-up passes really ran the reduce-scatter kernels: their bucket flags carry the current step
@@ -109,8 +125,15 @@ class MicroStepGraph:
             return (cls.build_if_it_fits(ddp, loss_scale, shape, device=device, **kw) if grad_accum > 1 else None), None
         # both graphs replay strictly one after the other and share one memory pool, and no micro-step runs eagerly
         # any more: one working set has to fit, not two (2.7B at T = 8192 on a 180 GB GPU)
-        g0 = cls(ddp, loss_scale, shape, device=device, **kw) if grad_accum > 1 else None
-        g1 = cls(ddp, loss_scale, shape, device=device, sync=True, share_pool_with=g0, **kw)
+        g0 = g1 = None
+        try:
+            g0 = cls(ddp, loss_scale, shape, device=device, **kw) if grad_accum > 1 else None
+            g1 = cls(ddp, loss_scale, shape, device=device, sync=True, share_pool_with=g0, **kw)
+        except torch.OutOfMemoryError:
+            # not even one captured working set fits next to the model: every micro-step runs eagerly
+            # (all ranks see the same sizes, so they all take this branch together)
+            g0 = g1 = None
+            torch.cuda.empty_cache()
         return g0, g1
 
     def _micro(self):
