@@ -402,36 +402,67 @@ static EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-// 2-D fp32 row-major output map with a {32, 32} box (128-byte rows), 128B swizzle.
-int make_tmap_f32_2d(CUtensorMap* map, const void* ptr, long long rows, long long cols, long long ld) {
+// ---- tensor-map cache -----------------------------------------------------------------------------------------
+// A CUtensorMap is a pure function of (address, extents, strides, box, element type, swizzle): encoding the same
+// key twice gives the same 128 bytes, and nothing about it depends on what the memory currently holds or on who
+// owns the allocation.  Training reuses the same arenas and (under the caching allocator / graph pools) the same
+// activation addresses every step, so every launcher here asks this small per-thread table first: a GEMM call
+// drops from four driver encode calls to four hash probes.  Direct-mapped, 4096 entries; a collision just re-encodes.
+struct TmapKey {
+  const void* ptr;
+  unsigned long long d0, d1, d2, s0, s1;
+  unsigned int b0, b1, b2, kind;   // kind: element type | rank << 4 | swizzle << 8
+  bool operator==(const TmapKey& o) const {
+    return ptr == o.ptr && d0 == o.d0 && d1 == o.d1 && d2 == o.d2 && s0 == o.s0 && s1 == o.s1 && b0 == o.b0 && b1 == o.b1 &&
+           b2 == o.b2 && kind == o.kind;
+  }
+};
+struct TmapSlot { TmapKey key; CUtensorMap map; bool used; };
+constexpr int kTmapSlots = 4096;
+static thread_local TmapSlot* g_tmap_cache = nullptr;
+
+static int encode_cached(CUtensorMap* out, CUtensorMapDataType dt, int rank, const void* ptr, const cuuint64_t* dims,
+                         const cuuint64_t* strides, const cuuint32_t* box, CUtensorMapSwizzle swz) {
+  TmapKey k = {};
+  k.ptr = ptr;
+  k.d0 = dims[0]; k.d1 = dims[1]; k.d2 = rank > 2 ? dims[2] : 0;
+  k.s0 = strides[0]; k.s1 = rank > 2 ? strides[1] : 0;
+  k.b0 = box[0]; k.b1 = box[1]; k.b2 = rank > 2 ? box[2] : 0;
+  k.kind = (unsigned)dt | ((unsigned)rank << 4) | ((unsigned)swz << 8);
+  unsigned long long h = (unsigned long long)(uintptr_t)ptr * 0x9E3779B97F4A7C15ull;
+  h ^= (k.d0 * 0x100000001B3ull) ^ (k.d1 << 17) ^ (k.s0 << 7) ^ (k.s1 << 29) ^ ((unsigned long long)k.b1 << 40) ^ ((unsigned long long)k.b0 << 48) ^ k.kind;
+  h ^= h >> 29;
+  if (g_tmap_cache == nullptr) g_tmap_cache = static_cast<TmapSlot*>(calloc(kTmapSlots, sizeof(TmapSlot)));
+  TmapSlot* slot = g_tmap_cache != nullptr ? &g_tmap_cache[h & (kTmapSlots - 1)] : nullptr;
+  if (slot != nullptr && slot->used && slot->key == k) { *out = slot->map; return 0; }
   EncodeTiledFn enc = get_encode_fn();
   MB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point not available");
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(out, dt, (cuuint32_t)rank, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  MB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with %d (rank %d, dims %llu x %llu x %llu, stride %llu, box %u x %u)",
+             (int)r, rank, (unsigned long long)dims[0], (unsigned long long)dims[1], rank > 2 ? (unsigned long long)dims[2] : 0ull,
+             (unsigned long long)strides[0], box[0], box[1]);
+  if (slot != nullptr) { slot->key = k; slot->map = *out; slot->used = true; }
+  return 0;
+}
+
+// 2-D fp32 row-major output map with a {32, 32} box (128-byte rows), 128B swizzle.
+int make_tmap_f32_2d(CUtensorMap* map, const void* ptr, long long rows, long long cols, long long ld) {
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
   cuuint32_t box[2] = {32, 32};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(ptr), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  MB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(f32 out) failed with %d", (int)r);
-  return 0;
+  return encode_cached(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, ptr, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
 // 2-D bf16 row-major [rows, cols] (row stride ld elements) with a {64, box_rows} box, 128B swizzle.
 int make_tmap_bf16_2d(CUtensorMap* map, const void* ptr, long long rows, long long cols, long long ld, int box_rows) {
-  EncodeTiledFn enc = get_encode_fn();
-  MB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point not available");
   MB_REQUIRE(((uintptr_t)ptr & 15) == 0 && (ld * 2) % 16 == 0,
              "TMA operand must be 16-byte aligned with a row stride that is a multiple of 8 elements (ptr=%p ld=%lld)", ptr, ld);
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
   cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  MB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with %d (rows=%lld cols=%lld ld=%lld)", (int)r, rows, cols, ld);
-  return 0;
+  return encode_cached(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, ptr, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
 // 3-D bf16 [d2][d1][cols] view of a row-major matrix whose rows are (d2, d1) pairs (row stride ld elements),
@@ -439,20 +470,14 @@ int make_tmap_bf16_2d(CUtensorMap* map, const void* ptr, long long rows, long lo
 // as zeros and are dropped on stores (ragged last chunk of a sequence).
 int make_tmap_bf16_3d(CUtensorMap* map, const void* ptr, long long d2, long long d1, long long cols, long long ld,
                       int box_rows, int box_cols) {
-  EncodeTiledFn enc = get_encode_fn();
-  MB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point not available");
   MB_REQUIRE(((uintptr_t)ptr & 15) == 0 && (ld * 2) % 16 == 0,
              "TMA operand must be 16-byte aligned with a row stride that is a multiple of 8 elements (ptr=%p ld=%lld)", ptr, ld);
+  MB_REQUIRE(box_cols == 64 || box_cols == 32, "make_tmap_bf16_3d: box_cols must be 64 or 32");
   cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)d1, (cuuint64_t)d2};
   cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)d1 * (cuuint64_t)ld * 2};
-  MB_REQUIRE(box_cols == 64 || box_cols == 32, "make_tmap_bf16_3d: box_cols must be 64 or 32");
   cuuint32_t box[3] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows, 1};
-  cuuint32_t estr[3] = {1, 1, 1};
-  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, box_cols == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  MB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(3d) failed with %d (d2=%lld d1=%lld cols=%lld ld=%lld)", (int)r, d2, d1, cols, ld);
-  return 0;
+  return encode_cached(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, ptr, dims, strides, box,
+                       box_cols == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B);
 }
 
 template <int BN, uint32_t AM, uint32_t BMJ, int EPI, bool TS, int MODE>

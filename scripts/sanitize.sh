@@ -1,8 +1,9 @@
 #!/bin/bash
 # compute-sanitizer over the kernel test-suite.  usage: scripts/sanitize.sh [memcheck|racecheck|synccheck] [pytest -k expr]
-# NOTE: on the pool this was developed on compute-sanitizer is closed (the wrapper refuses to start it), so this target
-# has not been run there; the kernels' own guards are bounded mbarrier waits that trap, shape checks in every launcher,
-# ragged-shape tests (T = 300, N = 3352, K = 48) and bit-for-bit rerun comparisons (scripts/debug_determinism.py).
+# NOTE: on the pool this was developed on compute-sanitizer is closed (the wrapper refuses to start it; tried again in
+# round 2: gpurun_out/r2_sanitizer_memcheck.log / profiles/sanitizer_attempt_r2.log), so this target has not been run there;
+# the kernels' own guards are bounded mbarrier / peer-flag waits that trap, shape checks in every launcher, ragged-shape
+# tests (T = 300, N = 3352, K = 48) and bit-for-bit rerun comparisons.
 # One tool per gpurun call; memcheck slows the kernels ~10-50x, so the default selection is the small-shape tests.
 # The summary ("ERROR SUMMARY: N errors") lands in gpurun_out/sanitizer_<tool>.log.
 cd "$(dirname "$0")/.."
