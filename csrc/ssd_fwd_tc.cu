@@ -21,6 +21,7 @@ constexpr int kThreads = 256;
 // ------------------------------------------------------------------------------------------
 constexpr int kOuterHalf = 128;  // K rows staged per pass: 2 passes keep smem at 64 KB -> 3 CTAs / SM
 constexpr int kOuterSmem = 2 * (kOuterHalf * 2 * 128) + 2 * kL * 4 + 64 + 1024;
+constexpr int kSeqSmem = kOuterSmem + 2 * 2 * 2 * kL * 4;   // + the a | dt stages of ssd_states_seq_kernel
 
 template <bool DSTATE>
 __global__ void __launch_bounds__(kThreads, 3)
@@ -145,7 +146,8 @@ ssd_states_seq_kernel(const bf16* __restrict__ arow, long long lda, const __grid
   uint8_t* sA = smem;                                // [128 k-rows][2 atoms]  MN-major A
   uint8_t* sB = smem + kOuterHalf * 2 * 128;         // [128 k-rows][2 atoms]  MN-major B
   float* s_scale = reinterpret_cast<float*>(smem + 2 * kOuterHalf * 2 * 128);  // [2][256]
-  uint64_t* bar = reinterpret_cast<uint64_t*>(s_scale + 2 * kL);
+  float* s_raw = s_scale + 2 * kL;   // [2 stages][2 heads][a(256) | dt(256)]: a | dt of the NEXT chunk, by cp.async
+  uint64_t* bar = reinterpret_cast<uint64_t*>(s_raw + 2 * 2 * 2 * kL);
   uint64_t* ld_bar = bar + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 2);
 
@@ -174,17 +176,34 @@ ssd_states_seq_kernel(const bf16* __restrict__ arow, long long lda, const __grid
     }
   }
   uint32_t mma_phase = 0, ld_phase = 0;
+  // a | dt of a chunk (2 heads x 256 tokens x 2 values = 4 KB) are fetched one chunk ahead with cp.async: their
+  // global latency was 14 % of this kernel's stall samples when each chunk loaded them on the spot.
+  auto fetch_adt = [&](int c_, int stage) {
+    const int bc_ = b * nc + c_;
+    for (int idx = tid; idx < 2 * kL; idx += kThreads) {
+      const int h2 = idx / kL, t = idx % kL;
+      const size_t base = ((size_t)bc_ * H + h0 + h2) * kL + t;
+      const uint32_t dst = smem_u32(s_raw + (stage * 2 + h2) * 2 * kL + t);
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(av + base) : "memory");
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + kL * 4), "l"(dtv + base) : "memory");
+    }
+    cp_async_commit();
+  };
+  fetch_adt(DSTATE ? nc - 1 : 0, 0);
   for (int ci = 0; ci < nc; ++ci) {
     const int c = DSTATE ? nc - 1 - ci : ci;
     const int bc = b * nc + c;
     const int valid = min(kL, T - c * kL);
+    if (ci + 1 < nc) { fetch_adt(DSTATE ? c - 1 : c + 1, (ci + 1) & 1); cp_async_wait<1>(); }
+    else cp_async_wait<0>();
+    __syncthreads();   // this chunk's a | dt (copied by all threads) are visible
+    const float* ra = s_raw + (ci & 1) * 2 * 2 * kL;
     for (int idx = tid; idx < 2 * kL; idx += kThreads) {
       const int h2 = idx / kL, t = idx % kL;
-      const size_t base = ((size_t)bc * H + h0 + h2) * kL;
-      const float a = av[base + t];
-      s_scale[h2 * kL + t] = DSTATE ? fast_exp(a) : fast_exp(av[base + kL - 1] - a) * dtv[base + t];
+      const float a = ra[h2 * 2 * kL + t];
+      s_scale[h2 * kL + t] = DSTATE ? fast_exp(a) : fast_exp(ra[h2 * 2 * kL + kL - 1] - a) * ra[h2 * 2 * kL + kL + t];
     }
-    const float decay = fast_exp(av[((size_t)bc * H + h0 + hh) * kL + kL - 1]);
+    const float decay = fast_exp(ra[hh * 2 * kL + kL - 1]);
     __syncthreads();   // scale vector visible; the previous chunk's TMA stores have finished reading the operand buffers
     const size_t row0 = (size_t)b * T + (size_t)c * kL;
     for (int half = 0; half < kL / kOuterHalf; ++half) {
@@ -815,13 +834,13 @@ extern "C" int mb_ssd_states_seq(const void* arow, long long lda, const void* bo
       make_tmap_bf16_3d(&tmBop, bop, B, T, (long long)G * N, ldb, kOuterHalf, 64)) return 1;
   if (dstate) {
     static bool once = false;
-    if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_states_seq_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kOuterSmem)); once = true; }
-    ssd_states_seq_kernel<true><<<grid, kThreads, kOuterSmem, stream>>>((const bf16*)arow, lda, tmBop, dt, a, tmOut, (const bf16*)sprev_bf16,
+    if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_states_seq_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSeqSmem)); once = true; }
+    ssd_states_seq_kernel<true><<<grid, kThreads, kSeqSmem, stream>>>((const bf16*)arow, lda, tmBop, dt, a, tmOut, (const bf16*)sprev_bf16,
                                                                         da_last, init, last_out, T, H, G, nc);
   } else {
     static bool once = false;
-    if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_states_seq_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kOuterSmem)); once = true; }
-    ssd_states_seq_kernel<false><<<grid, kThreads, kOuterSmem, stream>>>((const bf16*)arow, lda, tmBop, dt, a, tmOut, nullptr, nullptr,
+    if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_states_seq_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSeqSmem)); once = true; }
+    ssd_states_seq_kernel<false><<<grid, kThreads, kSeqSmem, stream>>>((const bf16*)arow, lda, tmBop, dt, a, tmOut, nullptr, nullptr,
                                                                          init, last_out, T, H, G, nc);
   }
   return check_launch("ssd_states_seq");
