@@ -99,11 +99,11 @@ def iterate_examples(split, synthetic=False, limit=2000):
     if not synthetic and not os.path.exists(path):
         try:
             download(split)
-        except Exception as e:  # no network
-            print(f"HellaSwag download failed ({type(e).__name__}); using synthetic examples")
+        except Exception as e:  # no network: fail like the reference does instead of quietly scoring generated examples
             if os.path.exists(path):
                 os.remove(path)
-            synthetic = True
+            raise RuntimeError(f"HellaSwag download failed ({type(e).__name__}: {e}); pass --synthetic to score "
+                               f"generated examples of the same shape instead") from e
     if synthetic:
         yield from hs.synthetic_examples(limit)
     else:
@@ -208,7 +208,9 @@ def evaluate(model_type="custom", hf_model_name: str = "state-spaces/mamba2-370m
               f"({world} rank(s), {batch_examples} examples per forward, warm-up excluded)")
         os.makedirs("log", exist_ok=True)
         with open("log/hellaswag_eval.txt", "a") as file:
-            file.write(f"{num_total} {num_correct_norm}/{num_total} {acc_norm:.4f}\n")
+            # reference line format (/root/reference/eval.py:181-182); generated examples are tagged so that the
+            # file cannot be mistaken for a HellaSwag result
+            file.write(f"{num_total} {num_correct_norm}/{num_total} {acc_norm:.4f}{' synthetic' if synthetic else ''}\n")
         print(f"final: acc {num_correct}/{num_total}={num_correct/max(num_total,1):.4f} "
               f"acc_norm {num_correct_norm}/{num_total}={acc_norm:.4f}")
     return {"num_total": num_total, "num_correct": num_correct, "num_correct_norm": num_correct_norm,
