@@ -508,6 +508,112 @@ gated_rmsnorm_bwd_rows_staged_kernel(const bf16* __restrict__ x, int ldx, const 
 template <int NV, int WARPS>
 constexpr int staged_smem_bytes(int D) { return WARPS * 2 * 3 * NV * 32 * 16 + D * 4 + WARPS * 264 * 4; }
 
+// add + RMSNorm backward with the same cp.async row pipeline as the gated kernel above: r (fp32), dy (bf16) and the
+// incoming residual gradient (fp32) of the NEXT row are copied into the warp's second stage while the current row is
+// processed, so neither the first loads nor the late dres_in loads of the plain kernel (issued only after the row
+// reduction) expose their latency.  Weight vector in shared memory; dw accumulated in registers across rows.
+template <int NV, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32)
+add_rmsnorm_bwd_staged_kernel(const float* __restrict__ r, const bf16* __restrict__ dy, const float* __restrict__ rstd_in,
+                              const float* __restrict__ weight, const float* dres_in, float* dres_out,
+                              bf16* __restrict__ dx_bf16, float* __restrict__ dw_partial, int M, int D) {
+  extern __shared__ __align__(16) uint8_t st_smem[];
+  constexpr int RB = NV * 32 * 32;     // bytes of one staged fp32 row (D = NV * 256)
+  constexpr int GB = NV * 32 * 16;     // bytes of one staged bf16 row
+  constexpr int STAGE = 2 * RB + GB;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint8_t* my = st_smem + (size_t)warp * 2 * STAGE;
+  float* s_w = reinterpret_cast<float*>(st_smem + (size_t)WARPS * 2 * STAGE);
+  float* red = s_w + D;
+  for (int i = threadIdx.x; i < D; i += WARPS * 32) s_w[i] = weight[i];
+  __syncthreads();
+  const bool has_res = dres_in != nullptr;
+  auto issue = [&](int row, int stage) {
+    uint8_t* base = my + stage * STAGE;
+    const size_t off = (size_t)row * D;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vec = lane + 32 * i;
+      cp_async_16(base + vec * 32, r + off + vec * 8);
+      cp_async_16(base + vec * 32 + 16, r + off + vec * 8 + 4);
+      cp_async_16(base + 2 * RB + vec * 16, dy + off + vec * 8);
+      if (has_res) {
+        cp_async_16(base + RB + vec * 32, dres_in + off + vec * 8);
+        cp_async_16(base + RB + vec * 32 + 16, dres_in + off + vec * 8 + 4);
+      }
+    }
+  };
+  float dw[NV][8];
+#pragma unroll
+  for (int i = 0; i < NV; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dw[i][j] = 0.f;
+  const int stride = gridDim.x * WARPS;
+  int row = blockIdx.x * WARPS + warp;
+  if (row < M) issue(row, 0);
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  for (int stage = 0; row < M; row += stride, stage ^= 1) {
+    if (row + stride < M) issue(row + stride, stage ^ 1);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+    const uint8_t* base = my + stage * STAGE;
+    const float rstd = rstd_in[row];
+    float xh[NV][8], wdy[NV][8];
+    float c = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vec = lane + 32 * i;
+      float g[8], w[8];
+      ld8f(reinterpret_cast<const float*>(base + vec * 32), xh[i]);
+      bf16x8 pg;
+      memcpy(&pg, base + 2 * RB + vec * 16, 16);
+      unpack8(pg, g);
+      ld8f(s_w + vec * 8, w);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        xh[i][j] *= rstd;
+        wdy[i][j] = g[j] * w[j];
+        dw[i][j] += g[j] * xh[i][j];
+        c += xh[i][j] * wdy[i][j];
+      }
+    }
+    c = warp_sum(c) / (float)D;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vec = lane + 32 * i;
+      const size_t off = (size_t)row * D + vec * 8;
+      float o[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = (wdy[i][j] - xh[i][j] * c) * rstd;
+      if (has_res) {
+        float a[8];
+        ld8f(reinterpret_cast<const float*>(base + RB + vec * 32), a);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] += a[j];
+      }
+      st8f(dres_out + off, o);
+      if (dx_bf16 != nullptr) st8(dx_bf16 + off, pack8(o));
+    }
+  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  float* my_partial = dw_partial + (size_t)blockIdx.x * D;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 8; ++j) red[warp * 264 + lane * 8 + j] = dw[i][j];
+    __syncthreads();
+    for (int k = threadIdx.x; k < 256; k += WARPS * 32) {
+      float sum = 0.f;
+#pragma unroll
+      for (int ww = 0; ww < WARPS; ++ww) sum += red[ww * 264 + k];
+      my_partial[i * 256 + k] = sum;
+    }
+  }
+}
+template <int NV, int WARPS>
+constexpr int add_staged_smem_bytes(int D) { return WARPS * 2 * (2 * NV * 32 * 32 + NV * 32 * 16) + D * 4 + WARPS * 264 * 4; }
+
 static int bwd_grid(int rows) {
   int g = cdiv(rows, kWarpsPerBlock);
   int cap = num_sms() * 8;
@@ -561,7 +667,31 @@ extern "C" int mb_add_rmsnorm_bwd(const float* r, const void* dy, const float* r
   MB_REQUIRE(D % 8 == 0 && D <= 8192, "add_rmsnorm_bwd: D=%d must be a multiple of 8 and <= 8192", D);
   if (M == 0) return 0;
   const int nv = cdiv(D, 256);
-  const int grid = bwd_grid(M);
+  int grid = bwd_grid(M);
+  if (D % 256 == 0 && (nv == 3 || nv == 6 || nv == 10)) {   // 280M / 780M / 2.7B widths: cp.async row pipeline
+#define LAUNCH_ADD_STAGED(NV_, W_)                                                                                     \
+    {                                                                                                                  \
+      auto kern = add_rmsnorm_bwd_staged_kernel<NV_, W_>;                                                              \
+      const int smem = add_staged_smem_bytes<NV_, W_>(D);                                                              \
+      static int per_sm = 0;                                                                                           \
+      if (per_sm == 0) {                                                                                               \
+        MB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));                        \
+        MB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, W_ * 32, smem));                          \
+        if (per_sm < 1) per_sm = 1;                                                                                    \
+      }                                                                                                                \
+      int g2 = cdiv(M, W_);                                                                                            \
+      if (g2 > num_sms() * per_sm) g2 = num_sms() * per_sm;                                                            \
+      if (g2 > grid) g2 = grid;   /* never more partial rows than the caller's scratch holds */                        \
+      grid = g2;                                                                                                       \
+      kern<<<grid, W_ * 32, smem, stream>>>(r, (const bf16*)dy, rstd, weight, dres_in, dres_out, (bf16*)dx_bf16,      \
+                                           scratch, M, D);                                                             \
+    }
+    if (nv == 3) LAUNCH_ADD_STAGED(3, 4) else if (nv == 6) LAUNCH_ADD_STAGED(6, 2) else LAUNCH_ADD_STAGED(10, 2)
+#undef LAUNCH_ADD_STAGED
+    if (check_launch("add_rmsnorm_bwd/staged")) return 1;
+    colsum_partials_kernel<<<cdiv(D, 32), 1024, 0, stream>>>(scratch, dw, grid, D, dw_accumulate);
+    return check_launch("add_rmsnorm_bwd/colsum");
+  }
   DISPATCH_NV(nv, {
     add_rmsnorm_bwd_kernel<NV><<<grid, kWarpsPerBlock * 32, 0, stream>>>(
         r, (const bf16*)dy, rstd, weight, dres_in, dres_out, (bf16*)dx_bf16, scratch, M, D);
