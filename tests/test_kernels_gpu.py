@@ -128,7 +128,7 @@ def test_gated_rmsnorm_fwd_bwd(M, D, G):
     _close(wn.grad, wr.grad, 3e-2 * M ** 0.5, 3e-2, "dw")
 
 
-@pytest.mark.parametrize("B,T,C,W", [(2, 64, 1792, 4), (3, 100, 512, 4), (1, 7, 64, 4), (2, 130, 1536, 4), (2, 65, 128, 3), (1, 40, 128, 2)])
+@pytest.mark.parametrize("B,T,C,W", [(2, 64, 1792, 4), (5, 1027, 1792, 4), (3, 100, 512, 4), (1, 7, 64, 4), (2, 130, 1536, 4), (2, 65, 128, 3), (1, 40, 128, 2)])
 def test_conv1d_fwd_bwd(B, T, C, W):
     nat = _native()
     torch.manual_seed(0)
