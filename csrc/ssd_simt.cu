@@ -12,34 +12,46 @@
 
 namespace mb {
 
-// one block = one (b, c); thread t = token c*L + t (L == blockDim.x == 256 or 128 or 64)
+// one block = one (b, c, group of kPrepHeads heads); thread t = token c*L + t (L == blockDim.x == 256 or 128 or 64).
+// Eight heads per block: the eight dt loads of a thread are independent and issue together, each of the block's
+// warps scans one head, and the grid is 3x the (b, c) count -- one block per (b, c) walking all heads in turn
+// left 128 blocks serialising 24 dependent load + softplus rounds (15 us for 5 MB).
+constexpr int kPrepHeads = 8;
 __global__ void ssd_prep_kernel(const bf16* __restrict__ dt_raw, long long ld_dt,
                                 const float* __restrict__ dt_bias, const float* __restrict__ A_log,
                                 float* __restrict__ dt_out, float* __restrict__ a_out, int T, int H, int L,
                                 int nc, float dt_min, float dt_max) {
-  extern __shared__ float sm[];  // [H][L] dA, then scanned in place
+  extern __shared__ float sm[];  // [kPrepHeads][L] dA, then scanned in place
   const int b = blockIdx.x / nc, c = blockIdx.x % nc;
+  const int h0 = blockIdx.y * kPrepHeads;
   const int t = threadIdx.x;
-  const int tok = c * L + t;
-  const bool valid = tok < T;
+  const int tok = min(c * L + t, T - 1);
+  const bool valid = c * L + t < T;
   const bf16* src = dt_raw + ((size_t)b * T + tok) * ld_dt;
   float* dt_o = dt_out + ((size_t)(b * nc + c) * H) * L;
   float* a_o = a_out + ((size_t)(b * nc + c) * H) * L;
-  for (int h = 0; h < H; ++h) {
-    float dt = 0.f;
-    if (valid) dt = fminf(fmaxf(softplus_f(__bfloat162float(src[h]) + dt_bias[h]), dt_min), dt_max);  // dt_limit
-    dt_o[(size_t)h * L + t] = dt;
-    sm[h * L + t] = dt * (-fast_exp(A_log[h]));
+  float raw[kPrepHeads];
+#pragma unroll
+  for (int i = 0; i < kPrepHeads; ++i) raw[i] = __bfloat162float(src[min(h0 + i, H - 1)]);
+#pragma unroll
+  for (int i = 0; i < kPrepHeads; ++i) {
+    const int h = h0 + i;
+    if (h < H) {
+      float dt = 0.f;
+      if (valid) dt = fminf(fmaxf(softplus_f(raw[i] + dt_bias[h]), dt_min), dt_max);  // dt_limit
+      dt_o[(size_t)h * L + t] = dt;
+      sm[i * L + t] = dt * (-fast_exp(A_log[h]));
+    }
   }
   __syncthreads();
-  // inclusive scan over t for each h: warp w handles heads w, w+nw, ...
+  // inclusive scan over t for each head: warp w handles heads w, w+nw, ...
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
   const int per = L / 32;  // consecutive elements per lane
-  for (int h = warp; h < H; h += nw) {
-    float* row = sm + h * L;
+  for (int i = warp; i < kPrepHeads && h0 + i < H; i += nw) {
+    const float* row = sm + i * L;
     float run = 0.f;
     float loc[8];
-    for (int i = 0; i < per; ++i) { run += row[lane * per + i]; loc[i] = run; }
+    for (int k = 0; k < per; ++k) { run += row[lane * per + k]; loc[k] = run; }
     float incl = run;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -47,7 +59,7 @@ __global__ void ssd_prep_kernel(const bf16* __restrict__ dt_raw, long long ld_dt
       if (lane >= o) incl += v;
     }
     const float excl = incl - run;
-    for (int i = 0; i < per; ++i) a_o[(size_t)h * L + lane * per + i] = loc[i] + excl;
+    for (int k = 0; k < per; ++k) a_o[(size_t)(h0 + i) * L + lane * per + k] = loc[k] + excl;
   }
 }
 
@@ -133,13 +145,15 @@ __global__ void ssd_bwd_finalize_kernel(const bf16* __restrict__ dy, long long l
   __shared__ float wsum[8];
   __shared__ float red3[2][8];
   __shared__ float s_rowpart[256];
-  const int b = blockIdx.x / nc, c = blockIdx.x % nc;
+  // heads are the fastest grid index: blocks resident together read neighbouring 128-byte pieces of the same dY /
+  // y_off rows (and write neighbouring bf16 d(dt) columns), not the same piece of 128 different chunks
+  const int b = blockIdx.y / nc, c = blockIdx.y % nc;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5, nw = blockDim.x >> 5;
   const int tok = c * L + t;
   const bool valid = tok < T;
   const size_t row = (size_t)b * T + tok;
   {
-    const int h = blockIdx.y;
+    const int h = blockIdx.x;
     const size_t sidx = ((size_t)(b * nc + c) * H + h) * L + t;
     const float A = -fast_exp(A_log[h]);
     const float dtv = dt[sidx];
@@ -267,11 +281,9 @@ extern "C" int mb_ssd_prep(const void* dt_raw, long long ld_dt, const float* dt_
                            cudaStream_t stream) {
   MB_REQUIRE(L == 64 || L == 128 || L == 256, "ssd_prep: chunk size %d not in {64,128,256}", L);
   const int nc = cdiv(T, L);
-  const size_t smem = (size_t)H * L * sizeof(float);
-  MB_REQUIRE(smem <= 200 * 1024, "ssd_prep: H*L too large for shared memory");
-  if (smem > 48 * 1024) MB_CUDA(cudaFuncSetAttribute(ssd_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  ssd_prep_kernel<<<B * nc, L, smem, stream>>>((const bf16*)dt_raw, ld_dt, dt_bias, A_log, dt_out, a_out, T, H, L, nc,
-                                               dt_min, dt_max);
+  const size_t smem = (size_t)kPrepHeads * L * sizeof(float);
+  ssd_prep_kernel<<<dim3(B * nc, cdiv(H, kPrepHeads)), L, smem, stream>>>((const bf16*)dt_raw, ld_dt, dt_bias, A_log, dt_out,
+                                                                          a_out, T, H, L, nc, dt_min, dt_max);
   return check_launch("ssd_prep");
 }
 
@@ -306,7 +318,8 @@ extern "C" int mb_ssd_bwd_finalize(const void* dy, long long lddy, const void* y
   MB_REQUIRE(P == 8 || P == 16 || P == 32 || P == 64 || P == 128 || P == 256,
              "ssd_bwd_finalize: headdim %d must be a power of two in [8, 256] (lanes of one row reduce by shuffles)", P);
   const int nc = cdiv(T, L);
-  ssd_bwd_finalize_kernel<<<dim3(B * nc, H), L, 0, stream>>>((const bf16*)dy, lddy, (const bf16*)y_off, ldy,
+  MB_REQUIRE((long long)B * nc <= 65535, "ssd_bwd_finalize: B * chunks = %lld exceeds the grid's y extent", (long long)B * nc);
+  ssd_bwd_finalize_kernel<<<dim3(H, B * nc), L, 0, stream>>>((const bf16*)dy, lddy, (const bf16*)y_off, ldy,
                                                     (const bf16*)dt_raw, ld_dt, dt, ddt1, ddt2, rowsum_m, da_last, dt_bias,
                                                     A_log, (bf16*)draw_out, ld_draw, dA_log, ddt_bias, T, H, P, L, nc,
                                                     dt_min, dt_max);
