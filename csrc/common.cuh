@@ -70,27 +70,11 @@ __device__ __forceinline__ float ex2_approx(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
   return r;
 }
-#ifdef MB_SIGMOID_NEWTON
-// 1 / d for d in [1, 1e30] on the FMA pipe: bit-trick seed (5 % off) + two Newton steps -> 7e-6 relative error.
-__device__ __forceinline__ float2 rcp2_newton(float2 d) {
-  float2 r = f2(__int_as_float(0x7EF311C7 - __float_as_int(d.x)), __int_as_float(0x7EF311C7 - __float_as_int(d.y)));
-  const float2 nd = f2(-d.x, -d.y), two = f2(2.f, 2.f);
-  r = mul2(r, fma2(nd, r, two));
-  r = mul2(r, fma2(nd, r, two));
-  return r;
-}
-__device__ __forceinline__ float2 sigmoid2(float2 x) {
-  const float2 t = mul2(x, f2(-1.4426950408889634f, -1.4426950408889634f));
-  const float2 d = add2(f2(ex2_approx(fminf(t.x, 96.f)), ex2_approx(fminf(t.y, 96.f))), f2(1.f, 1.f));
-  return rcp2_newton(d);
-}
-#else
 __device__ __forceinline__ float2 sigmoid2(float2 x) {
   const float2 t = mul2(x, f2(-1.4426950408889634f, -1.4426950408889634f));
   const float2 d = add2(f2(ex2_approx(t.x), ex2_approx(t.y)), f2(1.f, 1.f));
   return f2(rcp_approx(d.x), rcp_approx(d.y));
 }
-#endif
 __device__ __forceinline__ float2 silu2(float2 x) { return mul2(x, sigmoid2(x)); }
 // silu and its derivative s + x*s*(1-s) = s * (1 + x - x*s) from one sigmoid
 __device__ __forceinline__ void silu_both2(float2 x, float2& f, float2& df) {
