@@ -36,6 +36,8 @@ ce_slab_kernel(const void* logits, long long ld, const long long* __restrict__ t
                float* __restrict__ loss, bf16* dlogits, long long ldd, int V, float scale) {
   __shared__ float s_m[kCeThreads / 32], s_s[kCeThreads / 32];
   __shared__ float s_max, s_lse;
+  pdl_wait();      // common.cuh: programmatic dependent launch
+  pdl_trigger();
   const int row = blockIdx.x, tid = threadIdx.x;
   const void* lr = reinterpret_cast<const char*>(logits) + (size_t)row * ld * (BF16_IN ? 2 : 4);
   const int nv8 = V >> 3;
@@ -111,7 +113,9 @@ extern "C" int mb_ce_slab(const void* logits, int logits_bf16, long long ld, con
   MB_REQUIRE(ld % 8 == 0 && (dlogits_bf16 == nullptr || ldd % 8 == 0), "ce_slab: row strides must keep 16-byte alignment");
   MB_REQUIRE(dlogits_bf16 != logits || logits_bf16, "ce_slab: the gradient can only overwrite a bf16 logits slab");
   if (R == 0) return 0;
-  if (logits_bf16) ce_slab_kernel<true><<<R, kCeThreads, 0, stream>>>(logits, ld, targets, loss, (bf16*)dlogits_bf16, ldd, V, scale);
-  else ce_slab_kernel<false><<<R, kCeThreads, 0, stream>>>(logits, ld, targets, loss, (bf16*)dlogits_bf16, ldd, V, scale);
+  if (logits_bf16)
+    MB_CUDA(launch_pdl(ce_slab_kernel<true>, dim3(R), dim3(kCeThreads), 0, stream, logits, ld, targets, loss, (bf16*)dlogits_bf16, ldd, V, scale));
+  else
+    MB_CUDA(launch_pdl(ce_slab_kernel<false>, dim3(R), dim3(kCeThreads), 0, stream, logits, ld, targets, loss, (bf16*)dlogits_bf16, ldd, V, scale));
   return check_launch("ce_slab");
 }

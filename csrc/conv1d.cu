@@ -50,6 +50,8 @@ conv1d_fwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __rest
     for (int k = 0; k < W; ++k) wt[j][k] = f2(w[(c0 + 2 * j) * W + k], w[(c0 + 2 * j + 1) * W + k]);
     bs[j] = bias != nullptr ? f2(bias[c0 + 2 * j], bias[c0 + 2 * j + 1]) : f2(0.f, 0.f);
   }
+  pdl_wait();      // common.cuh: programmatic dependent launch
+  pdl_trigger();
   uint8_t* my = conv_smem + threadIdx.x * 16;                 // row r of the ring lives at my + r * (threads * 16)
   const uint32_t my_s = (uint32_t)__cvta_generic_to_shared(my);
   constexpr int kRowBytes = kConvThreads * 16;
@@ -202,6 +204,8 @@ conv1d_bwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __rest
     bs[j] = bias != nullptr ? f2(bias[c0 + 2 * j], bias[c0 + 2 * j + 1]) : f2(0.f, 0.f);
     dba[j] = f2(0.f, 0.f);
   }
+  pdl_wait();      // common.cuh: programmatic dependent launch
+  pdl_trigger();
   const int flat_end = min((tl + 1) * tile, N);
   for (int flat = tl * tile; flat < flat_end;) {   // one segment per sequence the flat tile touches
   const int b = flat / T;
@@ -462,8 +466,8 @@ extern "C" int mb_conv1d_fwd(const void* x, long long ldx, const float* w, const
     int tile, ntiles;
     const int ngroups = cdiv(C / 8, 32);
     conv_flat_tiles((long long)B * T, ngroups, per_sm * (kConvThreads / 32), &tile, &ntiles);
-    conv1d_fwd_kernel<W, S><<<cdiv(ntiles * ngroups, kConvThreads / 32), kConvThreads, kFwdSmem, stream>>>(
-        (const bf16*)x, ldx, w, bias, (bf16*)y, ldy, T, C, B * T, tile, ntiles, ngroups);
+    MB_CUDA(launch_pdl(conv1d_fwd_kernel<W, S>, dim3(cdiv(ntiles * ngroups, kConvThreads / 32)), dim3(kConvThreads), kFwdSmem,
+                       stream, (const bf16*)x, ldx, w, bias, (bf16*)y, ldy, T, C, B * T, tile, ntiles, ngroups));
   });
   return check_launch("conv1d_fwd");
 }
@@ -489,9 +493,9 @@ extern "C" int mb_conv1d_bwd(const void* x, long long ldx, const float* w, const
     int tile, ntiles;
     const int ngroups = cdiv(C / (2 * kBwdNP), 32);
     conv_flat_tiles((long long)B * T, ngroups, per_sm * (kConvThreads / 32), &tile, &ntiles);
-    conv1d_bwd_kernel<W, S, kBwdNP><<<cdiv(ntiles * ngroups, kConvThreads / 32), kConvThreads, conv_bwd_smem<kBwdNP>(),
-                                      stream>>>((const bf16*)x, ldx, w, bias, (const bf16*)dy, lddy, (bf16*)dx, lddx, dw,
-                                                dbias, T, C, B * T, tile, ntiles, ngroups);
+    MB_CUDA(launch_pdl(conv1d_bwd_kernel<W, S, kBwdNP>, dim3(cdiv(ntiles * ngroups, kConvThreads / 32)), dim3(kConvThreads),
+                       conv_bwd_smem<kBwdNP>(), stream, (const bf16*)x, ldx, w, bias, (const bf16*)dy, lddy, (bf16*)dx, lddx,
+                       dw, dbias, T, C, B * T, tile, ntiles, ngroups));
   });
   return check_launch("conv1d_bwd");
 }

@@ -121,6 +121,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (PAIR) cluster_sync_all();  // the peer's barriers exist before anything signals them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // everything above (barriers, TMEM, tensor-map prefetch) overlapped the previous kernel's tail (common.cuh: PDL)
+  pdl_wait();
+  pdl_trigger();
 
   if (warp == 0) {
     // ================================ TMA producer =====================================
@@ -499,13 +502,15 @@ static int launch_gemm_mode(const CUtensorMap& ta, const CUtensorMap& tb, const 
   cfg.blockDim = dim3(kGemmThreads);
   cfg.dynamicSmemBytes = GemmCfg<BN, MODE>::SMEM;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CL;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = pdl_for(stream) ? 2 : 1;
   MB_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, td, D, bias, M, N, K, ldd, splitk, kb_per_split, alpha));
   return check_launch("gemm_bf16");
 }

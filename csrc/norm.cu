@@ -22,6 +22,8 @@ add_rmsnorm_fwd_kernel(const void* __restrict__ xin, const float* __restrict__ r
                        const float* __restrict__ weight, bf16* __restrict__ y,
                        float* __restrict__ res_out, float* __restrict__ rstd_out, int M, int D,
                        float eps) {
+  pdl_wait();      // common.cuh: programmatic dependent launch
+  pdl_trigger();
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
   if (row >= M) return;
@@ -152,6 +154,8 @@ add_rmsnorm_bwd_kernel(const float* __restrict__ r, const bf16* __restrict__ dy,
 __global__ void colsum_partials_kernel(const float* __restrict__ partial, float* __restrict__ dw,
                                        int P, int D, int accumulate) {
   __shared__ float red[32][33];
+  pdl_wait();      // common.cuh: programmatic dependent launch
+  pdl_trigger();
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int col = blockIdx.x * 32 + tx;
   float s = 0.f;
@@ -419,8 +423,10 @@ gated_rmsnorm_fwd_staged_kernel(const bf16* __restrict__ x, int ldx, const bf16*
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   uint8_t* my = st_smem + (size_t)warp * (2 * 2 * ROWB);
   float* s_w = reinterpret_cast<float*>(st_smem + (size_t)WARPS * 2 * 2 * ROWB);
-  for (int i = threadIdx.x; i < D; i += WARPS * 32) s_w[i] = weight[i];
+  for (int i = threadIdx.x; i < D; i += WARPS * 32) s_w[i] = weight[i];   // a parameter: nothing the previous kernel wrote
   __syncthreads();
+  pdl_wait();      // common.cuh: programmatic dependent launch
+  pdl_trigger();
   auto issue = [&](int row, int stage) {
     uint8_t* base = my + stage * 2 * ROWB;
 #pragma unroll
@@ -485,8 +491,10 @@ gated_rmsnorm_bwd_rows_staged_kernel(const bf16* __restrict__ x, int ldx, const 
   uint8_t* my = st_smem + (size_t)warp * (2 * 3 * ROWB);
   float* s_w = reinterpret_cast<float*>(st_smem + (size_t)WARPS * 2 * 3 * ROWB);
   float* red = s_w + D;                              // [WARPS][256 + 8] for the final dw fold
-  for (int i = threadIdx.x; i < D; i += WARPS * 32) s_w[i] = weight[i];
+  for (int i = threadIdx.x; i < D; i += WARPS * 32) s_w[i] = weight[i];   // a parameter: nothing the previous kernel wrote
   __syncthreads();
+  pdl_wait();      // common.cuh: programmatic dependent launch
+  pdl_trigger();
   auto issue = [&](int row, int stage) {
     uint8_t* base = my + stage * 3 * ROWB;
 #pragma unroll
@@ -593,8 +601,10 @@ add_rmsnorm_bwd_staged_kernel(const float* __restrict__ r, const bf16* __restric
   uint8_t* my = st_smem + (size_t)warp * 2 * STAGE;
   float* s_w = reinterpret_cast<float*>(st_smem + (size_t)WARPS * 2 * STAGE);
   float* red = s_w + D;
-  for (int i = threadIdx.x; i < D; i += WARPS * 32) s_w[i] = weight[i];
+  for (int i = threadIdx.x; i < D; i += WARPS * 32) s_w[i] = weight[i];   // a parameter: nothing the previous kernel wrote
   __syncthreads();
+  pdl_wait();      // common.cuh: programmatic dependent launch
+  pdl_trigger();
   const bool has_res = dres_in != nullptr;
   auto issue = [&](int row, int stage) {
     uint8_t* base = my + stage * STAGE;
@@ -717,9 +727,9 @@ extern "C" int mb_add_rmsnorm_fwd(const void* x, int x_is_fp32, const float* res
   dim3 grid(cdiv(M, kWarpsPerBlock)), block(kWarpsPerBlock * 32);
   DISPATCH_NV(nv, {
     if (x_is_fp32)
-      add_rmsnorm_fwd_kernel<NV, true><<<grid, block, 0, stream>>>(x, residual, weight, (bf16*)y, res_out, rstd, M, D, eps);
+      MB_CUDA(launch_pdl(add_rmsnorm_fwd_kernel<NV, true>, grid, block, 0, stream, x, residual, weight, (bf16*)y, res_out, rstd, M, D, eps));
     else
-      add_rmsnorm_fwd_kernel<NV, false><<<grid, block, 0, stream>>>(x, residual, weight, (bf16*)y, res_out, rstd, M, D, eps);
+      MB_CUDA(launch_pdl(add_rmsnorm_fwd_kernel<NV, false>, grid, block, 0, stream, x, residual, weight, (bf16*)y, res_out, rstd, M, D, eps));
   });
   return check_launch("add_rmsnorm_fwd");
 }
@@ -751,13 +761,13 @@ extern "C" int mb_add_rmsnorm_bwd(const float* r, const void* dy, const float* r
       if (g2 > num_sms() * per_sm) g2 = num_sms() * per_sm;                                                            \
       if (g2 > grid) g2 = grid;   /* never more partial rows than the caller's scratch holds */                        \
       grid = g2;                                                                                                       \
-      kern<<<grid, W_ * 32, smem, stream>>>(r, (const bf16*)dy, rstd, weight, dres_in, dres_out, (bf16*)dx_bf16,      \
-                                           scratch, M, D);                                                             \
+      MB_CUDA(launch_pdl(kern, dim3(grid), dim3(W_ * 32), smem, stream, r, (const bf16*)dy, rstd, weight, dres_in,    \
+                         dres_out, (bf16*)dx_bf16, scratch, M, D));                                                    \
     }
     if (nv == 3) LAUNCH_ADD_STAGED(3, 4) else if (nv == 6) LAUNCH_ADD_STAGED(6, 2) else LAUNCH_ADD_STAGED(10, 2)
 #undef LAUNCH_ADD_STAGED
     if (check_launch("add_rmsnorm_bwd/staged")) return 1;
-    colsum_partials_kernel<<<cdiv(D, 32), 1024, 0, stream>>>(scratch, dw, grid, D, dw_accumulate);
+    MB_CUDA(launch_pdl(colsum_partials_kernel, dim3(cdiv(D, 32)), dim3(1024), 0, stream, scratch, dw, grid, D, dw_accumulate));
     return check_launch("add_rmsnorm_bwd/colsum");
   }
   DISPATCH_NV(nv, {
@@ -765,7 +775,7 @@ extern "C" int mb_add_rmsnorm_bwd(const float* r, const void* dy, const float* r
         r, (const bf16*)dy, rstd, weight, dres_in, dres_out, (bf16*)dx_bf16, scratch, M, D);
   });
   if (check_launch("add_rmsnorm_bwd")) return 1;
-  colsum_partials_kernel<<<cdiv(D, 32), 1024, 0, stream>>>(scratch, dw, grid, D, dw_accumulate);
+  MB_CUDA(launch_pdl(colsum_partials_kernel, dim3(cdiv(D, 32)), dim3(1024), 0, stream, scratch, dw, grid, D, dw_accumulate));
   return check_launch("add_rmsnorm_bwd/colsum");
 }
 
@@ -790,7 +800,8 @@ extern "C" int mb_gated_rmsnorm_fwd(const void* x, int ldx, const void* z, int l
       }                                                                                                                \
       int g2 = cdiv(M, W_);                                                                                            \
       if (g2 > num_sms() * per_sm) g2 = num_sms() * per_sm;                                                            \
-      kern<<<g2, W_ * 32, smem, stream>>>((const bf16*)x, ldx, (const bf16*)z, ldz, weight, (bf16*)out, ldo, rstd, M, D, eps); \
+      MB_CUDA(launch_pdl(kern, dim3(g2), dim3(W_ * 32), smem, stream, (const bf16*)x, ldx, (const bf16*)z, ldz, weight, \
+                         (bf16*)out, ldo, rstd, M, D, eps));                                                           \
     }
     if (nv == 6) LAUNCH_GFWD_STAGED(6, 4) else LAUNCH_GFWD_STAGED(12, 2)
 #undef LAUNCH_GFWD_STAGED
@@ -831,13 +842,13 @@ extern "C" int mb_gated_rmsnorm_bwd(const void* x, int ldx, const void* z, int l
         const int cap = bwd_grid(M);                                                                                   \
         if (grid1 > num_sms() * per_sm) grid1 = num_sms() * per_sm;                                                    \
         if (grid1 > cap) grid1 = cap;                                                                                  \
-        kern<<<grid1, W_ * 32, smem, stream>>>((const bf16*)x, ldx, (const bf16*)z, ldz, weight, rstd, (const bf16*)dout, \
-                                              ldo, (bf16*)dx, lddx, (bf16*)dz, lddz, scratch, M, D);                   \
+        MB_CUDA(launch_pdl(kern, dim3(grid1), dim3(W_ * 32), smem, stream, (const bf16*)x, ldx, (const bf16*)z, ldz,  \
+                           weight, rstd, (const bf16*)dout, ldo, (bf16*)dx, lddx, (bf16*)dz, lddz, scratch, M, D));    \
       }
       if (nv == 6) LAUNCH_STAGED(6, 4) else LAUNCH_STAGED(12, 2)
 #undef LAUNCH_STAGED
       if (check_launch("gated_rmsnorm_bwd/rows_staged")) return 1;
-      colsum_partials_kernel<<<cdiv(D, 32), 1024, 0, stream>>>(scratch, dw, grid1, D, dw_accumulate);
+      MB_CUDA(launch_pdl(colsum_partials_kernel, dim3(cdiv(D, 32)), dim3(1024), 0, stream, scratch, dw, grid1, D, dw_accumulate));
       return check_launch("gated_rmsnorm_bwd/colsum");
     }
     DISPATCH_NV(nv, {
@@ -851,7 +862,7 @@ extern "C" int mb_gated_rmsnorm_bwd(const void* x, int ldx, const void* z, int l
           scratch, M, D);
     });
     if (check_launch("gated_rmsnorm_bwd/rows")) return 1;
-    colsum_partials_kernel<<<cdiv(D, 32), 1024, 0, stream>>>(scratch, dw, grid1, D, dw_accumulate);
+    MB_CUDA(launch_pdl(colsum_partials_kernel, dim3(cdiv(D, 32)), dim3(1024), 0, stream, scratch, dw, grid1, D, dw_accumulate));
     return check_launch("gated_rmsnorm_bwd/colsum");
   }
   const int grid = bwd_grid(M * G);
@@ -862,7 +873,7 @@ extern "C" int mb_gated_rmsnorm_bwd(const void* x, int ldx, const void* z, int l
         (bf16*)dz, lddz, scratch, M, G, group_size);
   });
   if (check_launch("gated_rmsnorm_bwd")) return 1;
-  colsum_partials_kernel<<<cdiv(D, 32), 1024, 0, stream>>>(scratch, dw, grid, D, dw_accumulate);
+  MB_CUDA(launch_pdl(colsum_partials_kernel, dim3(cdiv(D, 32)), dim3(1024), 0, stream, scratch, dw, grid, D, dw_accumulate));
   return check_launch("gated_rmsnorm_bwd/colsum");
 }
 
@@ -927,6 +938,6 @@ extern "C" int mb_add_rmsnorm_bwd_noalloc(const float* r, const void* dy, const 
         r, (const bf16*)dy, rstd, weight, dres_in, dres_out, (bf16*)dx_bf16, scratch, M, D);
   });
   if (check_launch("add_rmsnorm_bwd_noalloc")) return 1;
-  colsum_partials_kernel<<<cdiv(D, 32), 1024, 0, stream>>>(scratch, dw, grid, D, dw_accumulate);
+  MB_CUDA(launch_pdl(colsum_partials_kernel, dim3(cdiv(D, 32)), dim3(1024), 0, stream, scratch, dw, grid, D, dw_accumulate));
   return check_launch("add_rmsnorm_bwd_noalloc/colsum");
 }

@@ -1,6 +1,7 @@
 // Library runtime: error string, device queries, version.  Everything else in csrc/ is a
 // kernel family with its extern "C" launchers (declared in include/mamba_b200.h).
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -26,6 +27,15 @@ int check_launch(const char* what) {
     return 1;
   }
   return 0;
+}
+
+bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("MAMBA_B200_PDL");
+    on = (e != nullptr && e[0] == '0') ? 0 : 1;
+  }
+  return on == 1;
 }
 
 int num_sms() {

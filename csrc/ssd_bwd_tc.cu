@@ -49,6 +49,7 @@ ssd_dcb_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__
   if (warp == 0 && elect_one()) {
     mbar_init(bar, 1); mbar_init(&tile_bar[0], 1); mbar_init(&tile_bar[1], 1); mbar_init(ld_bar, 1);
     fence_mbar_init();
+    pdl_wait();   // the loads below read the previous kernel's output
     // C / B tiles for the CB block: two 64-column boxes each, straight away (they borrow the per-head buffers)
     mbar_arrive_expect_tx(ld_bar, 2 * 2 * 128 * 128);
     for (int kb = 0; kb < 2; ++kb) {
@@ -63,6 +64,8 @@ ssd_dcb_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__
   const uint32_t tmem = *tmem_slot;
   const uint32_t tCB = tmem + 128;
   uint32_t phase = 0;
+  pdl_wait();      // common.cuh: programmatic dependent launch
+  pdl_trigger();
 
   // CB block (rows ri0.., columns cj0..) once per CTA: needed for the row sums of dM o M below.
   // The C / B tiles borrow the per-head double buffer (2 x 32 KB) before the head loop starts.
@@ -269,6 +272,8 @@ ssd_dbdc_kernel(const __grid_constant__ CUtensorMap tmG,    // dCB   [B*nc*G*256
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  pdl_wait();      // common.cuh: programmatic dependent launch
+  pdl_trigger();
 
   // part 1: K = j in [0, (rb+1)*128) for dC ; K = i in [rb*128, 256) for dB   (64 per stage)
   const int k_begin = IS_DB ? m0 : 0;
@@ -422,7 +427,8 @@ extern "C" int mb_ssd_bwd_dcb(const void* dy, long long lddy, const void* x, lon
   if (make_tmap_bf16_3d(&tmDY, dy, B, T, (long long)H * P, lddy, 128, 64) || make_tmap_bf16_3d(&tmX, x, B, T, (long long)H * P, ldx, 128, 64) ||
       make_tmap_bf16_3d(&tmC, Cm, B, T, (long long)G * N, ldbc, 128, 64) || make_tmap_bf16_3d(&tmB, Bm, B, T, (long long)G * N, ldbc, 128, 64))
     return 1;
-  ssd_dcb_kernel<<<grid, kThreadsB, kDcbSmem, stream>>>(tmDY, tmX, tmC, tmB, dt, a, (bf16*)dcb, rowsum_m, T, H, G, nc);
+  MB_CUDA(launch_pdl(ssd_dcb_kernel, grid, dim3(kThreadsB), kDcbSmem, stream, tmDY, tmX, tmC, tmB, dt, a, (bf16*)dcb, rowsum_m,
+                     T, H, G, nc));
   return check_launch("ssd_bwd_dcb");
 }
 
@@ -447,8 +453,10 @@ extern "C" int mb_ssd_bwd_dbdc(const void* dcb, const void* Bm, const void* Cm, 
       make_tmap_bf16_2d(&tmSp, sprev_bf16, (long long)B * nc * H * P, N, N, 64) ||
       make_tmap_bf16_2d(&tmDs, ds_bf16, (long long)B * nc * H * P, N, N, 64))
     return 1;
-  ssd_dbdc_kernel<false><<<grid, kThreadsB, kDbdcSmem, stream>>>(tmG, tmBm, tmDy, tmSp, dt, a, (bf16*)dC, ldo, T, H, G, nc);
+  MB_CUDA(launch_pdl(ssd_dbdc_kernel<false>, grid, dim3(kThreadsB), kDbdcSmem, stream, tmG, tmBm, tmDy, tmSp, dt, a, (bf16*)dC,
+                     ldo, T, H, G, nc));
   if (check_launch("ssd_bwd_dbdc/dC")) return 1;
-  ssd_dbdc_kernel<true><<<grid, kThreadsB, kDbdcSmem, stream>>>(tmG, tmCm, tmX, tmDs, dt, a, (bf16*)dB, ldo, T, H, G, nc);
+  MB_CUDA(launch_pdl(ssd_dbdc_kernel<true>, grid, dim3(kThreadsB), kDbdcSmem, stream, tmG, tmCm, tmX, tmDs, dt, a, (bf16*)dB,
+                     ldo, T, H, G, nc));
   return check_launch("ssd_bwd_dbdc/dB");
 }

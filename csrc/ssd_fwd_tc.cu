@@ -165,6 +165,8 @@ ssd_states_seq_kernel(const bf16* __restrict__ arow, long long lda, const __grid
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  pdl_wait();      // common.cuh: programmatic dependent launch
+  pdl_trigger();
 
   float run[64];   // this thread's 64 columns (colhalf * 64 ..) of the carried state / gradient
   {
@@ -396,6 +398,7 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
       mbar_init(&acc_empty[i], kScanWarpsEpi); mbar_init(&tiles_full[i], 1); mbar_init(&tiles_empty[i], kScanWarpsEpi);
     }
     fence_mbar_init();
+    pdl_wait();   // the loads below read the previous kernel's output (common.cuh: programmatic dependent launch)
     mbar_arrive_expect_tx(ld_bar, (uint32_t)((128 + ncols) * 2 * 128));
     for (int kb = 0; kb < 2; ++kb) {
       tma_load_3d(sR + kb * 128 * 128, &tmRow, ld_bar, g * kN + kb * 64, c * kL + r0, b);
@@ -406,6 +409,8 @@ ssd_scan_kernel(const __grid_constant__ CUtensorMap tmRow, const __grid_constant
     if (hgs > 1) issue_head(1);
   }
   if (warp == kScanWarpsScale + kScanWarpsEpi) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
+  pdl_wait();      // common.cuh: programmatic dependent launch
+  pdl_trigger();
 
   // ---- prologue: a | dt of every head of the group (2 KB each, cp.async by everyone) ----
   for (int i = tid; i < hgs * kL; i += kScanThreads) {
@@ -835,13 +840,13 @@ extern "C" int mb_ssd_states_seq(const void* arow, long long lda, const void* bo
   if (dstate) {
     static bool once = false;
     if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_states_seq_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSeqSmem)); once = true; }
-    ssd_states_seq_kernel<true><<<grid, kThreads, kSeqSmem, stream>>>((const bf16*)arow, lda, tmBop, dt, a, tmOut, (const bf16*)sprev_bf16,
-                                                                        da_last, init, last_out, T, H, G, nc);
+    MB_CUDA(launch_pdl(ssd_states_seq_kernel<true>, grid, dim3(kThreads), kSeqSmem, stream, (const bf16*)arow, lda, tmBop, dt, a,
+                       tmOut, (const bf16*)sprev_bf16, da_last, init, last_out, T, H, G, nc));
   } else {
     static bool once = false;
     if (!once) { MB_CUDA(cudaFuncSetAttribute(ssd_states_seq_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSeqSmem)); once = true; }
-    ssd_states_seq_kernel<false><<<grid, kThreads, kSeqSmem, stream>>>((const bf16*)arow, lda, tmBop, dt, a, tmOut, nullptr, nullptr,
-                                                                         init, last_out, T, H, G, nc);
+    MB_CUDA(launch_pdl(ssd_states_seq_kernel<false>, grid, dim3(kThreads), kSeqSmem, stream, (const bf16*)arow, lda, tmBop, dt, a,
+                       tmOut, (const bf16*)nullptr, (float*)nullptr, init, last_out, T, H, G, nc));
   }
   return check_launch("ssd_states_seq");
 }
@@ -864,8 +869,8 @@ extern "C" int mb_ssd_chunk_scan_fwd(const void* Cm, const void* Bm, long long l
   CUtensorMap tmOut, tmOut2;
   if (make_tmap_bf16_3d(&tmOut, y, B, T, (long long)H * P, ldy, 32, 32) ||
       make_tmap_bf16_3d(&tmOut2, y_off, B, T, (long long)H * P, ldy, 32, 32)) return 1;
-  ssd_scan_kernel<false><<<grid, kScanThreads, kScanSmem, stream>>>(tmRow, tmCol, tmV, tmS, tmOut, tmOut2, dt, a, D,
-                                                                nullptr, nullptr, nullptr, T, H, G, nc, hgs);
+  MB_CUDA(launch_pdl(ssd_scan_kernel<false>, grid, dim3(kScanThreads), kScanSmem, stream, tmRow, tmCol, tmV, tmS, tmOut, tmOut2,
+                     dt, a, D, (float*)nullptr, (float*)nullptr, (float*)nullptr, T, H, G, nc, hgs));
   return check_launch("ssd_chunk_scan_fwd");
 }
 
@@ -890,6 +895,7 @@ extern "C" int mb_ssd_chunk_scan_bwd_dx(const void* Bm, const void* Cm, long lon
   CUtensorMap tmOut, tmX;  // the kernel's second output map is unused in backward: it carries x instead
   if (make_tmap_bf16_3d(&tmOut, dx, B, T, (long long)H * P, lddx, 32, 32) ||
       make_tmap_bf16_3d(&tmX, x, B, T, (long long)H * P, ldx, 32, 32)) return 1;
-  ssd_scan_kernel<true><<<grid, kScanThreads, kScanSmem, stream>>>(tmRow, tmCol, tmV, tmS, tmOut, tmX, dt, a, D, ddt1, ddt2, dD, T, H, G, nc, hgs);
+  MB_CUDA(launch_pdl(ssd_scan_kernel<true>, grid, dim3(kScanThreads), kScanSmem, stream, tmRow, tmCol, tmV, tmS, tmOut, tmX, dt, a,
+                     D, ddt1, ddt2, dD, T, H, G, nc, hgs));
   return check_launch("ssd_chunk_scan_bwd_dx");
 }

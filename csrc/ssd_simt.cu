@@ -22,6 +22,8 @@ __global__ void ssd_prep_kernel(const bf16* __restrict__ dt_raw, long long ld_dt
                                 float* __restrict__ dt_out, float* __restrict__ a_out, int T, int H, int L,
                                 int nc, float dt_min, float dt_max) {
   extern __shared__ float sm[];  // [kPrepHeads][L] dA, then scanned in place
+  pdl_wait();      // common.cuh: programmatic dependent launch
+  pdl_trigger();
   const int b = blockIdx.x / nc, c = blockIdx.x % nc;
   const int h0 = blockIdx.y * kPrepHeads;
   const int t = threadIdx.x;
@@ -145,6 +147,8 @@ __global__ void ssd_bwd_finalize_kernel(const bf16* __restrict__ dy, long long l
   __shared__ float wsum[8];
   __shared__ float red3[2][8];
   __shared__ float s_rowpart[256];
+  pdl_wait();      // common.cuh: programmatic dependent launch
+  pdl_trigger();
   // heads are the fastest grid index: blocks resident together read neighbouring 128-byte pieces of the same dY /
   // y_off rows (and write neighbouring bf16 d(dt) columns), not the same piece of 128 different chunks
   const int b = blockIdx.y / nc, c = blockIdx.y % nc;
@@ -282,8 +286,8 @@ extern "C" int mb_ssd_prep(const void* dt_raw, long long ld_dt, const float* dt_
   MB_REQUIRE(L == 64 || L == 128 || L == 256, "ssd_prep: chunk size %d not in {64,128,256}", L);
   const int nc = cdiv(T, L);
   const size_t smem = (size_t)kPrepHeads * L * sizeof(float);
-  ssd_prep_kernel<<<dim3(B * nc, cdiv(H, kPrepHeads)), L, smem, stream>>>((const bf16*)dt_raw, ld_dt, dt_bias, A_log, dt_out,
-                                                                          a_out, T, H, L, nc, dt_min, dt_max);
+  MB_CUDA(launch_pdl(ssd_prep_kernel, dim3(B * nc, cdiv(H, kPrepHeads)), dim3(L), smem, stream, (const bf16*)dt_raw, ld_dt,
+                     dt_bias, A_log, dt_out, a_out, T, H, L, nc, dt_min, dt_max));
   return check_launch("ssd_prep");
 }
 
@@ -319,10 +323,9 @@ extern "C" int mb_ssd_bwd_finalize(const void* dy, long long lddy, const void* y
              "ssd_bwd_finalize: headdim %d must be a power of two in [8, 256] (lanes of one row reduce by shuffles)", P);
   const int nc = cdiv(T, L);
   MB_REQUIRE((long long)B * nc <= 65535, "ssd_bwd_finalize: B * chunks = %lld exceeds the grid's y extent", (long long)B * nc);
-  ssd_bwd_finalize_kernel<<<dim3(H, B * nc), L, 0, stream>>>((const bf16*)dy, lddy, (const bf16*)y_off, ldy,
-                                                    (const bf16*)dt_raw, ld_dt, dt, ddt1, ddt2, rowsum_m, da_last, dt_bias,
-                                                    A_log, (bf16*)draw_out, ld_draw, dA_log, ddt_bias, T, H, P, L, nc,
-                                                    dt_min, dt_max);
+  MB_CUDA(launch_pdl(ssd_bwd_finalize_kernel, dim3(H, B * nc), dim3(L), 0, stream, (const bf16*)dy, lddy, (const bf16*)y_off,
+                     ldy, (const bf16*)dt_raw, ld_dt, dt, ddt1, ddt2, rowsum_m, da_last, dt_bias, A_log, (bf16*)draw_out,
+                     ld_draw, dA_log, ddt_bias, T, H, P, L, nc, dt_min, dt_max));
   return check_launch("ssd_bwd_finalize");
 }
 

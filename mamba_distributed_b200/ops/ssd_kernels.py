@@ -95,8 +95,12 @@ def ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, s
     lddy = dy.stride(0)
     ds = torch.empty(Bsz, nc, H, P, N, dtype=torch.bfloat16, device=dev)
     dinit = None
+    # one zero fill per layer for everything the kernels accumulate into: ddt1 | ddt2 | row sums of dM o M | da_last
+    n12 = Bsz * nc * H * L
+    zeroed = torch.zeros(3 * n12 + Bsz * nc * H, dtype=torch.float32, device=dev)
+    ddt12 = zeroed[:3 * n12].view(3, Bsz, nc, H, L)
     if _seq_states(Bsz, H, G, dfinal_states is not None or want_dinitial):
-        da_last = torch.zeros(Bsz, nc, H, dtype=torch.float32, device=dev)
+        da_last = zeroed[3 * n12:].view(Bsz, nc, H)
         dinit = torch.empty(Bsz, H, P, N, dtype=torch.float32, device=dev) if want_dinitial else None
         dfin = dfinal_states.float().contiguous() if dfinal_states is not None else None
         call("mb_ssd_states_seq", dy, lddy, Cm, ld, dt, a, ds, sprev, da_last, dfin, dinit, 1, Bsz, T, H, G, P, N, L)
@@ -105,7 +109,6 @@ def ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, s
         call("mb_ssd_chunk_state", dy, lddy, Cm, ld, dt, a, dstates, 1, Bsz, T, H, G, P, N, L)
         da_last = torch.empty(Bsz, nc, H, dtype=torch.float32, device=dev)
         call("mb_ssd_state_passing_bwd", dstates, sprev, a, ds, da_last, Bsz, nc, H, P * N, L)
-    ddt12 = torch.zeros(3, Bsz, nc, H, L, dtype=torch.float32, device=dev)  # ddt1 | ddt2 | row sums of dM o M
     lddx = dxBC.stride(0)
     if red_out is not None:   # (ddt_bias, dA_log, dD) fp32 [H] buffers the kernels add into (parameter .grad)
         red = (red_out[1], red_out[0], red_out[2])
