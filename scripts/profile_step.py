@@ -1,5 +1,8 @@
 """Per-kernel device-time breakdown of one training micro-step (torch.profiler / CUPTI)."""
 import os, sys, time, json
+# per-kernel durations are only meaningful without programmatic dependent launch (a dependent kernel's duration
+# would include the time it waits for its predecessor); PDL=1 in the environment measures the overlapped timeline
+os.environ.setdefault("MAMBA_B200_PDL", "0")
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from torch.profiler import profile, ProfilerActivity
