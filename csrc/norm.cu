@@ -484,7 +484,8 @@ __global__ void __launch_bounds__(WARPS * 32)
 gated_rmsnorm_bwd_rows_staged_kernel(const bf16* __restrict__ x, int ldx, const bf16* __restrict__ z, int ldz,
                                      const float* __restrict__ weight, const float* __restrict__ rstd_in,
                                      const bf16* __restrict__ dout, int ldo, bf16* __restrict__ dx, int lddx,
-                                     bf16* __restrict__ dz, int lddz, float* __restrict__ dw_partial, int M, int D) {
+                                     bf16* __restrict__ dz, int lddz, float* __restrict__ dw_partial, int M, int D,
+                                     int dw_atomic) {   // 1: dw_partial is the gradient itself, added to with atomics
   extern __shared__ __align__(16) uint8_t st_smem[];
   constexpr int ROWB = NV * 32 * 16;                 // bytes of one staged row of one operand (D = NV * 256 exactly)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -577,7 +578,8 @@ gated_rmsnorm_bwd_rows_staged_kernel(const bf16* __restrict__ x, int ldx, const 
       float sum = 0.f;
 #pragma unroll
       for (int ww = 0; ww < WARPS; ++ww) sum += red[ww * 264 + k];
-      my_partial[i * 256 + k] = sum;
+      if (dw_atomic) atomicAdd(dw_partial + i * 256 + k, sum);   // 600 blocks x D adds spread over D addresses
+      else my_partial[i * 256 + k] = sum;
     }
   }
 }
@@ -592,7 +594,7 @@ template <int NV, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32)
 add_rmsnorm_bwd_staged_kernel(const float* __restrict__ r, const bf16* __restrict__ dy, const float* __restrict__ rstd_in,
                               const float* __restrict__ weight, const float* dres_in, float* dres_out,
-                              bf16* __restrict__ dx_bf16, float* __restrict__ dw_partial, int M, int D) {
+                              bf16* __restrict__ dx_bf16, float* __restrict__ dw_partial, int M, int D, int dw_atomic) {
   extern __shared__ __align__(16) uint8_t st_smem[];
   constexpr int RB = NV * 32 * 32;     // bytes of one staged fp32 row (D = NV * 256)
   constexpr int GB = NV * 32 * 16;     // bytes of one staged bf16 row
@@ -685,7 +687,8 @@ add_rmsnorm_bwd_staged_kernel(const float* __restrict__ r, const bf16* __restric
       float sum = 0.f;
 #pragma unroll
       for (int ww = 0; ww < WARPS; ++ww) sum += red[ww * 264 + k];
-      my_partial[i * 256 + k] = sum;
+      if (dw_atomic) atomicAdd(dw_partial + i * 256 + k, sum);   // 600 blocks x D adds spread over D addresses
+      else my_partial[i * 256 + k] = sum;
     }
   }
 }
@@ -762,11 +765,13 @@ extern "C" int mb_add_rmsnorm_bwd(const float* r, const void* dy, const float* r
       if (g2 > grid) g2 = grid;   /* never more partial rows than the caller's scratch holds */                        \
       grid = g2;                                                                                                       \
       MB_CUDA(launch_pdl(kern, dim3(grid), dim3(W_ * 32), smem, stream, r, (const bf16*)dy, rstd, weight, dres_in,    \
-                         dres_out, (bf16*)dx_bf16, scratch, M, D));                                                    \
+                         dres_out, (bf16*)dx_bf16, dw_accumulate ? dw : scratch, M, D, dw_accumulate ? 1 : 0));        \
     }
     if (nv == 3) LAUNCH_ADD_STAGED(3, 4) else if (nv == 6) LAUNCH_ADD_STAGED(6, 2) else LAUNCH_ADD_STAGED(10, 2)
 #undef LAUNCH_ADD_STAGED
     if (check_launch("add_rmsnorm_bwd/staged")) return 1;
+    // accumulating into an existing gradient (training): the blocks added their column sums with atomics, no second launch
+    if (dw_accumulate) return 0;
     MB_CUDA(launch_pdl(colsum_partials_kernel, dim3(cdiv(D, 32)), dim3(1024), 0, stream, scratch, dw, grid, D, dw_accumulate));
     return check_launch("add_rmsnorm_bwd/colsum");
   }
@@ -843,11 +848,13 @@ extern "C" int mb_gated_rmsnorm_bwd(const void* x, int ldx, const void* z, int l
         if (grid1 > num_sms() * per_sm) grid1 = num_sms() * per_sm;                                                    \
         if (grid1 > cap) grid1 = cap;                                                                                  \
         MB_CUDA(launch_pdl(kern, dim3(grid1), dim3(W_ * 32), smem, stream, (const bf16*)x, ldx, (const bf16*)z, ldz,  \
-                           weight, rstd, (const bf16*)dout, ldo, (bf16*)dx, lddx, (bf16*)dz, lddz, scratch, M, D));    \
+                           weight, rstd, (const bf16*)dout, ldo, (bf16*)dx, lddx, (bf16*)dz, lddz,                     \
+                           dw_accumulate ? dw : scratch, M, D, dw_accumulate ? 1 : 0));                                \
       }
       if (nv == 6) LAUNCH_STAGED(6, 4) else LAUNCH_STAGED(12, 2)
 #undef LAUNCH_STAGED
       if (check_launch("gated_rmsnorm_bwd/rows_staged")) return 1;
+      if (dw_accumulate) return 0;   // column sums already added to dw with atomics
       MB_CUDA(launch_pdl(colsum_partials_kernel, dim3(cdiv(D, 32)), dim3(1024), 0, stream, scratch, dw, grid1, D, dw_accumulate));
       return check_launch("gated_rmsnorm_bwd/colsum");
     }

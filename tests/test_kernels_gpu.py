@@ -82,7 +82,8 @@ def test_gemm_strided_operands():
     _close(y, x.float() @ w.float().t(), 2e-2, 2e-2, "strided A")
 
 
-@pytest.mark.parametrize("M,D", [(64, 768), (1000, 768), (33, 256), (129, 1536), (50, 2560)])
+@pytest.mark.parametrize("M,D", [(64, 768), (1000, 768), (33, 256), (129, 1536), (50, 2560),
+                                 (9001, 768), (7000, 1536), (5000, 2560)])   # several rows per persistent warp
 @pytest.mark.parametrize("x_fp32,has_res", [(False, True), (True, False), (False, False)])
 def test_add_rmsnorm_fwd_bwd(M, D, x_fp32, has_res):
     nat = _native()
@@ -108,7 +109,8 @@ def test_add_rmsnorm_fwd_bwd(M, D, x_fp32, has_res):
     _close(wn.grad, wr.grad, 2e-2 * M ** 0.5, 2e-2, "dw")
 
 
-@pytest.mark.parametrize("M,D,G", [(100, 1536, 1), (64, 512, 1), (37, 512, 2), (50, 3072, 1)])
+@pytest.mark.parametrize("M,D,G", [(100, 1536, 1), (64, 512, 1), (37, 512, 2), (50, 3072, 1),
+                                   (9001, 1536, 1), (4000, 3072, 1)])   # several rows per persistent warp
 def test_gated_rmsnorm_fwd_bwd(M, D, G):
     nat = _native()
     torch.manual_seed(0)
