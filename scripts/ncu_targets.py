@@ -1,5 +1,5 @@
 """Runs every kernel of the library a few times at the 280M benchmark shape (B = 32, T = 1024) so that
-`ncu -k regex:<name> -s N -c 1` captures a warm launch.  Usage: python scripts/ncu_targets.py [which]
+`ncu --profile-from-start off -k regex:<name>` captures the third (warm) iteration.  Usage: python scripts/ncu_targets.py [which]
 which: conv | ssd | norm | gemm | ce | sscan | comm | all"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -26,6 +26,9 @@ def sel(*names):
 
 
 for it in range(3):
+    if it == 2:   # `ncu --profile-from-start off` captures exactly this (warm) iteration
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
     if sel("conv"):
         nat.k_conv1d_fwd(zx.view(B, T, -1)[:, :, d_in:d_in + conv_dim], cw, cb, xBC.view(B, T, conv_dim), True)
         dxBC = torch.randn_like(xBC); dzx = torch.empty_like(zx); dcw = torch.zeros_like(cw); dcb = torch.zeros_like(cb)
@@ -80,4 +83,5 @@ for it in range(3):
         ddp.flat_grad.normal_()
         opt.step(max_norm=1.0)
 torch.cuda.synchronize()
+torch.cuda.profiler.stop()
 print("done")
