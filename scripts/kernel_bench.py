@@ -53,10 +53,11 @@ def main():
             fn = lambda i: native.gated_rms_norm(ys[i], zx[i].view(B * T, -1)[:, :d_inner], wn, 1e-5, d_inner)
             nbytes = 3 * B * T * d_inner * 2
         else:
-            leaves = [(ys[i].clone().requires_grad_(True), zx[i].clone().requires_grad_(True)) for i in range(n_sets)]
-            wp = wn.clone().requires_grad_(True)
-            outs = [native.gated_rms_norm(a, b_.view(B * T, -1)[:, :d_inner], wp, 1e-5, d_inner) for a, b_ in leaves]
-            fn = lambda i: outs[i].backward(dos[i], retain_graph=True)
+            out0, rstd = native.k_gated_rmsnorm_fwd(ys[0], zx[0].view(B * T, -1)[:, :d_inner], wn, 1e-5, d_inner)
+            dxs = [torch.empty_like(ys[0]) for _ in range(n_sets)]
+            dzs = [torch.empty_like(zx[0]) for _ in range(n_sets)]
+            fn = lambda i: native.k_gated_rmsnorm_bwd(ys[i], zx[i].view(B * T, -1)[:, :d_inner], wn, rstd, dos[i], dxs[i],
+                                                      dzs[i].view(B * T, -1)[:, :d_inner], d_inner)
             nbytes = 5 * B * T * d_inner * 2
     else:
         raise SystemExit("unknown kernel")
