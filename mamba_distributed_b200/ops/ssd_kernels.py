@@ -12,6 +12,8 @@ Everything reads x | B | C as column slices of the conv output and writes dx | d
 matching slices of ``dxBC`` and d(dt_raw) into the dt columns of ``d(zxbcdt)``."""
 from __future__ import annotations
 
+import os
+
 import torch
 
 from . import _lib
@@ -22,6 +24,20 @@ INF = float("inf")
 
 
 FORCE_SEQ_STATES = None   # tests set True / False to pin one of the two state paths
+# backward: run kernels that do not depend on each other on a second stream (see ssd_bwd); MAMBA_B200_SSD_STREAMS=0 serialises
+TWO_STREAMS = os.environ.get("MAMBA_B200_SSD_STREAMS", "1") != "0"
+
+_side_streams = {}
+
+
+def _side_stream(dev):
+    """One extra stream per device for the independent branches of the backward (captured as parallel graph
+    branches when the step is being recorded)."""
+    key = (dev.type, dev.index if dev.index is not None else torch.cuda.current_device())
+    st = _side_streams.get(key)
+    if st is None:
+        st = _side_streams[key] = torch.cuda.Stream(device=dev)
+    return st
 
 
 def _seq_states(Bsz, H, G, need_boundary_states):
@@ -99,6 +115,26 @@ def ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, s
     n12 = Bsz * nc * H * L
     zeroed = torch.zeros(3 * n12 + Bsz * nc * H, dtype=torch.float32, device=dev)
     ddt12 = zeroed[:3 * n12].view(3, Bsz, nc, H, L)
+    lddx = dxBC.stride(0)
+    if red_out is not None:   # (ddt_bias, dA_log, dD) fp32 [H] buffers the kernels add into (parameter .grad)
+        red = (red_out[1], red_out[0], red_out[2])
+    else:
+        red = torch.zeros(3, H, dtype=torch.float32, device=dev)  # dA_log | ddt_bias | dD
+    dcb = torch.empty(Bsz, nc, G, L, L, dtype=torch.bfloat16, device=dev)
+    # Two branches that do not depend on each other: dCB needs only dy and the saved operands, while d(states) ->
+    # dx is a chain.  dCB (384 CTAs) and the fused d(states) kernel (384 CTAs) each fill 1.3 waves of the 296
+    # two-per-SM slots on their own; side by side they pack into 2.6.  Later, finalize (memory-bound, tiny blocks)
+    # runs beside the two dB / dC kernels (tensor / latency-bound, 0.86 wave each).
+    cur = torch.cuda.current_stream(dev)
+    side = _side_stream(dev) if TWO_STREAMS else None
+    if side is not None:
+        fork = torch.cuda.Event()
+        fork.record(cur)
+        side.wait_event(fork)
+        with torch.cuda.stream(side):
+            call("mb_ssd_bwd_dcb", dy, lddy, x, ld, Cm, Bm, ld, dt, a, dcb, ddt12[2], Bsz, T, H, G, P, N, L)
+            dcb_done = torch.cuda.Event()
+            dcb_done.record(side)
     if _seq_states(Bsz, H, G, dfinal_states is not None or want_dinitial):
         da_last = zeroed[3 * n12:].view(Bsz, nc, H)
         dinit = torch.empty(Bsz, H, P, N, dtype=torch.float32, device=dev) if want_dinitial else None
@@ -109,22 +145,32 @@ def ssd_bwd(dy, y, xBC, zxbcdt, dxBC, dzxbcdt, Bsz, T, cfg, dt_bias, A_log, D, s
         call("mb_ssd_chunk_state", dy, lddy, Cm, ld, dt, a, dstates, 1, Bsz, T, H, G, P, N, L)
         da_last = torch.empty(Bsz, nc, H, dtype=torch.float32, device=dev)
         call("mb_ssd_state_passing_bwd", dstates, sprev, a, ds, da_last, Bsz, nc, H, P * N, L)
-    lddx = dxBC.stride(0)
-    if red_out is not None:   # (ddt_bias, dA_log, dD) fp32 [H] buffers the kernels add into (parameter .grad)
-        red = (red_out[1], red_out[0], red_out[2])
-    else:
-        red = torch.zeros(3, H, dtype=torch.float32, device=dev)  # dA_log | ddt_bias | dD
     call("mb_ssd_chunk_scan_bwd_dx", Bm, Cm, ld, dy, lddy, ds, dt, a, D, dxBC, lddx, x, ld, ddt12[0], ddt12[1],
          red[2], Bsz, T, H, G, P, N, L)
-    dcb = torch.empty(Bsz, nc, G, L, L, dtype=torch.bfloat16, device=dev)
-    call("mb_ssd_bwd_dcb", dy, lddy, x, ld, Cm, Bm, ld, dt, a, dcb, ddt12[2], Bsz, T, H, G, P, N, L)
+    draw = dzxbcdt[:, dzxbcdt.shape[1] - H:]
+
+    def finalize():
+        call("mb_ssd_bwd_finalize", dy, lddy, y_ssm, y_ssm.stride(0), dt_raw, zxbcdt.stride(0), dt, ddt12[0], ddt12[1],
+             ddt12[2], da_last, dt_bias, A_log, draw, dzxbcdt.stride(0), red[0], red[1], Bsz, T, H, P, L,
+             float(dt_limit[0]), min(float(dt_limit[1]), 3.0e38))
+
     dB = dxBC[:, d_in:]
     dC = dxBC[:, d_in + G * N:]
-    call("mb_ssd_bwd_dbdc", dcb, Bm, Cm, ld, dy, lddy, x, ld, sprev, ds, dt, a, dB, dC, lddx, Bsz, T, H, G, P, N, L)
-    draw = dzxbcdt[:, dzxbcdt.shape[1] - H:]
-    call("mb_ssd_bwd_finalize", dy, lddy, y_ssm, y_ssm.stride(0), dt_raw, zxbcdt.stride(0), dt, ddt12[0], ddt12[1],
-         ddt12[2], da_last, dt_bias, A_log, draw, dzxbcdt.stride(0), red[0], red[1], Bsz, T, H, P, L,
-         float(dt_limit[0]), min(float(dt_limit[1]), 3.0e38))
+    if side is not None:
+        cur.wait_event(dcb_done)          # dB / dC and finalize both need dCB's outputs
+        fork2 = torch.cuda.Event()
+        fork2.record(cur)                 # ... and finalize needs the dx kernel's d(dt) partials
+        side.wait_event(fork2)
+        with torch.cuda.stream(side):
+            finalize()
+            fin_done = torch.cuda.Event()
+            fin_done.record(side)
+        call("mb_ssd_bwd_dbdc", dcb, Bm, Cm, ld, dy, lddy, x, ld, sprev, ds, dt, a, dB, dC, lddx, Bsz, T, H, G, P, N, L)
+        cur.wait_event(fin_done)
+    else:
+        call("mb_ssd_bwd_dcb", dy, lddy, x, ld, Cm, Bm, ld, dt, a, dcb, ddt12[2], Bsz, T, H, G, P, N, L)
+        call("mb_ssd_bwd_dbdc", dcb, Bm, Cm, ld, dy, lddy, x, ld, sprev, ds, dt, a, dB, dC, lddx, Bsz, T, H, G, P, N, L)
+        finalize()
     if want_dinitial:
         return red[1], red[0], red[2], dinit
     return red[1], red[0], red[2]  # ddt_bias, dA_log, dD
