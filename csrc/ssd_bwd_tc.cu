@@ -453,10 +453,16 @@ extern "C" int mb_ssd_bwd_dbdc(const void* dcb, const void* Bm, const void* Cm, 
       make_tmap_bf16_2d(&tmSp, sprev_bf16, (long long)B * nc * H * P, N, N, 64) ||
       make_tmap_bf16_2d(&tmDs, ds_bf16, (long long)B * nc * H * P, N, N, 64))
     return 1;
-  MB_CUDA(launch_pdl(ssd_dbdc_kernel<false>, grid, dim3(kThreadsB), kDbdcSmem, stream, tmG, tmBm, tmDy, tmSp, dt, a, (bf16*)dC,
-                     ldo, T, H, G, nc));
-  if (check_launch("ssd_bwd_dbdc/dC")) return 1;
-  MB_CUDA(launch_pdl(ssd_dbdc_kernel<true>, grid, dim3(kThreadsB), kDbdcSmem, stream, tmG, tmCm, tmX, tmDs, dt, a, (bf16*)dB,
-                     ldo, T, H, G, nc));
-  return check_launch("ssd_bwd_dbdc/dB");
+  // dB or dC may be null: the two kernels are independent, a caller can put them on different streams
+  if (dC != nullptr) {
+    MB_CUDA(launch_pdl(ssd_dbdc_kernel<false>, grid, dim3(kThreadsB), kDbdcSmem, stream, tmG, tmBm, tmDy, tmSp, dt, a,
+                       (bf16*)dC, ldo, T, H, G, nc));
+    if (check_launch("ssd_bwd_dbdc/dC")) return 1;
+  }
+  if (dB != nullptr) {
+    MB_CUDA(launch_pdl(ssd_dbdc_kernel<true>, grid, dim3(kThreadsB), kDbdcSmem, stream, tmG, tmCm, tmX, tmDs, dt, a,
+                       (bf16*)dB, ldo, T, H, G, nc));
+    if (check_launch("ssd_bwd_dbdc/dB")) return 1;
+  }
+  return 0;
 }

@@ -119,6 +119,7 @@ int mb_ssd_chunk_scan_bwd_dx(const void* Bm, const void* Cm, long long ldbc, con
 int mb_ssd_bwd_dcb(const void* dy, long long lddy, const void* x, long long ldx, const void* Cm,
                    const void* Bm, long long ldbc, const float* dt, const float* a, void* dcb,
                    float* rowsum_m, int B, int T, int H, int G, int P, int N, int L, cudaStream_t stream);
+/* dB or dC may be NULL: that kernel is skipped (the two are independent and may run on different streams). */
 int mb_ssd_bwd_dbdc(const void* dcb, const void* Bm, const void* Cm, long long ldbc, const void* dy,
                     long long lddy, const void* x, long long ldx, const void* sprev_bf16,
                     const void* ds_bf16, const float* dt, const float* a, void* dB, void* dC, long long ldo,
