@@ -5,7 +5,6 @@ import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from mamba_distributed_b200.ops import ce_native, native as nat, ssd_kernels
-from mamba_distributed_b200.ops._lib import call
 
 which = sys.argv[1] if len(sys.argv) > 1 else "all"
 dev = "cuda"

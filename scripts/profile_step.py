@@ -1,5 +1,5 @@
 """Per-kernel device-time breakdown of one training micro-step (torch.profiler / CUPTI)."""
-import os, sys, time, json
+import os, sys, time
 # per-kernel durations are only meaningful without programmatic dependent launch (a dependent kernel's duration
 # would include the time it waits for its predecessor); PDL=1 in the environment measures the overlapped timeline
 os.environ.setdefault("MAMBA_B200_PDL", "0")
