@@ -5,7 +5,6 @@ Mirrors the pre-norm block of the upstream model body the reference builds
 in fp32, and the add is fused into the norm (K14)."""
 from __future__ import annotations
 
-import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
