@@ -14,15 +14,22 @@ for i, h in enumerate(hdr):
         print(f"{h} = {vals[i]} {rows[1][i]}")
 src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(src)))
-hdr, data = rows[1], rows[2:]
-iS, isrc, iex = hdr.index('# Samples'), hdr.index('Source'), hdr.index('Instructions Executed')
-sc = [i for i, h in enumerate(hdr) if h.startswith('stall_') and 'Not Issued' not in h]
-print("total samples", sum(int(r[iS]) for r in data), "warp-instr", sum(int(r[iex]) for r in data))
-agg = {hdr[i]: sum(int(r[i]) for r in data) for i in sc}
-print(sorted(agg.items(), key=lambda kv: -kv[1])[:8])
 n = int(sys.argv[2]) if len(sys.argv) > 2 else 24
-top = sorted(range(len(data)), key=lambda i: -int(data[i][iS]))[:n]
-for i in sorted(top):
-    r = data[i]
-    rs = sorted([(hdr[c], int(r[c])) for c in sc if int(r[c]) > 0], key=lambda kv: -kv[1])[:2]
-    print(i, r[iS], r[iex], r[isrc].strip()[:64], rs)
+# the source page repeats "<kernel line>, <header>, <rows...>" for every kernel of the report
+heads = [i for i, r in enumerate(rows) if '# Samples' in r and 'Source' in r]
+for k, h0 in enumerate(heads):
+    hdr = rows[h0]
+    end = heads[k + 1] - 1 if k + 1 < len(heads) else len(rows)
+    iS, isrc, iex = hdr.index('# Samples'), hdr.index('Source'), hdr.index('Instructions Executed')
+    data = [r for r in rows[h0 + 1:end] if len(r) == len(hdr) and r[iS].strip().isdigit()]
+    sc = [i for i, h in enumerate(hdr) if h.startswith('stall_') and 'Not Issued' not in h]
+    title = " ".join(rows[h0 - 1])[:120] if h0 > 0 else ""
+    print(f"==== kernel {k}: {title}")
+    print("total samples", sum(int(r[iS]) for r in data), "warp-instr", sum(int(r[iex]) for r in data if r[iex].strip().isdigit()))
+    agg = {hdr[i]: sum(int(r[i]) for r in data if r[i].strip().isdigit()) for i in sc}
+    print(sorted(agg.items(), key=lambda kv: -kv[1])[:8])
+    top = sorted(range(len(data)), key=lambda i: -int(data[i][iS]))[:n]
+    for i in sorted(top):
+        r = data[i]
+        rs = sorted([(hdr[c], int(r[c])) for c in sc if r[c].strip().isdigit() and int(r[c]) > 0], key=lambda kv: -kv[1])[:2]
+        print(i, r[iS], r[iex], r[isrc].strip()[:64], rs)
