@@ -441,6 +441,13 @@ static void conv_flat_tiles(long long N, int ngroups, int warps_per_sm, int* til
   *ntiles = (int)cdiv(N, (long long)best_tile);
 }
 
+// Host-only view of the planner (no kernel launch): lets the work decomposition be checked without a GPU.
+extern "C" int mb_conv1d_plan(long long tokens, int column_groups, int warps_per_sm, int* tile, int* ntiles) {
+  MB_REQUIRE(tokens > 0 && column_groups > 0 && warps_per_sm > 0, "conv1d_plan: arguments must be positive");
+  conv_flat_tiles(tokens, column_groups, warps_per_sm, tile, ntiles);
+  return 0;
+}
+
 #define DISPATCH_W(W_, SILU_, ...)                                                     \
   if (W_ == 4 && SILU_) { constexpr int W = 4; constexpr bool S = true; __VA_ARGS__; }  \
   else if (W_ == 4) { constexpr int W = 4; constexpr bool S = false; __VA_ARGS__; }    \

@@ -64,6 +64,11 @@ int mb_conv1d_bwd(const void* x, long long ldx, const float* w, const float* bia
 int mb_conv1d_update(const void* x, long long ldx, float* state, const float* w, const float* bias,
                      void* y, long long ldy, int B, int C, int width, int silu, cudaStream_t stream);
 
+/* Work decomposition of the two conv kernels (host only, no launch): tokens = B*T on the flat token axis,
+ * column_groups = groups of 32 threads across the channels, warps_per_sm = resident warps per SM.  Returns the
+ * tile length (>= 64 tokens) and the number of tiles; work items = ntiles * column_groups, one per warp. */
+int mb_conv1d_plan(long long tokens, int column_groups, int warps_per_sm, int* tile, int* ntiles);
+
 /* ---- K18: embedding gather / scatter-add (ATen embedding fwd/bwd) ------------------------- */
 int mb_embedding_fwd(const long long* ids, const float* w, float* out, int M, int D, int V,
                      cudaStream_t stream);
