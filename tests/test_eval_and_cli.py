@@ -106,3 +106,28 @@ def test_eval_batched_equals_unbatched(tmp_path):
     finally:
         os.chdir(cwd)
     assert a == b and a["num_total"] == 8
+
+
+def test_eval_two_ranks_scores_what_one_rank_scores(tmp_path):
+    """A14 at world 2 (gloo): examples are sharded by index over the ranks and the counters summed, so the totals and
+    the accuracy line equal the single-process run on the same checkpoint."""
+    cwd = str(tmp_path)
+    r = _run([os.path.join(ROOT, "train.py"), "--device", "cpu", "--synthetic", "--d_model", "32", "--n_layer", "1",
+              "--vocab_size", "50304", "--B", "2", "--T", "32", "--total_batch_size", "128", "--max_steps", "2",
+              "--val_every", "100", "--val_steps", "1", "--sample_every", "100", "--ckpt_every", "1",
+              "--warmup_steps", "2"], cwd)
+    assert r.returncode == 0, r.stderr[-3000:]
+    ck = os.path.join(cwd, "log", "model_00001.pt")
+    assert os.path.exists(ck)
+    common = ["-m", "custom", "-d", "cpu", "-c", ck, "--synthetic", "--limit", "10", "--batch_examples", "2"]
+    one = _run([os.path.join(ROOT, "eval.py")] + common, cwd)
+    assert one.returncode == 0, one.stderr[-3000:]
+    res_one = open(os.path.join(cwd, "log", "hellaswag_eval.txt")).read().split()
+    os.remove(os.path.join(cwd, "log", "hellaswag_eval.txt"))
+    two = _run(["-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                "--master-port", "29777", os.path.join(ROOT, "eval.py")] + common, cwd,
+               env_extra={"OMP_NUM_THREADS": "2"})
+    assert two.returncode == 0, (two.stdout[-2000:], two.stderr[-3000:])
+    res_two = open(os.path.join(cwd, "log", "hellaswag_eval.txt")).read().split()
+    assert res_one[0] == res_two[0] == "10"
+    assert res_one[1] == res_two[1], (res_one, res_two)      # "<correct_norm>/10"
