@@ -132,3 +132,34 @@ def test_against_transformers_mamba2():
         a = ours(ids).logits
         b = hf(ids).logits
     assert torch.allclose(a, b, atol=2e-4, rtol=2e-4), (a - b).abs().max()
+
+
+def test_against_transformers_mamba1():
+    """Same check for the Mamba-1 mixer (the reference's literal default, SURVEY Finding 1): transformers'
+    MambaForCausalLM loaded with our state dict gives the same logits and the same loss gradient."""
+    tr = pytest.importorskip("transformers")
+    from mamba_distributed_b200.config import MambaConfig
+    from mamba_distributed_b200.models.lm import MambaLMHeadModel
+    torch.manual_seed(2)
+    cfg = MambaConfig(d_model=64, n_layer=2, vocab_size=128, ssm_cfg={"layer": "Mamba1"})
+    ours = MambaLMHeadModel(cfg)
+    hf_cfg = tr.MambaConfig(hidden_size=64, num_hidden_layers=2, vocab_size=128, state_size=16, expand=2,
+                            conv_kernel=4, use_bias=False, use_conv_bias=True, time_step_rank=4,
+                            layer_norm_epsilon=1e-5, residual_in_fp32=True, tie_word_embeddings=True,
+                            use_mambapy=False)
+    hf = tr.MambaForCausalLM(hf_cfg).eval()
+    sd = {k.replace("backbone.embedding.", "backbone.embeddings."): v for k, v in ours.state_dict().items()}
+    missing = hf.load_state_dict(sd, strict=False)
+    assert not missing.unexpected_keys, missing
+    assert all("lm_head" in k or "embeddings" in k for k in missing.missing_keys), missing
+    ids = torch.randint(0, 128, (2, 40))
+    with torch.no_grad():
+        a = ours(ids).logits
+        b = hf(ids).logits
+    assert torch.allclose(a, b, atol=2e-4, rtol=2e-4), (a - b).abs().max()
+    # gradient of a scalar loss w.r.t. one mixer parameter of the first layer
+    la = ours(ids).logits.float().square().mean()
+    lb = hf(ids).logits.float().square().mean()
+    ga = torch.autograd.grad(la, ours.backbone.layers[0].mixer.A_log)[0]
+    gb = torch.autograd.grad(lb, hf.backbone.layers[0].mixer.A_log)[0]
+    assert torch.allclose(ga, gb, atol=1e-5, rtol=1e-3), (ga - gb).abs().max()
