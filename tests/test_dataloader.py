@@ -78,3 +78,28 @@ def test_synthetic_source(tmp_path, monkeypatch):
     dl = DataLoaderLite(2, 16, 0, 1, "val", data_root="synthetic", pin=False)
     x, y = dl.next_batch()
     assert x.shape == (2, 16) and int(x.max()) < 50304
+
+
+def test_property_windows_match_bruteforce(tmp_path_factory):
+    """The same invariant over randomised geometries (hypothesis): any (B, T, world, shard sizes) whose shards hold at
+    least one full global batch reproduces the brute-force walk on every rank, across shard wrap-arounds."""
+    hyp = pytest.importorskip("hypothesis")
+    st = hyp.strategies
+
+    @hyp.settings(max_examples=25, deadline=None)
+    @hyp.given(B=st.integers(1, 3), T=st.integers(4, 40), world=st.integers(1, 4),
+               extra=st.lists(st.integers(0, 400), min_size=1, max_size=3), seed=st.integers(0, 10))
+    def check(B, T, world, extra, seed):
+        root = tmp_path_factory.mktemp("shards")
+        need = 2 * B * T * world + 1                      # every shard serves at least one window per rank
+        rng = np.random.default_rng(seed)
+        for i, e in enumerate(extra):
+            np.save(root / f"shard_train_{i:03d}.npy", rng.integers(0, 50000, need + e).astype(np.uint16))
+        shards = sorted(os.path.join(str(root), s) for s in os.listdir(root) if "train" in s)
+        for rank in range(world):
+            dl = DataLoaderLite(B, T, rank, world, "train", data_root=str(root), pin=False)
+            for ex, ey in _brute(shards, B, T, rank, world, 12):
+                x, y = dl.next_batch()
+                assert torch.equal(x, ex) and torch.equal(y, ey)
+
+    check()
