@@ -7,7 +7,8 @@ Forward : prep (softplus + dt_limit clamp + chunk cumsum) -> chunk states + inte
           chunk-state kernel + the stand-alone state-passing kernel instead.
 Backward: dstates + reverse recurrence (same fused kernel) -> dx + d(dt) partials (tcgen05) -> dCB
           (tcgen05) -> dB, dC (tcgen05, K-concatenated over heads) -> finalize (d dt_raw, dA_log,
-          d dt_bias, dD).
+          d dt_bias, dD).  dCB does not depend on the d(states) -> dx chain and runs beside it on a second
+          stream; after the join the dB kernel and finalize run beside the dC kernel (``TWO_STREAMS``).
 Everything reads x | B | C as column slices of the conv output and writes dx | dB | dC into the
 matching slices of ``dxBC`` and d(dt_raw) into the dt columns of ``d(zxbcdt)``."""
 from __future__ import annotations
